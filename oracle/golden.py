@@ -1,0 +1,109 @@
+"""ctypes front-end of oracle/golden_raster.c (numpy in, numpy out).
+
+TEST INFRASTRUCTURE ONLY.  Only tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs may import this module; the product package
+dirt_b200/ never does.  Parity status is stated in golden_raster.c's header:
+coverage pinned by the reference's KAT-1 / KAT-2, attribute values and gradients unpinned.
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "_build", "libgolden_raster.so")
+_lib = None
+
+
+def build(force=False):
+    src = os.path.join(_HERE, "golden_raster.c")
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-s", "-C", _HERE] + (["-B"] if force else []))
+    return _SO
+
+
+def _load():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(_SO):
+            build()
+        lib = ctypes.CDLL(_SO)
+        i32, i64, vp = ctypes.c_int, ctypes.c_int64, ctypes.c_void_p
+        lib.golden_rasterise_forward.argtypes = [i32] * 6 + [vp, i64, vp, i64, vp, i64, vp, i64, vp, vp, vp, i32]
+        lib.golden_rasterise_forward.restype = i32
+        lib.golden_rasterise_backward.argtypes = [i32] * 6 + [vp, i64, vp, vp, vp, vp, vp, i64, vp, i64, vp, i32]
+        lib.golden_rasterise_backward.restype = i32
+        lib.golden_num_threads.restype = i32
+        _lib = lib
+    return _lib
+
+
+def _prep(a, dtype, ndim, name):
+    a = np.ascontiguousarray(a, dtype=dtype)
+    if a.ndim == ndim - 1:
+        a = a[None]
+    if a.ndim != ndim:
+        raise ValueError("%s must have %d dims (or %d, unbatched)" % (name, ndim, ndim - 1))
+    return a
+
+
+def _bstride(a, B):
+    if a.shape[0] == B:
+        return int(np.prod(a.shape[1:]))
+    if a.shape[0] == 1:
+        return 0
+    raise ValueError("batch dim must be %d or 1" % B)
+
+
+def max_threads():
+    return int(_load().golden_num_threads())
+
+
+def forward(background, vertices, vertex_colors, faces, threads=1):
+    """Batched forward.  Inputs [B|1, ...]; returns pixels [B,H,W,C], face_id [B,H,W] (-1 =
+    background), gbuf [B,H,W,4] = (B0, B1, w_clip, zw)."""
+    lib = _load()
+    bg = _prep(background, np.float32, 4, "background")
+    v = _prep(vertices, np.float32, 3, "vertices")
+    c = _prep(vertex_colors, np.float32, 3, "vertex_colors")
+    f = _prep(faces, np.int32, 3, "faces")
+    B = max(bg.shape[0], v.shape[0], c.shape[0], f.shape[0])
+    _, H, W, C = bg.shape
+    V, F = v.shape[1], f.shape[1]
+    assert v.shape[2] == 4 and f.shape[2] == 3 and c.shape[1] == V and c.shape[2] == C
+    pixels = np.empty((B, H, W, C), np.float32)
+    face_id = np.empty((B, H, W), np.int32)
+    gbuf = np.empty((B, H, W, 4), np.float32)
+    rc = lib.golden_rasterise_forward(
+        B, H, W, C, V, F, bg.ctypes.data, _bstride(bg, B), v.ctypes.data, _bstride(v, B),
+        c.ctypes.data, _bstride(c, B), f.ctypes.data, _bstride(f, B),
+        pixels.ctypes.data, face_id.ctypes.data, gbuf.ctypes.data, int(threads))
+    if rc != 0:
+        raise RuntimeError("golden_rasterise_forward failed: %d" % rc)
+    return pixels, face_id, gbuf
+
+
+def backward(faces, pixels, grad_pixels, face_id, gbuf, V, shared_vertices=False, shared_colors=False,
+             threads=1):
+    """Batched backward.  Returns grad_vertices [B|1,V,4], grad_vertex_colors [B|1,V,C],
+    grad_background [B,H,W,C]."""
+    lib = _load()
+    px = _prep(pixels, np.float32, 4, "pixels")
+    g = _prep(grad_pixels, np.float32, 4, "grad_pixels")
+    f = _prep(faces, np.int32, 3, "faces")
+    fid = _prep(face_id, np.int32, 3, "face_id")
+    gb = _prep(gbuf, np.float32, 4, "gbuf")
+    B, H, W, C = px.shape
+    F = f.shape[1]
+    gv = np.zeros((1 if shared_vertices else B, V, 4), np.float32)
+    gc = np.zeros((1 if shared_colors else B, V, C), np.float32)
+    gbg = np.empty((B, H, W, C), np.float32)
+    rc = lib.golden_rasterise_backward(
+        B, H, W, C, V, F, f.ctypes.data, _bstride(f, B), px.ctypes.data, g.ctypes.data,
+        fid.ctypes.data, gb.ctypes.data,
+        gv.ctypes.data, 0 if shared_vertices else V * 4, gc.ctypes.data, 0 if shared_colors else V * C,
+        gbg.ctypes.data, int(threads))
+    if rc != 0:
+        raise RuntimeError("golden_rasterise_backward failed: %d" % rc)
+    return gv, gc, gbg
