@@ -1,0 +1,340 @@
+"""bench.py -- rasterise fwd+bwd throughput (Mpix/s) on the headline workload of BASELINE.json.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
+
+A "step" is one forward + one backward pass of the rasterise path over one batch of synthetic
+input.  Prints ONE JSON line (rank 0).  Under torchrun (N > 1) every rank renders its own batch
+shard (weak scaling, no data-path collective; the `c5` shared-mesh workload adds the NCCL
+allreduce of the vertex gradients).
+
+  value         whole-job Mpix/s, inputs resident in HBM, CUDA events, max over ranks
+  e2e           same metric through the public API with pinned HOST inputs: H2D of the step's
+                inputs and D2H of its results inside the timed region
+  roofline      dominant kernel: algorithmic bytes per launch / its mean duration (CUDA events
+                recorded inside the library around each kernel) against the measured HBM peak
+  cpu_baseline  the oracle (scalar C port, oracle/golden_raster.c) on the host cores, bounded sample
+"""
+import argparse
+import ctypes
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "tests")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+METRIC = "rasterise fwd+bwd Mpix/s"
+UNIT = "Mpix/s"
+
+WORKLOADS = {
+    # name: (B per GPU, H, W, C, n_lat, n_lon)  -- sphere recipe of SURVEY.md 8(d)
+    "headline": dict(B=64, H=512, W=512, C=3, n_lat=224, n_lon=224,
+                     desc="B=64 per GPU, 512x512x3, bumpy UV sphere F=99,904 V=49,954, per-element mesh"),
+    "c4": dict(B=256, H=256, W=256, C=3, n_lat=224, n_lon=224,
+               desc="B=256 per GPU, 256x256x3, sphere F=99,904"),
+    "small": dict(B=4, H=128, W=128, C=3, n_lat=48, n_lon=48, desc="debug size"),
+}
+
+
+def build_scene(wl, B, seed_shift=0):
+    import scenes
+    return scenes.sphere(B, wl["H"], wl["W"], wl["C"], wl["n_lat"], wl["n_lon"],
+                         seeds=(1, 2 + seed_shift, 3 + seed_shift, 4 + seed_shift))
+
+
+def algorithmic_bytes(B, H, W, C, V, F):
+    """BASELINE.md section 3 / SURVEY.md 8(d): every input read once, every output written once;
+    aux buffers and workspace not counted.  Returns per-kernel and total figures."""
+    img = 4 * B * H * W * C
+    mesh_v, mesh_c, mesh_f = 16 * B * V, 4 * C * B * V, 12 * B * F
+    per_kernel = {
+        "setup": mesh_v + mesh_f,                       # vertices + faces read once
+        "resolve": 2 * img + mesh_c,                    # background read, pixels written, colours read
+        "grad_assemble": 3 * img + mesh_f + mesh_v + mesh_c,   # grad_pixels, pixels, grad_background; faces; grad outputs
+    }
+    fwd = 2 * img + mesh_v + mesh_c + mesh_f
+    bwd = 3 * img + mesh_v + mesh_c + mesh_f + mesh_v + mesh_c
+    return per_kernel, fwd, bwd
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons while the timed region runs."""
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); smax.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_baseline_run(wl, target_seconds, threads=None):
+    """Times the oracle (fwd+bwd) on a bounded sample of the workload with all host threads."""
+    from oracle import golden
+    threads = threads or min(golden.max_threads(), os.cpu_count() or 1)
+    H, W = wl["H"], wl["W"]
+    # calibrate on `threads` elements, then size the sample for ~target_seconds
+    nb = threads
+    sc = build_scene(wl, nb)
+    g = np.random.RandomState(0).randn(nb, H, W, wl["C"]).astype(np.float32)
+    V = sc["vertices"].shape[1]
+
+    def once(sc, g):
+        t0 = time.perf_counter()
+        px, fid, gb = golden.forward(sc["background"], sc["vertices"], sc["vertex_colors"], sc["faces"], threads=threads)
+        golden.backward(sc["faces"], px, g, fid, gb, V, threads=threads)
+        return time.perf_counter() - t0
+
+    t = once(sc, g)
+    reps = max(1, int(target_seconds / max(t, 1e-3)))
+    ts = [t] + [once(sc, g) for _ in range(reps - 1)]
+    best = float(np.median(ts))
+    return {"value": nb * H * W / best / 1e6, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": "%d elements of the workload (%dx%d, F=%d), fwd+bwd, median of %d runs, %d OpenMP threads over batch "
+                      "elements; scalar CPU golden rasteriser (oracle/golden_raster.c) -- the reference's OpenGL path is "
+                      "unavailable on this box" % (nb, H, W, sc["faces"].shape[1], len(ts), threads),
+            "seconds_per_run": best}
+
+
+def hbm_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic(kernel):
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture, or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
+            return json.load(f).get(kernel)
+    except Exception:
+        return None
+
+
+def run_reference(args, wl, rank, world):
+    """--impl reference: the CPU implementation of the path on the host cores.  The reference has
+    no CPU code for this path and cannot be compiled here (needs TensorFlow + EGL/OpenGL), so this
+    times the oracle port; rank 0 alone runs."""
+    if rank != 0:
+        return
+    per_step = 8.0 if args.steps * 8.0 < 200 else 200.0 / max(args.steps, 1)
+    for _ in range(args.warmup):
+        cpu_baseline_run(wl, 0.0)
+    vals, base = [], None
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        base = cpu_baseline_run(wl, per_step)
+        vals.append(base["value"])
+    total = time.perf_counter() - t0
+    v = float(np.median(vals))
+    base["value"] = v
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * total / max(args.steps, 1), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload + ": " + wl["desc"], "note": "host-CPU run of the oracle port; bounded sample per step"},
+        "cpu_baseline": base,
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+def run_ours(args, wl, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    from dirt_b200 import rasterise_ops as ops, _lib
+    import dirt_b200
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.load()
+
+    B, H, W, C = wl["B"], wl["H"], wl["W"], wl["C"]
+    sc = build_scene(wl, B, seed_shift=10 * rank)
+    V, F = sc["vertices"].shape[1], sc["faces"].shape[1]
+    host = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for k, v in sc.items()}
+    host["target"] = torch.from_numpy(np.random.RandomState(7 + rank).uniform(0, 1, (B, H, W, C)).astype(np.float32)).pin_memory()
+    d = {k: v.to(dev) for k, v in host.items()}
+    grad_pixels = torch.from_numpy(np.random.RandomState(5 + rank).randn(B, H, W, C).astype(np.float32)).to(dev)
+
+    def step():
+        px, fid, gb = ops.forward_raw(d["background"], d["vertices"], d["vertex_colors"], d["faces"], want_aux=True)
+        return ops.backward_raw(d["faces"], px, grad_pixels, fid, gb, V)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(ms):
+        if world > 1:
+            t = torch.tensor([ms], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        return ms
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    n0 = _lib.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    barrier()
+    ms_total = max_over_ranks(ev0.elapsed_time(ev1))
+    launches = _lib.launch_count() - n0
+    clock_info = clocks.stop() if rank == 0 else None
+    ms_step = ms_total / args.steps
+    value = world * B * H * W / (ms_step * 1e-3) / 1e6
+
+    # ---- per-kernel durations, measured live with CUDA events inside the library -------------
+    _lib.check(lib.dirt_profile_reset())
+    _lib.check(lib.dirt_profile_enable(1))
+    for _ in range(min(args.steps, 10)):
+        step()
+        torch.cuda.synchronize()
+        _lib.check(lib.dirt_profile_collect())
+    _lib.check(lib.dirt_profile_enable(0))
+    stages = {k: (ms / n if n else 0.0) for k, (ms, n) in _lib.stage_times().items()}
+    per_kernel, fwd_bytes, bwd_bytes = algorithmic_bytes(B, H, W, C, V, F)
+    dominant = max(per_kernel, key=lambda k: stages.get(k, 0.0))
+    peak, peak_src = hbm_peak()
+    achieved = per_kernel[dominant] / (stages[dominant] * 1e-3) / 1e9 if stages[dominant] > 0 else 0.0
+    roofline = {"bound": "hbm", "kernel": "k_" + dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                "frac": achieved / peak, "traffic": ncu_traffic("k_" + dominant), "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": per_kernel[dominant], "kernel_ms": stages[dominant],
+                "step_algorithmic_bytes": fwd_bytes + bwd_bytes,
+                "step_achieved_GBps": (fwd_bytes + bwd_bytes) / (ms_step * 1e-3) / 1e9,
+                "step_frac": (fwd_bytes + bwd_bytes) / (ms_step * 1e-3) / 1e9 / peak}
+
+    # ---- e2e: public API, pinned host inputs, H2D + D2H inside the timed region -------------
+    out_gv = torch.empty((B, V, 4), dtype=torch.float32).pin_memory()
+    out_gc = torch.empty((B, V, C), dtype=torch.float32).pin_memory()
+
+    def e2e_step():
+        bg = host["background"].to(dev, non_blocking=True).requires_grad_(True)
+        v = host["vertices"].to(dev, non_blocking=True).requires_grad_(True)
+        c = host["vertex_colors"].to(dev, non_blocking=True).requires_grad_(True)
+        f = host["faces"].to(dev, non_blocking=True)
+        tgt = host["target"].to(dev, non_blocking=True)
+        px = dirt_b200.rasterise_batch(bg, v, c, f)
+        loss = 0.5 * ((px - tgt) ** 2).sum()
+        loss.backward()
+        out_gv.copy_(v.grad, non_blocking=True)
+        out_gc.copy_(c.grad, non_blocking=True)
+        return float(loss.item())          # D2H of the scalar; also a stream sync
+
+    e2e_steps = max(1, min(args.steps, 5))
+    for _ in range(2):
+        e2e_step()
+    barrier()
+    ev0.record()
+    for _ in range(e2e_steps):
+        e2e_step()
+    ev1.record()
+    barrier()
+    e2e_ms = max_over_ranks(ev0.elapsed_time(ev1)) / e2e_steps
+    h2d = sum(host[k].numel() * host[k].element_size() for k in ("background", "vertices", "vertex_colors", "faces", "target"))
+    d2h = out_gv.numel() * 4 + out_gc.numel() * 4 + 4
+    e2e = {"value": world * B * H * W / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d,
+           "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": e2e_steps,
+           "path": "dirt_b200.rasterise_batch + autograd backward on pinned host tensors"}
+
+    cpu_base = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu_base = cpu_baseline_run(wl, 12.0)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank != 0:
+        return
+    print(json.dumps({
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": args.workload + ": " + wl["desc"], "batch_per_gpu": B, "height": H, "width": W, "channels": C,
+                   "vertices": V, "faces": F, "sharding": "batch elements across ranks, no data-path collective",
+                   "l2": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2; no explicit flush" % ((fwd_bytes + bwd_bytes) / 1e6)},
+        "roofline": roofline, "stages_ms": stages, "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": int(launches),
+        "clocks": clock_info}))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="headline", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    wl = WORKLOADS[args.workload]
+    if args.impl == "reference":
+        run_reference(args, wl, rank, world)
+    else:
+        run_ours(args, wl, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,272 @@
+// capi.cu -- the extern "C" surface declared in include/dirt_b200.h: argument validation
+// (the OP_REQUIRES block of csrc/rasterise_egl.cpp:309-336), workspace carve-up, and the
+// host-buffer convenience calls.
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include "../../include/dirt_b200.h"
+#include "kernels.h"
+
+namespace {
+
+thread_local char g_error[512] = "";
+std::atomic<uint64_t> g_launches{0};
+
+// stage timing (dirt_profile_*): one global timer, guarded by a mutex when (re)configured
+std::mutex g_prof_mu;
+dirt::StageTimer g_timer;
+double g_stage_ms[dirt::kStageCount] = {};
+uint64_t g_stage_calls[dirt::kStageCount] = {};
+const char *const kStageNames[dirt::kStageCount] = {
+    "clear", "setup", "bin_count", "bin_alloc", "bin_fill", "tile_raster", "resolve", "grad_clear", "grad_assemble"};
+
+int fail(int status, const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof(g_error), fmt, ap);
+    va_end(ap);
+    return status;
+}
+
+int cuda_fail(cudaError_t e, const char *what)
+{
+    return fail(DIRT_STATUS_CUDA_ERROR, "%s: %s", what, cudaGetErrorString(e));
+}
+
+constexpr int kTilePx = 16;
+constexpr size_t kAlign = 256;
+inline size_t align_up(size_t v) { return (v + kAlign - 1) / kAlign * kAlign; }
+
+// Workspace carve-up.  Offsets are a pure function of the shape.
+struct Layout {
+    size_t keys, counters, tile_count, tile_cursor, tile_offset, big, queue, total;
+    size_t zero_bytes;
+    uint32_t cap_big;
+    unsigned long long cap_queue;
+    int tiles_x, tiles_y;
+};
+
+Layout workspace_layout(const DirtShape &s)
+{
+    Layout L;
+    L.tiles_x = (s.width + kTilePx - 1) / kTilePx;
+    L.tiles_y = (s.height + kTilePx - 1) / kTilePx;
+    const size_t npix = (size_t)s.batch * s.height * s.width;
+    const size_t ntiles = (size_t)s.batch * L.tiles_x * L.tiles_y;
+    const size_t nfaces = (size_t)s.batch * s.face_count;
+    // Large-triangle list: one slot per face is enough unless many faces are split by the
+    // near/far planes; the kernels fall back to in-thread sampling when a list is full, so
+    // these capacities bound memory, not correctness.
+    size_t cap_big = nfaces + 1024;
+    if (cap_big > 0xFFFFFFF0ull) cap_big = 0xFFFFFFF0ull;
+    L.cap_big = (uint32_t)cap_big;
+    L.cap_queue = 8ull * ntiles + 4ull * nfaces + 4096ull;
+    size_t off = 0;
+    L.keys = off;        off = align_up(off + npix * sizeof(unsigned long long));
+    L.counters = off;    off += dirt::kCtrCount * sizeof(uint32_t);
+    L.tile_count = off;  off += ntiles * sizeof(uint32_t);
+    L.tile_cursor = off; off += ntiles * sizeof(uint32_t);
+    L.zero_bytes = off - L.counters;
+    off = align_up(off);
+    L.tile_offset = off; off = align_up(off + ntiles * sizeof(uint32_t));
+    L.big = off;         off = align_up(off + (size_t)L.cap_big * 16);
+    L.queue = off;       off = align_up(off + (size_t)(L.cap_queue + 4) * sizeof(uint32_t));
+    L.total = off;
+    return L;
+}
+
+int check_shape(const DirtShape &s)
+{
+    // csrc/hwc.h:27-28: CHECK(channels == 1 || channels == 3), CHECK(width > 0 && height > 0);
+    // channels is widened to [1, DIRT_MAX_CHANNELS] here (deferred G-buffers in one call)
+    if (s.height <= 0 || s.width <= 0) return fail(DIRT_STATUS_INVALID_ARGUMENT, "Rasterise expects height > 0 and width > 0");
+    if (s.height > 32768 || s.width > 32768) return fail(DIRT_STATUS_UNSUPPORTED, "height/width above 32768 are not supported");
+    if (s.channels < 1 || s.channels > DIRT_MAX_CHANNELS) return fail(DIRT_STATUS_INVALID_ARGUMENT, "Rasterise expects 1 <= channels <= %d", DIRT_MAX_CHANNELS);
+    if (s.batch < 0 || s.vertex_count < 0 || s.face_count < 0) return fail(DIRT_STATUS_INVALID_ARGUMENT, "negative batch / vertex / face count");
+    if ((unsigned long long)s.face_count >= (1ull << 30)) return fail(DIRT_STATUS_UNSUPPORTED, "face_count must be below 2^30");
+    if ((unsigned long long)s.batch * s.face_count >= (1ull << 40)) return fail(DIRT_STATUS_UNSUPPORTED, "batch * face_count too large");
+    return DIRT_STATUS_OK;
+}
+
+int check_stride(int64_t stride, int64_t block, const char *name)
+{
+    if (stride != 0 && stride < block)
+        return fail(DIRT_STATUS_INVALID_ARGUMENT, "%s batch stride %lld is neither 0 (broadcast) nor >= %lld", name, (long long)stride, (long long)block);
+    return DIRT_STATUS_OK;
+}
+
+int current_sm_count(int *out)
+{
+    static std::mutex m;
+    static int cached[64];
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetDevice (no CUDA device: libdirt_b200 has no CPU fallback)");
+    std::lock_guard<std::mutex> lock(m);
+    if (dev >= 0 && dev < 64 && cached[dev] > 0) { *out = cached[dev]; return DIRT_STATUS_OK; }
+    int n = 0;
+    e = cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaDeviceGetAttribute");
+    if (dev >= 0 && dev < 64) cached[dev] = n;
+    *out = n;
+    return DIRT_STATUS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int dirt_abi_version(void) { return DIRT_B200_ABI_VERSION; }
+
+const char *dirt_last_error(void) { return g_error; }
+
+uint64_t dirt_kernel_launch_count(void) { return g_launches.load(); }
+
+size_t dirt_workspace_bytes(const DirtShape *shape)
+{
+    if (!shape || check_shape(*shape) != DIRT_STATUS_OK) return 0;
+    return workspace_layout(*shape).total;
+}
+
+int dirt_rasterise_forward(const DirtForwardArgs *a, void *stream)
+{
+    if (!a) return fail(DIRT_STATUS_INVALID_ARGUMENT, "null arguments");
+    const DirtShape &s = a->shape;
+    int rc = check_shape(s);
+    if (rc) return rc;
+    const int64_t npix = (int64_t)s.height * s.width;
+    // the four OP_REQUIRES shape checks of rasterise_egl.cpp:310-321 become stride checks here
+    if ((rc = check_stride(a->background_bstride, npix * s.channels, "background"))) return rc;
+    if ((rc = check_stride(a->vertices_bstride, (int64_t)s.vertex_count * 4, "vertices"))) return rc;
+    if ((rc = check_stride(a->vertex_colors_bstride, (int64_t)s.vertex_count * s.channels, "vertex_colors"))) return rc;
+    if ((rc = check_stride(a->faces_bstride, (int64_t)s.face_count * 3, "faces"))) return rc;
+    if (s.batch == 0) return DIRT_STATUS_OK;
+    if (!a->background || !a->pixels) return fail(DIRT_STATUS_INVALID_ARGUMENT, "background and pixels must not be null");
+    if (s.face_count > 0 && (!a->vertices || !a->vertex_colors || !a->faces))
+        return fail(DIRT_STATUS_INVALID_ARGUMENT, "vertices, vertex_colors and faces must not be null when face_count > 0");
+    if ((a->face_id == nullptr) != (a->gbuffer == nullptr))
+        return fail(DIRT_STATUS_INVALID_ARGUMENT, "face_id and gbuffer must be both null or both set");
+    if (((uintptr_t)a->vertices & 15u) || ((uintptr_t)a->gbuffer & 15u) || ((a->vertices_bstride * 4) & 15))
+        return fail(DIRT_STATUS_INVALID_ARGUMENT, "vertices and gbuffer must be 16-byte aligned");
+    const Layout L = workspace_layout(s);
+    if (!a->workspace || a->workspace_bytes < L.total)
+        return fail(DIRT_STATUS_WORKSPACE_TOO_SMALL, "workspace of %zu bytes given, %zu needed", a->workspace_bytes, L.total);
+    if ((uintptr_t)a->workspace & (kAlign - 1))
+        return fail(DIRT_STATUS_INVALID_ARGUMENT, "workspace must be %zu-byte aligned", kAlign);
+    int sms = 0;
+    if ((rc = current_sm_count(&sms))) return rc;
+
+    dirt::FwdParams p;
+    p.B = s.batch; p.H = s.height; p.W = s.width; p.C = s.channels; p.V = s.vertex_count; p.F = s.face_count;
+    p.tiles_x = L.tiles_x; p.tiles_y = L.tiles_y;
+    p.background = a->background;       p.background_bs = a->background_bstride;
+    p.vertices = a->vertices;           p.vertices_bs = a->vertices_bstride;
+    p.vertex_colors = a->vertex_colors; p.vertex_colors_bs = a->vertex_colors_bstride;
+    p.faces = a->faces;                 p.faces_bs = a->faces_bstride;
+    p.pixels = a->pixels; p.face_id = a->face_id; p.gbuffer = a->gbuffer;
+    char *ws = static_cast<char *>(a->workspace);
+    p.keys = reinterpret_cast<unsigned long long *>(ws + L.keys);
+    p.counters = reinterpret_cast<uint32_t *>(ws + L.counters);
+    p.tile_count = reinterpret_cast<uint32_t *>(ws + L.tile_count);
+    p.tile_cursor = reinterpret_cast<uint32_t *>(ws + L.tile_cursor);
+    p.tile_offset = reinterpret_cast<uint32_t *>(ws + L.tile_offset);
+    p.big = ws + L.big;
+    p.queue = reinterpret_cast<uint32_t *>(ws + L.queue);
+    p.cap_big = L.cap_big; p.cap_queue = L.cap_queue; p.zero_bytes = L.zero_bytes;
+
+    uint64_t n = 0;
+    cudaError_t e = dirt::launch_forward(p, sms, static_cast<cudaStream_t>(stream), &n, g_timer);
+    g_launches += n;
+    if (e != cudaSuccess) return cuda_fail(e, "rasterise forward launch");
+    return DIRT_STATUS_OK;
+}
+
+int dirt_rasterise_backward(const DirtBackwardArgs *a, void *stream)
+{
+    if (!a) return fail(DIRT_STATUS_INVALID_ARGUMENT, "null arguments");
+    const DirtShape &s = a->shape;
+    int rc = check_shape(s);
+    if (rc) return rc;
+    if ((rc = check_stride(a->faces_bstride, (int64_t)s.face_count * 3, "faces"))) return rc;
+    if ((rc = check_stride(a->grad_vertices_bstride, (int64_t)s.vertex_count * 4, "grad_vertices"))) return rc;
+    if ((rc = check_stride(a->grad_vertex_colors_bstride, (int64_t)s.vertex_count * s.channels, "grad_vertex_colors"))) return rc;
+    if (s.batch == 0) return DIRT_STATUS_OK;
+    if (!a->pixels || !a->grad_pixels || !a->face_id || !a->gbuffer)
+        return fail(DIRT_STATUS_INVALID_ARGUMENT, "pixels, grad_pixels, face_id and gbuffer must not be null");
+    if (s.vertex_count > 0 && (!a->grad_vertices || !a->grad_vertex_colors))
+        return fail(DIRT_STATUS_INVALID_ARGUMENT, "grad_vertices and grad_vertex_colors must not be null");
+    if (s.face_count > 0 && !a->faces) return fail(DIRT_STATUS_INVALID_ARGUMENT, "faces must not be null");
+    if (((uintptr_t)a->gbuffer & 15u) || ((uintptr_t)a->grad_vertices & 15u) || ((a->grad_vertices_bstride * 4) & 15))
+        return fail(DIRT_STATUS_INVALID_ARGUMENT, "gbuffer and grad_vertices must be 16-byte aligned");
+    int sms = 0;
+    if ((rc = current_sm_count(&sms))) return rc;
+
+    dirt::BwdParams p;
+    p.B = s.batch; p.H = s.height; p.W = s.width; p.C = s.channels; p.V = s.vertex_count; p.F = s.face_count;
+    p.faces = a->faces; p.faces_bs = a->faces_bstride;
+    p.pixels = a->pixels; p.grad_pixels = a->grad_pixels; p.face_id = a->face_id; p.gbuffer = a->gbuffer;
+    p.grad_vertices = a->grad_vertices;           p.grad_vertices_bs = a->grad_vertices_bstride;
+    p.grad_vertex_colors = a->grad_vertex_colors; p.grad_vertex_colors_bs = a->grad_vertex_colors_bstride;
+    p.grad_background = a->grad_background;
+    uint64_t n = 0;
+    cudaError_t e = dirt::launch_backward(p, sms, static_cast<cudaStream_t>(stream), &n, g_timer);
+    g_launches += n;
+    if (e != cudaSuccess) return cuda_fail(e, "rasterise backward launch");
+    return DIRT_STATUS_OK;
+}
+
+int dirt_profile_enable(int enable)
+{
+    std::lock_guard<std::mutex> lock(g_prof_mu);
+    if (enable && !g_timer.ev[0][0]) {
+        for (int s = 0; s < dirt::kStageCount; ++s)
+            for (int k = 0; k < 2; ++k) {
+                cudaError_t e = cudaEventCreate(&g_timer.ev[s][k]);
+                if (e != cudaSuccess) return cuda_fail(e, "cudaEventCreate");
+            }
+    }
+    g_timer.enabled = enable != 0;
+    return DIRT_STATUS_OK;
+}
+
+int dirt_profile_collect(void)
+{
+    std::lock_guard<std::mutex> lock(g_prof_mu);
+    for (int s = 0; s < dirt::kStageCount; ++s) {
+        if (!g_timer.pending[s]) continue;
+        float ms = 0.f;
+        cudaError_t e = cudaEventElapsedTime(&ms, g_timer.ev[s][0], g_timer.ev[s][1]);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaEventElapsedTime (synchronise the stream before dirt_profile_collect)");
+        g_stage_ms[s] += ms;
+        g_stage_calls[s] += 1;
+        g_timer.pending[s] = false;
+    }
+    return DIRT_STATUS_OK;
+}
+
+int dirt_profile_read(double *total_ms, uint64_t *calls, int n)
+{
+    std::lock_guard<std::mutex> lock(g_prof_mu);
+    for (int s = 0; s < n && s < dirt::kStageCount; ++s) {
+        if (total_ms) total_ms[s] = g_stage_ms[s];
+        if (calls) calls[s] = g_stage_calls[s];
+    }
+    return DIRT_STATUS_OK;
+}
+
+int dirt_profile_reset(void)
+{
+    std::lock_guard<std::mutex> lock(g_prof_mu);
+    for (int s = 0; s < dirt::kStageCount; ++s) { g_stage_ms[s] = 0; g_stage_calls[s] = 0; g_timer.pending[s] = false; }
+    return DIRT_STATUS_OK;
+}
+
+const char *dirt_profile_stage_name(int stage)
+{
+    return (stage >= 0 && stage < dirt::kStageCount) ? kStageNames[stage] : "";
+}
+
+}  // extern "C"

@@ -1,0 +1,141 @@
+// capi_host.cu -- host-buffer variants of the two entry points (include/dirt_b200.h):
+// stage inputs to the current device, run the device entry points, copy the outputs back.
+// The staging buffers are library-owned and grow-only per device, the role RegisteredBuffer
+// plays in the reference (csrc/rasterise_egl.cpp:55-111).
+#include <cstring>
+#include <mutex>
+#include "../../include/dirt_b200.h"
+#include <cuda_runtime.h>
+
+namespace {
+
+struct Arena {
+    char *base = nullptr;
+    size_t cap = 0, used = 0;
+};
+std::mutex g_mu;
+Arena g_arena[64];
+
+// All staging for one call is carved from one grow-only device allocation.
+cudaError_t arena_reserve(Arena &a, size_t bytes)
+{
+    a.used = 0;
+    if (bytes <= a.cap) return cudaSuccess;
+    if (a.base) { cudaError_t e = cudaFree(a.base); a.base = nullptr; a.cap = 0; if (e != cudaSuccess) return e; }
+    cudaError_t e = cudaMalloc(&a.base, bytes);
+    if (e == cudaSuccess) a.cap = bytes;
+    return e;
+}
+inline size_t pad(size_t b) { return (b + 255) / 256 * 256; }
+template <typename T> T *arena_take(Arena &a, size_t count)
+{
+    T *p = reinterpret_cast<T *>(a.base + a.used);
+    a.used += pad(count * sizeof(T));
+    return p;
+}
+inline size_t extent(int64_t stride, int64_t block, int batch) { return (size_t)(stride == 0 ? block : stride * (int64_t)(batch - 1) + block); }
+
+#define HOST_TRY(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { cudaStreamDestroy(st); return DIRT_STATUS_CUDA_ERROR; } } while (0)
+
+}  // namespace
+
+extern "C" {
+
+int dirt_rasterise_forward_host(const DirtForwardArgs *h)
+{
+    if (!h) return DIRT_STATUS_INVALID_ARGUMENT;
+    const DirtShape &s = h->shape;
+    const size_t ws_bytes = dirt_workspace_bytes(&s);
+    if (ws_bytes == 0) return DIRT_STATUS_INVALID_ARGUMENT;
+    if (s.batch == 0) return DIRT_STATUS_OK;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DIRT_STATUS_CUDA_ERROR;
+    std::lock_guard<std::mutex> lock(g_mu);
+    Arena &A = g_arena[dev];
+    const size_t npix = (size_t)s.batch * s.height * s.width;
+    const size_t n_bg = extent(h->background_bstride, (int64_t)s.height * s.width * s.channels, s.batch);
+    const size_t n_v = extent(h->vertices_bstride, (int64_t)s.vertex_count * 4, s.batch);
+    const size_t n_c = extent(h->vertex_colors_bstride, (int64_t)s.vertex_count * s.channels, s.batch);
+    const size_t n_f = extent(h->faces_bstride, (int64_t)s.face_count * 3, s.batch);
+    const bool aux = h->face_id != nullptr;
+    size_t need = pad(ws_bytes) + pad(n_bg * 4) + pad(n_v * 4) + pad(n_c * 4) + pad(n_f * 4) + pad(npix * s.channels * 4) +
+                  (aux ? pad(npix * 4) + pad(npix * 16) : 0);
+    if (arena_reserve(A, need) != cudaSuccess) return DIRT_STATUS_CUDA_ERROR;
+    cudaStream_t st;
+    if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) return DIRT_STATUS_CUDA_ERROR;
+    DirtForwardArgs d = *h;
+    d.workspace = arena_take<char>(A, ws_bytes); d.workspace_bytes = ws_bytes;
+    float *bg = arena_take<float>(A, n_bg), *v = arena_take<float>(A, n_v), *c = arena_take<float>(A, n_c);
+    int32_t *f = arena_take<int32_t>(A, n_f);
+    d.pixels = arena_take<float>(A, npix * s.channels);
+    if (aux) { d.face_id = arena_take<int32_t>(A, npix); d.gbuffer = arena_take<float>(A, npix * 4); }
+    HOST_TRY(cudaMemcpyAsync(bg, h->background, n_bg * 4, cudaMemcpyHostToDevice, st));
+    if (n_v) HOST_TRY(cudaMemcpyAsync(v, h->vertices, n_v * 4, cudaMemcpyHostToDevice, st));
+    if (n_c) HOST_TRY(cudaMemcpyAsync(c, h->vertex_colors, n_c * 4, cudaMemcpyHostToDevice, st));
+    if (n_f) HOST_TRY(cudaMemcpyAsync(f, h->faces, n_f * 4, cudaMemcpyHostToDevice, st));
+    d.background = bg; d.vertices = v; d.vertex_colors = c; d.faces = f;
+    int rc = dirt_rasterise_forward(&d, st);
+    if (rc != DIRT_STATUS_OK) { cudaStreamDestroy(st); return rc; }
+    HOST_TRY(cudaMemcpyAsync(h->pixels, d.pixels, npix * s.channels * 4, cudaMemcpyDeviceToHost, st));
+    if (aux) {
+        HOST_TRY(cudaMemcpyAsync(h->face_id, d.face_id, npix * 4, cudaMemcpyDeviceToHost, st));
+        HOST_TRY(cudaMemcpyAsync(h->gbuffer, d.gbuffer, npix * 16, cudaMemcpyDeviceToHost, st));
+    }
+    HOST_TRY(cudaStreamSynchronize(st));
+    cudaStreamDestroy(st);
+    return DIRT_STATUS_OK;
+}
+
+int dirt_rasterise_backward_host(const DirtBackwardArgs *h)
+{
+    if (!h) return DIRT_STATUS_INVALID_ARGUMENT;
+    const DirtShape &s = h->shape;
+    if (s.batch == 0) return DIRT_STATUS_OK;
+    if (s.batch < 0 || s.height <= 0 || s.width <= 0 || s.channels <= 0) return DIRT_STATUS_INVALID_ARGUMENT;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DIRT_STATUS_CUDA_ERROR;
+    std::lock_guard<std::mutex> lock(g_mu);
+    Arena &A = g_arena[dev];
+    const size_t npix = (size_t)s.batch * s.height * s.width, nimg = npix * s.channels;
+    const size_t n_f = extent(h->faces_bstride, (int64_t)s.face_count * 3, s.batch);
+    const size_t n_gv = extent(h->grad_vertices_bstride, (int64_t)s.vertex_count * 4, s.batch);
+    const size_t n_gc = extent(h->grad_vertex_colors_bstride, (int64_t)s.vertex_count * s.channels, s.batch);
+    size_t need = pad(n_f * 4) + 3 * pad(nimg * 4) + pad(npix * 4) + pad(npix * 16) + pad(n_gv * 4) + pad(n_gc * 4);
+    if (arena_reserve(A, need) != cudaSuccess) return DIRT_STATUS_CUDA_ERROR;
+    cudaStream_t st;
+    if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) return DIRT_STATUS_CUDA_ERROR;
+    DirtBackwardArgs d = *h;
+    int32_t *f = arena_take<int32_t>(A, n_f);
+    float *px = arena_take<float>(A, nimg), *g = arena_take<float>(A, nimg), *gbg = arena_take<float>(A, nimg);
+    int32_t *fid = arena_take<int32_t>(A, npix);
+    float *gb = arena_take<float>(A, npix * 4);
+    float *gv = arena_take<float>(A, n_gv), *gc = arena_take<float>(A, n_gc);
+    if (n_f) HOST_TRY(cudaMemcpyAsync(f, h->faces, n_f * 4, cudaMemcpyHostToDevice, st));
+    HOST_TRY(cudaMemcpyAsync(px, h->pixels, nimg * 4, cudaMemcpyHostToDevice, st));
+    HOST_TRY(cudaMemcpyAsync(g, h->grad_pixels, nimg * 4, cudaMemcpyHostToDevice, st));
+    HOST_TRY(cudaMemcpyAsync(fid, h->face_id, npix * 4, cudaMemcpyHostToDevice, st));
+    HOST_TRY(cudaMemcpyAsync(gb, h->gbuffer, npix * 16, cudaMemcpyHostToDevice, st));
+    d.faces = f; d.pixels = px; d.grad_pixels = g; d.face_id = fid; d.gbuffer = gb;
+    d.grad_vertices = gv; d.grad_vertex_colors = gc; d.grad_background = h->grad_background ? gbg : nullptr;
+    int rc = dirt_rasterise_backward(&d, st);
+    if (rc != DIRT_STATUS_OK) { cudaStreamDestroy(st); return rc; }
+    if (n_gv) HOST_TRY(cudaMemcpyAsync(h->grad_vertices, gv, n_gv * 4, cudaMemcpyDeviceToHost, st));
+    if (n_gc) HOST_TRY(cudaMemcpyAsync(h->grad_vertex_colors, gc, n_gc * 4, cudaMemcpyDeviceToHost, st));
+    if (h->grad_background) HOST_TRY(cudaMemcpyAsync(h->grad_background, gbg, nimg * 4, cudaMemcpyDeviceToHost, st));
+    HOST_TRY(cudaStreamSynchronize(st));
+    cudaStreamDestroy(st);
+    return DIRT_STATUS_OK;
+}
+
+int dirt_release_host_staging(void)
+{
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DIRT_STATUS_CUDA_ERROR;
+    std::lock_guard<std::mutex> lock(g_mu);
+    Arena &A = g_arena[dev];
+    if (A.base) cudaFree(A.base);
+    A = Arena();
+    return DIRT_STATUS_OK;
+}
+
+}  // extern "C"

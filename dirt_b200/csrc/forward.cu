@@ -1,0 +1,427 @@
+// forward.cu -- the `Rasterise` forward pass as sm_100a CUDA kernels.
+//
+// Replaces RasteriseOpGpu::Compute (csrc/rasterise_egl.cpp:284-514): the per-element GL draw
+// loop (:440-458), the background upload and pixel download kernels
+// (csrc/rasterise_egl.cu:16-129) and the three device-to-device mesh copies (:365-367).
+// One launch per stage covers the whole batch; nothing is serial over batch elements.
+//
+// Stages (all on the caller's stream):
+//   S0  clear      keys := EMPTY, counters := 0
+//   S1  setup      1 thread / (element, face): clip, project, snap, edge setup.  Triangles whose
+//                  pixel bbox is at most kSmallDim x kSmallDim are sampled on the spot with a
+//                  64-bit atomicMin on the key buffer; the rest go to the large-triangle list.
+//   S2a bin_count  1 warp / large triangle: exact tile/triangle overlap test, per-tile counters
+//   S2b bin_alloc  1 thread / tile: reserve a contiguous, 16-byte aligned queue segment
+//   S2c bin_fill   1 warp / large triangle: write face references into the tile queues
+//   S3  tile_raster 1 CTA / 16x16 tile: queue segment -> shared memory (bulk async copy),
+//                  per-entry setup into shared memory, per-pixel register min of the key
+//   S4  resolve    1 thread / pixel: key -> face -> perspective-correct interpolation ->
+//                  pixels (+ face_id, gbuffer), background where uncovered
+#include "raster_core.cuh"
+#include "kernels.h"
+
+namespace dirt {
+
+constexpr int kSmallDim = 4;          // bbox (in pixels) handled inline by the setup thread
+constexpr int kTile = 16;             // tile edge in pixels
+constexpr int kTileThreads = kTile * kTile;
+constexpr int kChunk = 128;           // queue entries staged per round in tile_raster
+constexpr uint32_t kSubShift = 30;    // queue entry = face | fan-index << 30
+
+struct BigTri {            // 16 bytes
+    uint32_t elem;         // batch element
+    uint32_t ref;          // face | fan index << 30
+    uint16_t tx0, ty0, tx1, ty1;   // inclusive tile bbox (y up)
+};
+
+__device__ __forceinline__ const float4 *vertex_ptr(const float *vertices, int64_t bstride, int b)
+{
+    return reinterpret_cast<const float4 *>(vertices + (int64_t)b * bstride);
+}
+
+// Loads the three corners of a face; returns false if an index is outside [0, V).
+__device__ __forceinline__ bool load_face(const int32_t *faces, int64_t f_bs, const float *vertices, int64_t v_bs,
+                                          int b, int f, int V, float4 &a, float4 &bb, float4 &c)
+{
+    const int32_t *fp = faces + (int64_t)b * f_bs + 3 * (int64_t)f;
+    int i0 = __ldg(fp), i1 = __ldg(fp + 1), i2 = __ldg(fp + 2);
+    if ((unsigned)i0 >= (unsigned)V || (unsigned)i1 >= (unsigned)V || (unsigned)i2 >= (unsigned)V) return false;
+    const float4 *vp = vertex_ptr(vertices, v_bs, b);
+    a = __ldg(vp + i0); bb = __ldg(vp + i1); c = __ldg(vp + i2);
+    return true;
+}
+
+// Samples every pixel of t's bbox from one thread and merges into the key buffer.
+__device__ void raster_serial(const TriSetup &t, uint32_t face, unsigned long long *keys_elem, int W, int H,
+                              int x0, int x1, int y0, int y1)
+{
+    long long sx[3], sy[3], r0, r1, r2;
+    edge_steps(t, sx, sy);
+    edge_values(t, x0, y0, r0, r1, r2);
+    for (int py = y0; py <= y1; ++py) {
+        long long e0 = r0, e1 = r1, e2 = r2;
+        for (int px = x0; px <= x1; ++px) {
+            if (covered(t, e0, e1, e2)) {
+                float l0, l1, l2;
+                float zw = sample_depth(t, e0, e1, e2, l0, l1, l2);
+                unsigned long long key;
+                if (depth_key(zw, face, key))
+                    atomicMin(keys_elem + (size_t)(H - 1 - py) * W + px, key);
+            }
+            e0 += sx[0]; e1 += sx[1]; e2 += sx[2];
+        }
+        r0 += sy[0]; r1 += sy[1]; r2 += sy[2];
+    }
+}
+
+// Routes one set-up triangle: inline sampling when small, large-triangle list otherwise.
+__device__ __forceinline__ void route_triangle(const TriSetup &t, int b, uint32_t face, uint32_t fan,
+                                               const FwdParams &p)
+{
+    unsigned long long *keys_elem = p.keys + (size_t)b * p.H * p.W;
+    int bw = t.xmax - t.xmin + 1, bh = t.ymax - t.ymin + 1;
+    if (bw <= kSmallDim && bh <= kSmallDim) {
+        raster_serial(t, face, keys_elem, p.W, p.H, t.xmin, t.xmax, t.ymin, t.ymax);
+        return;
+    }
+    uint32_t slot = atomicAdd(&p.counters[kCtrBig], 1u);
+    if (slot < p.cap_big) {
+        BigTri bt;
+        bt.elem = (uint32_t)b;
+        bt.ref = face | (fan << kSubShift);
+        bt.tx0 = (uint16_t)(t.xmin / kTile); bt.tx1 = (uint16_t)(t.xmax / kTile);
+        bt.ty0 = (uint16_t)(t.ymin / kTile); bt.ty1 = (uint16_t)(t.ymax / kTile);
+        reinterpret_cast<uint4 *>(p.big)[slot] = *reinterpret_cast<uint4 *>(&bt);
+    } else {
+        // list full: still correct, just slow
+        raster_serial(t, face, keys_elem, p.W, p.H, t.xmin, t.xmax, t.ymin, t.ymax);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_setup(FwdParams p)
+{
+    long long total = (long long)p.B * p.F;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+         i += (long long)gridDim.x * blockDim.x) {
+        int b = (int)(i / p.F), f = (int)(i - (long long)b * p.F);
+        float4 va, vb, vc;
+        if (!load_face(p.faces, p.faces_bs, p.vertices, p.vertices_bs, b, f, p.V, va, vb, vc)) continue;
+        int cls = classify_face(va, vb, vc);
+        if (cls == 0) continue;
+        TriSetup t;
+        if (cls == 1) {
+            if (setup_face(va, vb, vc, p.W, p.H, t)) route_triangle(t, b, (uint32_t)f, 0u, p);
+        } else {
+            ClipVert poly[6];
+            int n = clip_face(va, vb, vc, poly);
+            for (int s = 1; s + 1 < n; ++s)
+                if (setup_fan(poly, s, p.W, p.H, t)) route_triangle(t, b, (uint32_t)f, (uint32_t)s, p);
+        }
+    }
+}
+
+// Re-derives the TriSetup a queue / list reference stands for.
+__device__ bool setup_from_ref(const FwdParams &p, int b, uint32_t ref, TriSetup &t)
+{
+    uint32_t face = ref & ((1u << kSubShift) - 1u), fan = ref >> kSubShift;
+    float4 va, vb, vc;
+    if (!load_face(p.faces, p.faces_bs, p.vertices, p.vertices_bs, b, (int)face, p.V, va, vb, vc)) return false;
+    if (fan == 0) return setup_face(va, vb, vc, p.W, p.H, t);
+    ClipVert poly[6];
+    int n = clip_face(va, vb, vc, poly);
+    if ((int)fan + 1 >= n) return false;
+    return setup_fan(poly, (int)fan, p.W, p.H, t);
+}
+
+// Exact conservative test: can any pixel centre of tile (tx, ty) be covered by t?
+__device__ __forceinline__ bool tile_overlaps(const TriSetup &t, const long long *sx, const long long *sy,
+                                              int tx, int ty, int W, int H)
+{
+    int px0 = max(tx * kTile, t.xmin), px1 = min(tx * kTile + kTile - 1, t.xmax);
+    int py0 = max(ty * kTile, t.ymin), py1 = min(ty * kTile + kTile - 1, t.ymax);
+    if (px0 > px1 || py0 > py1) return false;
+    long long e[3];
+    edge_values(t, px0, py0, e[0], e[1], e[2]);
+    const int bias[3] = {t.bias0, t.bias1, t.bias2};
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        // maximum of the (affine) edge value over the tile's sample rectangle
+        long long m = e[k] + (sx[k] > 0 ? sx[k] * (px1 - px0) : 0) + (sy[k] > 0 ? sy[k] * (py1 - py0) : 0);
+        if (m + bias[k] < 0) return false;
+    }
+    return true;
+}
+
+// S2a / S2c.  FILL = false: count references per tile; FILL = true: write them.
+template <bool FILL>
+__global__ void __launch_bounds__(256) k_bin(FwdParams p)
+{
+    const int lane = threadIdx.x & 31;
+    const int warps_per_grid = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t nbig = min(p.counters[kCtrBig], p.cap_big);
+    const int tiles_x = p.tiles_x, tiles = p.tiles_x * p.tiles_y;
+    for (uint32_t i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < nbig; i += warps_per_grid) {
+        uint4 raw = reinterpret_cast<const uint4 *>(p.big)[i];
+        BigTri bt = *reinterpret_cast<BigTri *>(&raw);
+        int b = (int)bt.elem;
+        TriSetup t;
+        if (!setup_from_ref(p, b, bt.ref, t)) continue;      // cannot happen: it was set up once already
+        long long sx[3], sy[3];
+        edge_steps(t, sx, sy);
+        int nx = bt.tx1 - bt.tx0 + 1, ny = bt.ty1 - bt.ty0 + 1;
+        for (int j = lane; j < nx * ny; j += 32) {
+            int tx = bt.tx0 + j % nx, ty = bt.ty0 + j / nx;
+            if (!tile_overlaps(t, sx, sy, tx, ty, p.W, p.H)) continue;
+            size_t tile = (size_t)b * tiles + (size_t)ty * tiles_x + tx;
+            if (!FILL) {
+                atomicAdd(&p.tile_count[tile], 1u);
+            } else {
+                uint32_t k = atomicAdd(&p.tile_cursor[tile], 1u);
+                unsigned long long slot = (unsigned long long)p.tile_offset[tile] + k;
+                if (slot < p.cap_queue) {
+                    p.queue[slot] = bt.ref;
+                } else {
+                    // queue full: this lane samples the tile itself (correct, slow)
+                    int px0 = max(tx * kTile, t.xmin), px1 = min(tx * kTile + kTile - 1, t.xmax);
+                    int py0 = max(ty * kTile, t.ymin), py1 = min(ty * kTile + kTile - 1, t.ymax);
+                    raster_serial(t, bt.ref & ((1u << kSubShift) - 1u), p.keys + (size_t)b * p.H * p.W,
+                                  p.W, p.H, px0, px1, py0, py1);
+                }
+            }
+        }
+    }
+}
+
+// S2b: reserve queue space per tile.  Segments start on a multiple of 4 entries (16 bytes) so
+// that tile_raster can fetch them with one bulk async copy.
+__global__ void __launch_bounds__(256) k_bin_alloc(FwdParams p)
+{
+    if (p.counters[kCtrBig] == 0) return;
+    size_t n = (size_t)p.B * p.tiles_x * p.tiles_y;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        uint32_t c = p.tile_count[i];
+        if (c == 0) continue;
+        uint32_t padded = (c + 3u) & ~3u;
+        p.tile_offset[i] = atomicAdd(&p.counters[kCtrQueue], padded);
+    }
+}
+
+// ---- bulk async copy (TMA engine, non-tensor form) + mbarrier helpers --------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *ptr) { return (uint32_t)__cvta_generic_to_shared(ptr); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred P1;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 P1, [%0], %1;\n"
+        "@P1 bra DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst_smem)), "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+// S3: one CTA per tile, one thread per pixel.
+__global__ void __launch_bounds__(kTileThreads) k_tile_raster(FwdParams p)
+{
+    __shared__ __align__(16) uint32_t s_ref[kChunk];
+    __shared__ TriSetup s_tri[kChunk];
+    __shared__ uint8_t s_ok[kChunk];
+    __shared__ __align__(8) uint64_t s_bar;
+
+    const int tiles = p.tiles_x * p.tiles_y;
+    const size_t tile = blockIdx.x;
+    const uint32_t count = p.tile_count[tile];
+    if (count == 0) return;
+    const int b = (int)(tile / tiles), tl = (int)(tile - (size_t)b * tiles);
+    const int ty = tl / p.tiles_x, tx = tl - ty * p.tiles_x;
+    const int px = tx * kTile + (threadIdx.x & (kTile - 1)), py = ty * kTile + (threadIdx.x >> 4);
+    const bool in_image = px < p.W && py < p.H;
+    unsigned long long *keyp = p.keys + (size_t)b * p.H * p.W + (size_t)(p.H - 1 - py) * p.W + px;
+    unsigned long long best = in_image ? *keyp : 0ull, orig = best;
+
+    // entries past the queue capacity were sampled by bin_fill's fallback
+    const unsigned long long off = p.tile_offset[tile];
+    uint32_t avail = off >= p.cap_queue ? 0u : (uint32_t)min((unsigned long long)count, p.cap_queue - off);
+
+    if (threadIdx.x == 0) mbar_init(&s_bar, 1);
+    __syncthreads();
+    uint32_t parity = 0;
+    for (uint32_t base = 0; base < avail; base += kChunk) {
+        uint32_t n = min((uint32_t)kChunk, avail - base);
+        // (1) queue segment -> shared memory: one bulk async copy (16-byte granules)
+        if (threadIdx.x == 0) {
+            uint32_t bytes = ((n + 3u) & ~3u) * 4u;
+            // the padded tail may reach past the queue's end only by whole granules we own
+            mbar_expect_tx(&s_bar, bytes);
+            bulk_g2s(s_ref, p.queue + off + base, bytes, &s_bar);
+        }
+        mbar_wait(&s_bar, parity);
+        parity ^= 1u;
+        // (2) one thread per entry re-derives the triangle's setup into shared memory
+        if (threadIdx.x < n) {
+            TriSetup t;
+            bool ok = setup_from_ref(p, b, s_ref[threadIdx.x], t);
+            s_ok[threadIdx.x] = ok;
+            if (ok) s_tri[threadIdx.x] = t;
+        }
+        __syncthreads();
+        // (3) every pixel walks the staged triangles; the running minimum stays in a register
+        if (in_image) {
+            for (uint32_t j = 0; j < n; ++j) {
+                if (!s_ok[j]) continue;
+                const TriSetup &t = s_tri[j];
+                if (px < t.xmin || px > t.xmax || py < t.ymin || py > t.ymax) continue;
+                long long e0, e1, e2;
+                edge_values(t, px, py, e0, e1, e2);
+                if (!covered(t, e0, e1, e2)) continue;
+                float l0, l1, l2;
+                float zw = sample_depth(t, e0, e1, e2, l0, l1, l2);
+                unsigned long long key;
+                if (depth_key(zw, s_ref[j] & ((1u << kSubShift) - 1u), key)) best = min(best, key);
+            }
+        }
+        __syncthreads();
+    }
+    if (in_image && best < orig) *keyp = best;
+}
+
+// S4: one thread per pixel.
+template <int C>
+__global__ void __launch_bounds__(256) k_resolve(FwdParams p)
+{
+    const size_t npix = (size_t)p.H * p.W, total = npix * p.B;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const int b = (int)(i / npix);
+        const size_t o = i - (size_t)b * npix;
+        const int row = (int)(o / p.W), px = (int)(o - (size_t)row * p.W), py = p.H - 1 - row;
+        const int CC = C > 0 ? C : p.C;
+        float *out = p.pixels + i * CC;
+        const unsigned long long key = p.keys[i];
+        if (key == kKeyEmpty) {
+            // the reference never clears the colour buffer: background shows through
+            const float *bg = p.background + (int64_t)b * p.background_bs + o * CC;
+            for (int c = 0; c < CC; ++c) out[c] = __ldg(bg + c);
+            if (p.face_id) {
+                p.face_id[i] = -1;
+                reinterpret_cast<float4 *>(p.gbuffer)[i] = make_float4(0.f, 0.f, 0.f, 1.0f);
+            }
+            continue;
+        }
+        const int f = (int)(uint32_t)(key & 0xFFFFFFFFull);
+        const int32_t *fp = p.faces + (int64_t)b * p.faces_bs + 3 * (int64_t)f;
+        const int i0 = __ldg(fp), i1 = __ldg(fp + 1), i2 = __ldg(fp + 2);
+        const float4 *vp = vertex_ptr(p.vertices, p.vertices_bs, b);
+        const float4 va = __ldg(vp + i0), vb = __ldg(vp + i1), vc = __ldg(vp + i2);
+        float B0 = 0.f, B1 = 0.f, wc = 1.f, zw = 1.f;
+        TriSetup t;
+        int cls = classify_face(va, vb, vc);
+        if (cls == 1) {
+            setup_face(va, vb, vc, p.W, p.H, t);
+            long long e0, e1, e2;
+            edge_values(t, px, py, e0, e1, e2);
+            float l0, l1, l2, b2;
+            zw = sample_depth(t, e0, e1, e2, l0, l1, l2);
+            perspective_weights(t, l0, l1, l2, B0, B1, b2, wc);
+        } else {
+            // clipped face: find the fan triangle that owns this pixel (exactly one does)
+            ClipVert poly[6];
+            int n = clip_face(va, vb, vc, poly);
+            for (int s = 1; s + 1 < n; ++s) {
+                if (!setup_fan(poly, s, p.W, p.H, t)) continue;
+                if (px < t.xmin || px > t.xmax || py < t.ymin || py > t.ymax) continue;
+                long long e0, e1, e2;
+                edge_values(t, px, py, e0, e1, e2);
+                if (!covered(t, e0, e1, e2)) continue;
+                float l0, l1, l2, b0, b1, b2;
+                zw = sample_depth(t, e0, e1, e2, l0, l1, l2);
+                if (!(zw >= 0.0f && zw <= 1.0f)) continue;
+                perspective_weights(t, l0, l1, l2, b0, b1, b2, wc);
+                const ClipVert &q0 = poly[0], &q1 = poly[s], &q2 = poly[s + 1];
+                B0 = fadd(fadd(fmul(b0, q0.b0), fmul(b1, q1.b0)), fmul(b2, q2.b0));
+                B1 = fadd(fadd(fmul(b0, q0.b1), fmul(b1, q1.b1)), fmul(b2, q2.b1));
+                break;
+            }
+        }
+        const float *cp = p.vertex_colors + (int64_t)b * p.vertex_colors_bs;
+        const float *c0 = cp + (int64_t)i0 * CC, *c1 = cp + (int64_t)i1 * CC, *c2 = cp + (int64_t)i2 * CC;
+        for (int c = 0; c < CC; ++c) {
+            // smooth varying (csrc/shaders.cpp:23,29), arranged so constant colours are exact
+            float k2 = __ldg(c2 + c);
+            float t0 = fsub(__ldg(c0 + c), k2), t1 = fsub(__ldg(c1 + c), k2);
+            out[c] = fadd(fadd(k2, fmul(B0, t0)), fmul(B1, t1));
+        }
+        if (p.face_id) {
+            p.face_id[i] = f;
+            reinterpret_cast<float4 *>(p.gbuffer)[i] = make_float4(B0, B1, wc, zw);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// Host-side launch sequence
+// ---------------------------------------------------------------------------------------
+static inline int grid_for(long long work, int block, int sm_count, int waves)
+{
+    long long g = (work + block - 1) / block;
+    long long cap = (long long)sm_count * waves;
+    if (g > cap) g = cap;
+    if (g < 1) g = 1;
+    return (int)g;
+}
+
+cudaError_t launch_forward(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_t *launches, StageTimer &tm)
+{
+    cudaError_t e;
+    const size_t npix_total = (size_t)p.B * p.H * p.W;
+    const size_t ntiles = (size_t)p.B * p.tiles_x * p.tiles_y;
+    // S0: keys := EMPTY; counters, tile_count, tile_cursor := 0 (contiguous in the workspace)
+    tm.begin(kStageClear, stream);
+    if ((e = cudaMemsetAsync(p.keys, 0xFF, npix_total * sizeof(unsigned long long), stream)) != cudaSuccess) return e;
+    if ((e = cudaMemsetAsync(p.counters, 0, p.zero_bytes, stream)) != cudaSuccess) return e;
+    tm.end(kStageClear, stream);
+    const long long nfaces = (long long)p.B * p.F;
+    if (nfaces > 0) {
+        tm.begin(kStageSetup, stream);
+        k_setup<<<grid_for(nfaces, 256, sm_count, 64), 256, 0, stream>>>(p);
+        tm.end(kStageSetup, stream);
+        tm.begin(kStageBinCount, stream);
+        k_bin<false><<<sm_count * 4, 256, 0, stream>>>(p);
+        tm.end(kStageBinCount, stream);
+        tm.begin(kStageBinAlloc, stream);
+        k_bin_alloc<<<grid_for((long long)ntiles, 256, sm_count, 8), 256, 0, stream>>>(p);
+        tm.end(kStageBinAlloc, stream);
+        tm.begin(kStageBinFill, stream);
+        k_bin<true><<<sm_count * 4, 256, 0, stream>>>(p);
+        tm.end(kStageBinFill, stream);
+        tm.begin(kStageTileRaster, stream);
+        k_tile_raster<<<(unsigned)ntiles, kTileThreads, 0, stream>>>(p);
+        tm.end(kStageTileRaster, stream);
+        *launches += 5;
+    }
+    const int g = grid_for((long long)npix_total, 256, sm_count, 64);
+    tm.begin(kStageResolve, stream);
+    switch (p.C) {
+        case 1: k_resolve<1><<<g, 256, 0, stream>>>(p); break;
+        case 3: k_resolve<3><<<g, 256, 0, stream>>>(p); break;
+        default: k_resolve<0><<<g, 256, 0, stream>>>(p); break;
+    }
+    tm.end(kStageResolve, stream);
+    *launches += 1;
+    return cudaGetLastError();
+}
+
+}  // namespace dirt

@@ -1,0 +1,64 @@
+// kernels.h -- parameter blocks passed by value to the kernels, and the launch entry points
+// capi.cu calls.  Internal to libdirt_b200.so; the public surface is include/dirt_b200.h.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace dirt {
+
+enum { kCtrBig = 0, kCtrQueue = 1, kCtrCount = 8 };
+
+struct FwdParams {
+    int B, H, W, C, V, F;
+    int tiles_x, tiles_y;
+    const float *background;     int64_t background_bs;
+    const float *vertices;       int64_t vertices_bs;
+    const float *vertex_colors;  int64_t vertex_colors_bs;
+    const int32_t *faces;        int64_t faces_bs;
+    float *pixels;
+    int32_t *face_id;            // optional (with gbuffer)
+    float *gbuffer;
+    // workspace carve-up (see workspace_layout in capi.cu)
+    unsigned long long *keys;    // [B*H*W] depth24 << 32 | face
+    uint32_t *counters;          // [kCtrCount]; counters, tile_count, tile_cursor are contiguous
+    uint32_t *tile_count;        // [B*tiles]
+    uint32_t *tile_cursor;       // [B*tiles]
+    uint32_t *tile_offset;       // [B*tiles]
+    void *big;                   // [cap_big] BigTri (16 B each)
+    uint32_t *queue;             // [cap_queue + 4]
+    uint32_t cap_big;
+    unsigned long long cap_queue;
+    size_t zero_bytes;           // bytes to clear starting at `counters`
+};
+
+struct BwdParams {
+    int B, H, W, C, V, F;
+    const int32_t *faces;        int64_t faces_bs;
+    const float *pixels;
+    const float *grad_pixels;
+    const int32_t *face_id;
+    const float *gbuffer;
+    float *grad_vertices;        int64_t grad_vertices_bs;
+    float *grad_vertex_colors;   int64_t grad_vertex_colors_bs;
+    float *grad_background;      // optional
+};
+
+enum Stage {
+    kStageClear = 0, kStageSetup, kStageBinCount, kStageBinAlloc, kStageBinFill, kStageTileRaster, kStageResolve,
+    kStageGradClear, kStageGradAssemble, kStageCount
+};
+
+// Records a CUDA event pair around each stage when enabled (capi.cu owns the storage).
+struct StageTimer {
+    bool enabled = false;
+    cudaEvent_t ev[kStageCount][2] = {};
+    bool pending[kStageCount] = {};
+    void begin(int s, cudaStream_t st) { if (enabled) cudaEventRecord(ev[s][0], st); }
+    void end(int s, cudaStream_t st) { if (enabled) { cudaEventRecord(ev[s][1], st); pending[s] = true; } }
+};
+
+cudaError_t launch_forward(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_t *launches, StageTimer &tm);
+cudaError_t launch_backward(const BwdParams &p, int sm_count, cudaStream_t stream, uint64_t *launches, StageTimer &tm);
+
+}  // namespace dirt

@@ -1,0 +1,151 @@
+/*
+ * dirt_b200.h -- C ABI of libdirt_b200.so: the `Rasterise` forward op and the `RasteriseGrad`
+ * backward of yyuting/dirt as hand-written sm_100a CUDA kernels.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no TensorFlow / torch types.  Each
+ * entry point names the reference interface it replaces (paths relative to the reference
+ * tree).  The reference-side binding a maintainer would add is shown in INTEGRATION.md.
+ *
+ * Conventions (identical to the reference op, csrc/rasterise_egl.cpp:33-53, :309-339):
+ *   - all tensors dense, row-major, fp32 / int32;
+ *   - background, pixels: [B, H, W, C], row 0 = TOP of the image (csrc/rasterise_egl.cu:29, :93);
+ *   - vertices: [B, V, 4] OpenGL clip space; vertex_colors: [B, V, C]; faces: [B, F, 3] int32,
+ *     indices local to the batch element (csrc/rasterise_egl.cpp:451-457);
+ *   - per-input batch strides are given in ELEMENTS; 0 broadcasts one [*, ...] block over the
+ *     batch (the relaxation the reference wishes for at csrc/rasterise_egl.cpp:334).
+ *
+ * Device-pointer entry points are asynchronous on the caller's stream: no host
+ * synchronisation, no device->host copy, no threads (the reference blocks on a GL thread and a
+ * synchronous cudaMemcpy, csrc/gl_dispatcher.h:58-67, csrc/rasterise_egl.cpp:323).
+ * There is no CPU fallback: without a CUDA device every compute entry point returns
+ * DIRT_STATUS_CUDA_ERROR (the reference registers a DEVICE_GPU kernel only, :520).
+ */
+#ifndef DIRT_B200_H
+#define DIRT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define DIRT_API __attribute__((visibility("default")))
+#else
+#define DIRT_API
+#endif
+
+#define DIRT_B200_ABI_VERSION 1
+#define DIRT_MAX_CHANNELS 16          /* reference: channels in {1,3} (csrc/hwc.h:27); wider
+                                         attribute sets serve deferred G-buffers in one call */
+
+typedef enum DirtStatus {
+    DIRT_STATUS_OK = 0,
+    DIRT_STATUS_INVALID_ARGUMENT = -1,   /* replaces OP_REQUIRES -> InvalidArgument, rasterise_egl.cpp:310-336 */
+    DIRT_STATUS_CUDA_ERROR = -2,         /* replaces LOG(FATAL) aborts, rasterise_egl.cpp:85-109 */
+    DIRT_STATUS_WORKSPACE_TOO_SMALL = -3,
+    DIRT_STATUS_UNSUPPORTED = -4
+} DirtStatus;
+
+/* Problem shape: the op attrs height/width/channels (csrc/rasterise_egl.cpp:34-36, csrc/hwc.h:21-30)
+ * plus the dynamic dims the reference reads from its input tensors (:313-336). */
+typedef struct DirtShape {
+    int32_t batch;        /* B  = vertices.dim0                          */
+    int32_t height;       /* H  > 0                                       */
+    int32_t width;        /* W  > 0                                       */
+    int32_t channels;     /* C  in [1, DIRT_MAX_CHANNELS]                 */
+    int32_t vertex_count; /* V                                            */
+    int32_t face_count;   /* F                                            */
+} DirtShape;
+
+/* Forward arguments.  Replaces the inputs/outputs of RasteriseOpGpu::Compute
+ * (csrc/rasterise_egl.cpp:284-514).  `camera_pos` (input 4 of the fork's op, :41) only
+ * parameterises the fork's procedural fragment shaders (:399-433) and is not an input of the
+ * mesh path; adapters accept and drop it. */
+typedef struct DirtForwardArgs {
+    DirtShape shape;
+    const float *background;      int64_t background_bstride;    /* [B,H,W,C]              */
+    const float *vertices;        int64_t vertices_bstride;      /* [B,V,4]                */
+    const float *vertex_colors;   int64_t vertex_colors_bstride; /* [B,V,C]                */
+    const int32_t *faces;         int64_t faces_bstride;         /* [B,F,3]                */
+    float *pixels;                /* out [B,H,W,C], required                               */
+    /* Optional per-pixel state for the backward pass (both NULL, or both set).  This is the
+     * G-buffer the reference's backward shaders render (csrc/shaders.cpp:2187-2221):
+     * face_id -> (i0,i1,i2) through `faces`; gbuffer = (b0, b1, clip-space w, window depth). */
+    int32_t *face_id;             /* out [B,H,W], -1 = background                          */
+    float *gbuffer;               /* out [B,H,W,4]                                         */
+    void *workspace;              /* device scratch, >= dirt_workspace_bytes(&shape)       */
+    size_t workspace_bytes;
+} DirtForwardArgs;
+
+/* Backward arguments.  Replaces launch_grad_assembly (declared, never defined, in the fork:
+ * csrc/rasterise_grad_common.h:19-24): same outputs (grad_vertices, grad_vertex_colors,
+ * grad_background), same inputs (G-buffer, pixels, grad_pixels) minus the debug tensor.
+ * Gradient outputs are zero-initialised by the callee.  A 0 batch stride on an output sums the
+ * gradients of all batch elements into one [V,*] block (shared mesh). */
+typedef struct DirtBackwardArgs {
+    DirtShape shape;
+    const int32_t *faces;         int64_t faces_bstride;         /* [B,F,3]                */
+    const float *pixels;          /* [B,H,W,C] forward output                              */
+    const float *grad_pixels;     /* [B,H,W,C]                                             */
+    const int32_t *face_id;       /* [B,H,W]   from forward                                */
+    const float *gbuffer;         /* [B,H,W,4] from forward                                */
+    float *grad_vertices;         int64_t grad_vertices_bstride;      /* out [B,V,4]       */
+    float *grad_vertex_colors;    int64_t grad_vertex_colors_bstride; /* out [B,V,C]       */
+    float *grad_background;       /* out [B,H,W,C]; may be NULL                            */
+} DirtBackwardArgs;
+
+/* Library identity. */
+DIRT_API int dirt_abi_version(void);
+/* Thread-local message of the last failing call on this thread ("" if none). */
+DIRT_API const char *dirt_last_error(void);
+
+/* Scratch the forward pass needs for `shape` (depth|face-id keys, tile counters and queues,
+ * large-triangle records).  Replaces the grow-only GL framebuffer / buffers the reference
+ * keeps per GL thread (csrc/rasterise_egl.cpp:73-89, :199-274, :347-354); here the caller
+ * owns it, so torch's / TF's caching allocator can. */
+DIRT_API size_t dirt_workspace_bytes(const DirtShape *shape);
+
+/* Forward: replaces op "Rasterise" (REGISTER_OP csrc/rasterise_egl.cpp:33-53; kernel :284-514;
+ * upload_background / download_pixels csrc/rasterise_egl.cu:16-129 are folded in).
+ * `stream` is a cudaStream_t passed as void* (NULL = legacy default stream). */
+DIRT_API int dirt_rasterise_forward(const DirtForwardArgs *args, void *stream);
+
+/* Backward: replaces op "RasteriseGrad" in its intended role (csrc/rasterise_grad_egl.cpp:33-53
+ * carries the name; csrc/rasterise_grad_common.h:13-24 the intended kernels). */
+DIRT_API int dirt_rasterise_backward(const DirtBackwardArgs *args, void *stream);
+
+/* Host-buffer convenience calls: every pointer in `args` is HOST memory (pinned or pageable);
+ * the library stages inputs to the current device, runs the kernels and copies the outputs
+ * back, then synchronises.  workspace / workspace_bytes are ignored (library-owned, grow-only,
+ * like the reference's RegisteredBuffer, csrc/rasterise_egl.cpp:55-111).  This is what a
+ * host-side caller of the reference effectively pays through session.run feeds/fetches. */
+DIRT_API int dirt_rasterise_forward_host(const DirtForwardArgs *args);
+DIRT_API int dirt_rasterise_backward_host(const DirtBackwardArgs *args);
+/* Frees the library-owned staging buffers of the *_host calls on the current device. */
+DIRT_API int dirt_release_host_staging(void);
+
+/* Number of kernel launches issued by this library since load (all threads); lets a
+ * benchmark report `gpu_launches` from a count, not a guess. */
+DIRT_API uint64_t dirt_kernel_launch_count(void);
+
+/* Per-stage device timing, the counterpart of the reference's compile-time TIME_SECTIONS
+ * stamps (csrc/rasterise_egl.cpp:292-294, :489-512), but measured on the device with CUDA
+ * events recorded on the caller's stream around each kernel.  Off by default.
+ *   dirt_profile_enable(1)  -> subsequent forward/backward calls record events per stage
+ *   dirt_profile_collect()  -> call after synchronising the stream: folds the elapsed time of
+ *                              every stage recorded since the last collect into the totals
+ *   dirt_profile_read()     -> cumulative milliseconds and launch counts per stage
+ * Stage order: see dirt_profile_stage_name(i), i in [0, DIRT_STAGE_COUNT). */
+#define DIRT_STAGE_COUNT 9
+DIRT_API int dirt_profile_enable(int enable);
+DIRT_API int dirt_profile_collect(void);
+DIRT_API int dirt_profile_read(double *total_ms, uint64_t *calls, int n);
+DIRT_API int dirt_profile_reset(void);
+DIRT_API const char *dirt_profile_stage_name(int stage);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DIRT_B200_H */

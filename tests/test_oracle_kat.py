@@ -1,0 +1,178 @@
+"""CPU: pins the oracle against the reference's own known-answer tests and checks the raster
+contract's micro-cases."""
+import numpy as np
+import pytest
+
+import scenes
+from oracle import golden
+
+
+def _fwd(sc, **kw):
+    return golden.forward(sc["background"], sc["vertices"], sc["vertex_colors"], sc["faces"], **kw)
+
+
+def test_kat1_readme_square():
+    # README.md:46-70; upstream asserted "successful: all pixels agree" (README.md:104)
+    sc = scenes.kat1_square()
+    px, fid, _ = _fwd(sc)
+    assert np.array_equal(px, sc["expected"])
+    assert px.sum() == 256.0
+    assert set(np.unique(fid)) == {-1, 0, 1}
+
+
+def test_kat2_multi_gpu_square():
+    # tests/multi_gpu_test.py:8-17: asymmetric in y => pins the row flip; clockwise faces => no culling
+    sc = scenes.kat2_square()
+    px, _, _ = _fwd(sc)
+    assert np.array_equal(px, sc["expected"])
+
+
+def test_both_windings_render():
+    sc = scenes.kat1_square()
+    a, fa, _ = _fwd(sc)
+    sc["faces"] = sc["faces"][:, :, ::-1].copy()
+    b, fb, _ = _fwd(sc)
+    assert np.array_equal(a, b) and np.array_equal(fa, fb)
+
+
+def test_shared_edge_covered_exactly_once():
+    # two triangles sharing the diagonal of a pixel-aligned square whose diagonal passes through
+    # pixel centres: every centre on the diagonal must belong to exactly one face
+    W = H = 16
+    v = np.array([[-1, -1, 0, 1], [1, -1, 0, 1], [1, 1, 0, 1], [-1, 1, 0, 1]], np.float32)
+    faces = np.array([[0, 1, 2], [0, 2, 3]], np.int32)
+    px, fid, _ = golden.forward(np.zeros((H, W, 1)), v, np.ones((4, 1)), faces)
+    assert (fid >= 0).all()
+    cnt = np.zeros((H, W), int)
+    for f in range(2):
+        _, fid1, _ = golden.forward(np.zeros((H, W, 1)), v, np.ones((4, 1)), faces[f:f + 1])
+        cnt += (fid1[0] >= 0)
+    assert (cnt == 1).all()
+
+
+def test_depth_tie_lowest_face_wins_and_nearer_wins():
+    W = H = 8
+    quad = lambda z: [[-1, -1, z, 1], [1, -1, z, 1], [1, 1, z, 1], [-1, 1, z, 1]]
+    v = np.array(quad(0.0) + quad(0.0) + quad(-0.5), np.float32)
+    faces = np.array([[4, 5, 6], [0, 1, 2], [8, 9, 10]], np.int32)
+    cols = np.repeat(np.array([[1.], [2.], [3.]], np.float32), 4, axis=0)
+    px, fid, _ = golden.forward(np.zeros((H, W, 1)), v, cols, faces[:2])
+    assert set(np.unique(fid)) <= {-1, 0}            # equal depth: face 0 (drawn first) wins
+    px, fid, _ = golden.forward(np.zeros((H, W, 1)), v, cols, faces)
+    assert set(np.unique(fid)) <= {-1, 2}            # z = -0.5 is nearer
+
+
+def test_depth_range_clip_and_background_passthrough():
+    W = H = 8
+    tri = lambda z: [[-1, -1, z, 1], [3, -1, z, 1], [-1, 3, z, 1]]
+    bg = np.full((H, W, 3), -np.inf, np.float32)     # samples/deferred.py:67 uses -inf backgrounds
+    for z, visible in ((-1.5, False), (1.5, False), (1.0, False), (0.999, True), (-1.0, True)):
+        px, fid, _ = golden.forward(bg, np.array(tri(z), np.float32), np.ones((3, 3)), [[0, 1, 2]])
+        assert (fid >= 0).all() == visible, z
+        if not visible:
+            assert np.isneginf(px).all()
+
+
+def test_near_plane_crossing_keeps_barycentrics_of_original_vertices():
+    # a triangle with one vertex behind the camera; colour = clip-space w, which is linear over
+    # the triangle, so every covered pixel must read back its own interpolated w (gbuf[...,2])
+    W = H = 64
+    v = np.array([[-0.5, -0.5, -0.8, 1.0], [0.5, -0.5, -0.8, 1.0], [0.0, 3.0, -2.0, -0.5]], np.float32)
+    cols = v[:, 3:4].copy()
+    px, fid, gb = golden.forward(np.zeros((H, W, 1)), v, cols, [[0, 1, 2]])
+    m = fid[0] >= 0
+    assert m.sum() > 100
+    np.testing.assert_allclose(px[0, :, :, 0][m], gb[0, :, :, 2][m], rtol=2e-4, atol=1e-5)
+    assert (gb[0, :, :, 2][m] > 0).all()
+
+
+def test_batch_local_indices_and_broadcast():
+    sc = scenes.cube(B=3, H=48, W=48)
+    px, fid, _ = _fwd(sc)
+    for b in range(3):
+        p1, f1, _ = golden.forward(sc["background"][b], sc["vertices"][b], sc["vertex_colors"][b], sc["faces"][b])
+        assert np.array_equal(p1[0], px[b]) and np.array_equal(f1[0], fid[b])
+    # faces given once, broadcast over the batch
+    p2, f2, _ = golden.forward(sc["background"], sc["vertices"], sc["vertex_colors"], sc["faces"][:1])
+    assert np.array_equal(p2, px) and np.array_equal(f2, fid)
+
+
+def test_constant_colour_is_exact_and_vertex_rotation_invariant_coverage():
+    sc = scenes.random_triangles(1, 64, 64, 3, 200, seed=3)
+    sc["vertex_colors"][:] = 0.7
+    px, fid, _ = _fwd(sc)
+    assert np.all(px[fid >= 0] == np.float32(0.7))
+    sc2 = dict(sc)
+    sc2["faces"] = np.roll(sc["faces"], 1, axis=2).copy()
+    _, fid2, _ = _fwd(sc2)
+    assert np.array_equal(fid, fid2)
+
+
+def test_threads_do_not_change_results():
+    sc = scenes.random_triangles(4, 40, 56, 3, 150, seed=9)
+    a = _fwd(sc, threads=1)
+    b = _fwd(sc, threads=4)
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+
+
+def test_backward_colour_and_background_parts_are_exact():
+    sc = scenes.cube(B=2, H=40, W=40)
+    px, fid, gb = _fwd(sc)
+    rng = np.random.RandomState(0)
+    g = rng.randn(*px.shape).astype(np.float32)
+    V = sc["vertices"].shape[1]
+    gv, gc, gbg = golden.backward(sc["faces"], px, g, fid, gb, V)
+    assert np.array_equal(gbg, np.where((fid < 0)[..., None], g, 0))
+    # colours: pixels are linear in vertex_colors => sum(g * pixels(colours=e)) reproduces gc
+    for b in range(2):
+        for vi in (0, 7, 20):
+            for c in range(3):
+                e = np.zeros_like(sc["vertex_colors"])
+                e[b, vi, c] = 1
+                p1, _, _ = golden.forward(np.zeros_like(sc["background"]), sc["vertices"], e, sc["faces"])
+                np.testing.assert_allclose((p1 * g).sum(), gc[b, vi, c], rtol=1e-4, atol=1e-5)
+
+
+def test_backward_position_gradient_is_boundary_only_for_flat_square():
+    # README.md:41: gradients w.r.t. the square's centre "should be non-zero at the boundary"
+    sc = scenes.kat1_square()
+    px, fid, gb = _fwd(sc)
+    H, W = px.shape[1:3]
+    for (r, x, expect_nonzero) in ((64, 32, False), (64, 24, True), (64, 23, True), (10, 100, False)):
+        g = np.zeros_like(px)
+        g[0, r, x, 0] = 1
+        gv, _, _ = golden.backward(sc["faces"], px, g, fid, gb, 4)
+        assert (np.abs(gv).sum() > 0) == expect_nonzero, (r, x)
+    # moving the square right (+x) brightens pixels just right of its right edge
+    g = np.zeros_like(px)
+    g[0, 64, 40, 0] = 1           # first background pixel right of the square
+    gv, _, _ = golden.backward(sc["faces"], px, g, fid, gb, 4)
+    assert gv[0, :, 0].sum() > 0
+
+
+def test_backward_finite_difference_translation():
+    # d/dt of a smooth loss under a rigid x-translation of a shaded cube, against central
+    # differences of 4x supersampled renders (band: same sign, within 35 %)
+    H = W = 48
+    ss = 4
+    sc = scenes.cube(B=1, H=H, W=W)
+    sc["background"][:] = 0.1
+    big = scenes.cube(B=1, H=H * ss, W=W * ss)
+
+    def render_ss(dx):
+        v = big["vertices"].copy()
+        v[..., 0] += dx * v[..., 3]
+        p, _, _ = golden.forward(np.full((1, H * ss, W * ss, 3), 0.1, np.float32), v, sc["vertex_colors"], sc["faces"])
+        return p.reshape(1, H, ss, W, ss, 3).mean(axis=(2, 4))
+
+    yy, xx = np.mgrid[0:H, 0:W]
+    wgt = (np.sin(xx / 7.0) + np.cos(yy / 5.0))[None, :, :, None].astype(np.float32) * np.ones((1, 1, 1, 3), np.float32)
+    eps = 0.5 * 2.0 / W           # half a pixel in NDC
+    fd = ((render_ss(eps) - render_ss(-eps)) * wgt).sum() / (2 * eps)
+    px, fid, gb = _fwd(sc)
+    gv, _, _ = golden.backward(sc["faces"], px, wgt, fid, gb, 36)
+    # x_clip = x_ndc * w  =>  d/dt sum over vertices of gx * w
+    an = (gv[0, :, 0] * sc["vertices"][0, :, 3]).sum()
+    assert np.sign(fd) == np.sign(an)
+    assert abs(an - fd) <= 0.35 * abs(fd), (an, fd)

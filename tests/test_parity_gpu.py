@@ -1,0 +1,229 @@
+"""GPU: the CUDA path (through the C ABI) against the CPU oracle on identical seeded inputs.
+
+Bars (BASELINE.json north_star): face-id / coverage maps bit-exact; interpolated attributes
+<= 1e-5 relative (abs floor 1e-6); gradients <= 1e-4 relative to max|grad| per tensor.
+"""
+import numpy as np
+import pytest
+import torch
+
+import scenes
+from oracle import golden
+
+pytestmark = pytest.mark.gpu
+
+ATTR_RTOL, ATTR_ATOL = 1e-5, 1e-6
+GRAD_RTOL = 1e-4
+
+
+def _cuda(sc):
+    return {k: torch.from_numpy(np.ascontiguousarray(v)).cuda() for k, v in sc.items() if k != "expected"}
+
+
+def _run_forward(sc, aux=True):
+    from dirt_b200 import rasterise_ops as ops
+    t = _cuda(sc)
+    px, fid, gb = ops.forward_raw(t["background"], t["vertices"], t["vertex_colors"], t["faces"], want_aux=aux)
+    torch.cuda.synchronize()
+    return px, fid, gb, t
+
+
+def _check_forward(sc, threads=8):
+    px, fid, gb, t = _run_forward(sc)
+    opx, ofid, ogb = golden.forward(sc["background"], sc["vertices"], sc["vertex_colors"], sc["faces"], threads=threads)
+    fid_n = fid.cpu().numpy()
+    assert np.array_equal(fid_n, ofid), "face-id maps differ at %d pixels" % (fid_n != ofid).sum()
+    px_n, gb_n = px.cpu().numpy(), gb.cpu().numpy()
+    fin = np.isfinite(opx)
+    assert np.array_equal(np.isfinite(px_n), fin)
+    assert np.array_equal(px_n[~fin], opx[~fin])
+    np.testing.assert_allclose(px_n[fin], opx[fin], rtol=ATTR_RTOL, atol=ATTR_ATOL)
+    np.testing.assert_allclose(gb_n, ogb, rtol=ATTR_RTOL, atol=ATTR_ATOL)
+    return (px, fid, gb, t), (opx, ofid, ogb)
+
+
+def _check_backward(sc, dev, ora, seed=0, shared=False):
+    from dirt_b200 import rasterise_ops as ops
+    px, fid, gb, t = dev
+    opx, ofid, ogb = ora
+    g = np.random.RandomState(seed).randn(*opx.shape).astype(np.float32)
+    g[~np.isfinite(opx)] = 0
+    V = sc["vertices"].shape[1]
+    gv, gc, gbg = ops.backward_raw(t["faces"], px, torch.from_numpy(g).cuda(), fid, gb, V,
+                                   shared_vertices=shared, shared_colors=shared)
+    torch.cuda.synchronize()
+    ogv, ogc, ogbg = golden.backward(sc["faces"], opx, g, ofid, ogb, V, shared_vertices=shared, shared_colors=shared, threads=8)
+    assert np.array_equal(gbg.cpu().numpy(), ogbg)
+    for name, a, b in (("grad_vertices", gv.cpu().numpy(), ogv), ("grad_vertex_colors", gc.cpu().numpy(), ogc)):
+        scale = max(np.abs(b).max(), 1e-12)
+        err = np.abs(a - b).max() / scale
+        assert err <= GRAD_RTOL, "%s: max err %.3g of max|grad|" % (name, err)
+
+
+def test_kat1_and_kat2_bit_exact():
+    for sc in (scenes.kat1_square(), scenes.kat2_square()):
+        px, _, _, _ = _run_forward(sc)
+        assert np.array_equal(px.cpu().numpy(), sc["expected"])
+
+
+def test_c1_square_forward_only_without_aux():
+    sc = scenes.kat1_square()
+    px, fid, gb, _ = _run_forward(sc, aux=False)
+    assert fid is None and gb is None
+    assert np.array_equal(px.cpu().numpy(), sc["expected"])
+
+
+@pytest.mark.parametrize("C", [1, 3])
+def test_cube_c2_forward_backward(C):
+    sc = scenes.cube(B=1, H=256, W=256, C=C)
+    dev, ora = _check_forward(sc)
+    _check_backward(sc, dev, ora)
+
+
+def test_cube_c3_deferred_shapes():
+    # config c3 geometry: B=16, 512x512, three attribute sets incl. a -inf background
+    sc = scenes.cube(B=16, H=512, W=512, C=3)
+    world = np.random.RandomState(1).randn(*sc["vertex_colors"].shape).astype(np.float32) * 3
+    for cols, bgval in ((world, -np.inf), (sc["vertex_colors"], 0.0)):
+        s2 = dict(sc)
+        s2["vertex_colors"] = cols
+        s2["background"] = np.full_like(sc["background"], bgval)
+        dev, ora = _check_forward(s2)
+        _check_backward(s2, dev, ora)
+
+
+def test_cylinder_scene():
+    sc = scenes.cylinder()
+    dev, ora = _check_forward(sc)
+    _check_backward(sc, dev, ora)
+
+
+@pytest.mark.parametrize("F,size,ties", [(300, 0.6, False), (3000, 0.08, False), (400, 0.5, True), (20000, 0.02, False)])
+def test_triangle_soup(F, size, ties):
+    sc = scenes.random_triangles(3, 120, 200, 3, F, seed=F, size=size, depth_ties=ties)
+    dev, ora = _check_forward(sc)
+    _check_backward(sc, dev, ora)
+
+
+def test_ragged_frame_sizes_and_single_channel():
+    for (H, W) in ((1, 1), (7, 33), (17, 16), (31, 250)):
+        sc = scenes.random_triangles(2, H, W, 1, 64, seed=H * W, size=0.9)
+        dev, ora = _check_forward(sc)
+        _check_backward(sc, dev, ora)
+
+
+def test_wide_channels_generic_path():
+    sc = scenes.random_triangles(2, 64, 64, 9, 100, seed=4)
+    dev, ora = _check_forward(sc)
+    _check_backward(sc, dev, ora)
+
+
+def test_near_and_far_plane_clipping():
+    sc = scenes.near_crossing()
+    dev, ora = _check_forward(sc)
+    assert (ora[1] >= 0).mean() > 0.2
+    _check_backward(sc, dev, ora)
+
+
+def test_sphere_small_triangles():
+    sc = scenes.sphere(2, 256, 256, n_lat=96, n_lon=96)
+    dev, ora = _check_forward(sc)
+    _check_backward(sc, dev, ora)
+
+
+def test_empty_inputs():
+    from dirt_b200 import rasterise_ops as ops
+    bg = torch.rand(2, 16, 16, 3, device="cuda")
+    px, fid, gb = ops.forward_raw(bg, torch.zeros(2, 0, 4, device="cuda"), torch.zeros(2, 0, 3, device="cuda"),
+                                  torch.zeros(2, 0, 3, dtype=torch.int32, device="cuda"))
+    assert torch.equal(px, bg) and (fid == -1).all()
+    px, fid, gb = ops.forward_raw(bg[:0], torch.zeros(0, 3, 4, device="cuda"), torch.zeros(0, 3, 3, device="cuda"),
+                                  torch.zeros(0, 1, 3, dtype=torch.int32, device="cuda"))
+    assert px.shape == (0, 16, 16, 3)
+
+
+def test_out_of_range_and_nonfinite_faces_are_skipped():
+    sc = scenes.random_triangles(1, 64, 64, 3, 50, seed=11)
+    sc["faces"][0, 3] = [0, 1, 10 ** 6]
+    sc["faces"][0, 4] = [-1, 1, 2]
+    sc["vertices"][0, 30] = np.nan
+    sc["vertices"][0, 33, 0] = np.inf
+    _check_forward(sc)
+
+
+def test_broadcast_shared_mesh_and_summed_gradients():
+    sc = scenes.cube(B=4, H=64, W=64)
+    sc["faces"] = sc["faces"][:1].copy()
+    sc["vertices"] = np.repeat(sc["vertices"][:1], 1, 0)
+    sc["vertex_colors"] = sc["vertex_colors"][:1].copy()
+    dev, ora = _check_forward(sc)
+    _check_backward(sc, dev, ora, shared=True)
+
+
+def test_determinism_run_to_run():
+    sc = scenes.sphere(2, 128, 128, n_lat=64, n_lon=64)
+    a = _run_forward(sc)
+    b = _run_forward(sc)
+    for x, y in zip(a[:3], b[:3]):
+        assert torch.equal(x, y)
+
+
+def test_public_api_autograd_matches_raw_calls():
+    import dirt_b200
+    sc = scenes.cube(B=2, H=64, W=64)
+    t = _cuda(sc)
+    v = t["vertices"].clone().requires_grad_(True)
+    c = t["vertex_colors"].clone().requires_grad_(True)
+    bg = t["background"].clone().requires_grad_(True)
+    px = dirt_b200.rasterise_batch(bg, v, c, t["faces"])
+    g = torch.randn_like(px)
+    (px * g).sum().backward()
+    gbg, gv, gc = dirt_b200.rasterise_grad(t["background"], t["vertices"], t["vertex_colors"], t["faces"], grad_pixels=g)
+    assert torch.equal(bg.grad, gbg)
+    torch.testing.assert_close(v.grad, gv, rtol=1e-4, atol=1e-5 * float(gv.abs().max()))
+    torch.testing.assert_close(c.grad, gc, rtol=1e-4, atol=1e-5 * float(gc.abs().max()))
+    # unbatched call = batch of one (dirt/rasterise_ops.py:50-54)
+    p1 = dirt_b200.rasterise(t["background"][0], t["vertices"][0], t["vertex_colors"][0], t["faces"][0], None)
+    assert torch.equal(p1, px[0].detach())
+
+
+def test_reference_validation_errors():
+    import dirt_b200
+    bg = torch.zeros(8, 8, 3, device="cuda")
+    v = torch.zeros(3, 4, device="cuda")
+    with pytest.raises(dirt_b200.InvalidArgumentError):
+        dirt_b200.rasterise(bg, v[:, :3], torch.zeros(3, 3, device="cuda"), [[0, 1, 2]])
+    with pytest.raises(dirt_b200.InvalidArgumentError):
+        dirt_b200.rasterise(bg, v, torch.zeros(3, 1, device="cuda"), [[0, 1, 2]])
+    with pytest.raises(dirt_b200.InvalidArgumentError):
+        dirt_b200.rasterise(bg, v, torch.zeros(3, 3, device="cuda"), [[0, 1]])
+    with pytest.raises(dirt_b200.InvalidArgumentError):
+        dirt_b200.rasterise_batch(bg[None].repeat(2, 1, 1, 1), v[None].repeat(3, 1, 1), torch.zeros(3, 3, 3, device="cuda"),
+                                  torch.zeros(3, 1, 3, dtype=torch.int32, device="cuda"))
+
+
+def test_host_buffer_entry_points():
+    import ctypes
+    from dirt_b200 import _lib
+    lib = _lib.load()
+    sc = scenes.cube(B=2, H=48, W=48)
+    B, H, W, C = sc["background"].shape
+    V, F = sc["vertices"].shape[1], sc["faces"].shape[1]
+    px = np.empty((B, H, W, C), np.float32); fid = np.empty((B, H, W), np.int32); gb = np.empty((B, H, W, 4), np.float32)
+    p = lambda a: a.ctypes.data
+    fa = _lib.DirtForwardArgs(_lib.DirtShape(B, H, W, C, V, F), p(sc["background"]), H * W * C, p(sc["vertices"]), V * 4,
+                              p(sc["vertex_colors"]), V * C, p(sc["faces"]), F * 3, p(px), p(fid), p(gb), None, 0)
+    _lib.check(lib.dirt_rasterise_forward_host(ctypes.byref(fa)))
+    opx, ofid, ogb = golden.forward(sc["background"], sc["vertices"], sc["vertex_colors"], sc["faces"])
+    assert np.array_equal(fid, ofid)
+    np.testing.assert_allclose(px, opx, rtol=ATTR_RTOL, atol=ATTR_ATOL)
+    g = np.random.RandomState(0).randn(B, H, W, C).astype(np.float32)
+    gv = np.empty((B, V, 4), np.float32); gc = np.empty((B, V, C), np.float32); gbg = np.empty((B, H, W, C), np.float32)
+    ba = _lib.DirtBackwardArgs(_lib.DirtShape(B, H, W, C, V, F), p(sc["faces"]), F * 3, p(px), p(g), p(fid), p(gb),
+                               p(gv), V * 4, p(gc), V * C, p(gbg))
+    _lib.check(lib.dirt_rasterise_backward_host(ctypes.byref(ba)))
+    ogv, ogc, ogbg = golden.backward(sc["faces"], opx, g, ofid, ogb, V)
+    assert np.array_equal(gbg, ogbg)
+    assert np.abs(gv - ogv).max() <= GRAD_RTOL * np.abs(ogv).max()
+    assert np.abs(gc - ogc).max() <= GRAD_RTOL * np.abs(ogc).max()
+    _lib.check(lib.dirt_release_host_staging())
