@@ -7,9 +7,10 @@
 //
 // Stages (all on the caller's stream):
 //   S0  clear      keys := EMPTY, counters := 0
-//   S1  setup      1 thread / (element, face): clip, project, snap, edge setup.  Triangles whose
-//                  pixel bbox is at most kSmallDim x kSmallDim are sampled on the spot with a
-//                  64-bit atomicMin on the key buffer; the rest go to the large-triangle list.
+//   S1  setup      1 thread / (element, face): clip, project, snap, edge setup.  Three size classes:
+//                  bbox height <= kInlineRows: the thread walks the rows' spans itself, 64-bit
+//                  atomicMin on the key buffer; bbox <= kSpanDim^2: the whole warp does (lane =
+//                  row); larger: appended to the large-triangle list for S2/S3.
 //   S2a bin_count  1 warp / large triangle: exact tile/triangle overlap test, per-tile counters
 //   S2b bin_alloc  1 thread / tile: reserve a contiguous, 16-byte aligned queue segment
 //   S2c bin_fill   1 warp / large triangle: write face references into the tile queues
@@ -17,121 +18,9 @@
 //                  per-entry setup into shared memory, per-pixel register min of the key
 //   S4  resolve    1 thread / pixel: key -> face -> perspective-correct interpolation ->
 //                  pixels (+ face_id, gbuffer), background where uncovered
-#include "raster_core.cuh"
-#include "kernels.h"
+#include "forward_common.cuh"
 
 namespace dirt {
-
-constexpr int kSmallDim = 4;          // bbox (in pixels) handled inline by the setup thread
-constexpr int kTile = 16;             // tile edge in pixels
-constexpr int kTileThreads = kTile * kTile;
-constexpr int kChunk = 128;           // queue entries staged per round in tile_raster
-constexpr uint32_t kSubShift = 30;    // queue entry = face | fan-index << 30
-
-struct BigTri {            // 16 bytes
-    uint32_t elem;         // batch element
-    uint32_t ref;          // face | fan index << 30
-    uint16_t tx0, ty0, tx1, ty1;   // inclusive tile bbox (y up)
-};
-
-__device__ __forceinline__ const float4 *vertex_ptr(const float *vertices, int64_t bstride, int b)
-{
-    return reinterpret_cast<const float4 *>(vertices + (int64_t)b * bstride);
-}
-
-// Loads the three corners of a face; returns false if an index is outside [0, V).
-__device__ __forceinline__ bool load_face(const int32_t *faces, int64_t f_bs, const float *vertices, int64_t v_bs,
-                                          int b, int f, int V, float4 &a, float4 &bb, float4 &c)
-{
-    const int32_t *fp = faces + (int64_t)b * f_bs + 3 * (int64_t)f;
-    int i0 = __ldg(fp), i1 = __ldg(fp + 1), i2 = __ldg(fp + 2);
-    if ((unsigned)i0 >= (unsigned)V || (unsigned)i1 >= (unsigned)V || (unsigned)i2 >= (unsigned)V) return false;
-    const float4 *vp = vertex_ptr(vertices, v_bs, b);
-    a = __ldg(vp + i0); bb = __ldg(vp + i1); c = __ldg(vp + i2);
-    return true;
-}
-
-// Samples every pixel of t's bbox from one thread and merges into the key buffer.
-__device__ void raster_serial(const TriSetup &t, uint32_t face, unsigned long long *keys_elem, int W, int H,
-                              int x0, int x1, int y0, int y1)
-{
-    long long sx[3], sy[3], r0, r1, r2;
-    edge_steps(t, sx, sy);
-    edge_values(t, x0, y0, r0, r1, r2);
-    for (int py = y0; py <= y1; ++py) {
-        long long e0 = r0, e1 = r1, e2 = r2;
-        for (int px = x0; px <= x1; ++px) {
-            if (covered(t, e0, e1, e2)) {
-                float l0, l1, l2;
-                float zw = sample_depth(t, e0, e1, e2, l0, l1, l2);
-                unsigned long long key;
-                if (depth_key(zw, face, key))
-                    atomicMin(keys_elem + (size_t)(H - 1 - py) * W + px, key);
-            }
-            e0 += sx[0]; e1 += sx[1]; e2 += sx[2];
-        }
-        r0 += sy[0]; r1 += sy[1]; r2 += sy[2];
-    }
-}
-
-// Routes one set-up triangle: inline sampling when small, large-triangle list otherwise.
-__device__ __forceinline__ void route_triangle(const TriSetup &t, int b, uint32_t face, uint32_t fan,
-                                               const FwdParams &p)
-{
-    unsigned long long *keys_elem = p.keys + (size_t)b * p.H * p.W;
-    int bw = t.xmax - t.xmin + 1, bh = t.ymax - t.ymin + 1;
-    if (bw <= kSmallDim && bh <= kSmallDim) {
-        raster_serial(t, face, keys_elem, p.W, p.H, t.xmin, t.xmax, t.ymin, t.ymax);
-        return;
-    }
-    uint32_t slot = atomicAdd(&p.counters[kCtrBig], 1u);
-    if (slot < p.cap_big) {
-        BigTri bt;
-        bt.elem = (uint32_t)b;
-        bt.ref = face | (fan << kSubShift);
-        bt.tx0 = (uint16_t)(t.xmin / kTile); bt.tx1 = (uint16_t)(t.xmax / kTile);
-        bt.ty0 = (uint16_t)(t.ymin / kTile); bt.ty1 = (uint16_t)(t.ymax / kTile);
-        reinterpret_cast<uint4 *>(p.big)[slot] = *reinterpret_cast<uint4 *>(&bt);
-    } else {
-        // list full: still correct, just slow
-        raster_serial(t, face, keys_elem, p.W, p.H, t.xmin, t.xmax, t.ymin, t.ymax);
-    }
-}
-
-__global__ void __launch_bounds__(256) k_setup(FwdParams p)
-{
-    long long total = (long long)p.B * p.F;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-         i += (long long)gridDim.x * blockDim.x) {
-        int b = (int)(i / p.F), f = (int)(i - (long long)b * p.F);
-        float4 va, vb, vc;
-        if (!load_face(p.faces, p.faces_bs, p.vertices, p.vertices_bs, b, f, p.V, va, vb, vc)) continue;
-        int cls = classify_face(va, vb, vc);
-        if (cls == 0) continue;
-        TriSetup t;
-        if (cls == 1) {
-            if (setup_face(va, vb, vc, p.W, p.H, t)) route_triangle(t, b, (uint32_t)f, 0u, p);
-        } else {
-            ClipVert poly[6];
-            int n = clip_face(va, vb, vc, poly);
-            for (int s = 1; s + 1 < n; ++s)
-                if (setup_fan(poly, s, p.W, p.H, t)) route_triangle(t, b, (uint32_t)f, (uint32_t)s, p);
-        }
-    }
-}
-
-// Re-derives the TriSetup a queue / list reference stands for.
-__device__ bool setup_from_ref(const FwdParams &p, int b, uint32_t ref, TriSetup &t)
-{
-    uint32_t face = ref & ((1u << kSubShift) - 1u), fan = ref >> kSubShift;
-    float4 va, vb, vc;
-    if (!load_face(p.faces, p.faces_bs, p.vertices, p.vertices_bs, b, (int)face, p.V, va, vb, vc)) return false;
-    if (fan == 0) return setup_face(va, vb, vc, p.W, p.H, t);
-    ClipVert poly[6];
-    int n = clip_face(va, vb, vc, poly);
-    if ((int)fan + 1 >= n) return false;
-    return setup_fan(poly, (int)fan, p.W, p.H, t);
-}
 
 // Exact conservative test: can any pixel centre of tile (tx, ty) be covered by t?
 __device__ __forceinline__ bool tile_overlaps(const TriSetup &t, const long long *sx, const long long *sy,
@@ -396,7 +285,7 @@ cudaError_t launch_forward(const FwdParams &p, int sm_count, cudaStream_t stream
     const long long nfaces = (long long)p.B * p.F;
     if (nfaces > 0) {
         tm.begin(kStageSetup, stream);
-        k_setup<<<grid_for(nfaces, 256, sm_count, 64), 256, 0, stream>>>(p);
+        launch_setup(p, sm_count, stream);
         tm.end(kStageSetup, stream);
         tm.begin(kStageBinCount, stream);
         k_bin<false><<<sm_count * 4, 256, 0, stream>>>(p);

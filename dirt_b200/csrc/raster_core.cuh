@@ -136,7 +136,7 @@ struct ClipVert {
     float b0, b1, b2;       // weights w.r.t. the face's original corners
 };
 
-__device__ __noinline__ int clip_depth_plane(const ClipVert *in, int n, ClipVert *out, int plane)
+static __device__ __noinline__ int clip_depth_plane(const ClipVert *in, int n, ClipVert *out, int plane)
 {
     float d[6];
     int m = 0;
@@ -168,7 +168,7 @@ __device__ __noinline__ int clip_depth_plane(const ClipVert *in, int n, ClipVert
 
 // Clips a face against near then far; poly must hold 6 entries.  Returns the corner count
 // (0 or 3..5).  The clipped polygon is sampled as the fan (0,s,s+1), s = 1..n-2.
-__device__ __noinline__ int clip_face(const float4 &a, const float4 &b, const float4 &c, ClipVert *poly)
+static __device__ __noinline__ int clip_face(const float4 &a, const float4 &b, const float4 &c, ClipVert *poly)
 {
     ClipVert tmp[6];
     poly[0] = {a.x, a.y, a.z, a.w, 1.f, 0.f, 0.f};

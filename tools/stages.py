@@ -1,0 +1,71 @@
+"""Per-stage device times (ms) of fwd+bwd for several workloads; development aid.
+    python tools/stages.py [headline c4 c3 c2 ...]"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "tests")]
+import scenes  # noqa: E402
+from dirt_b200 import rasterise_ops as ops, _lib  # noqa: E402
+
+
+def scene(name):
+    if name == "headline":
+        return scenes.sphere(64, 512, 512)
+    if name == "h8":
+        return scenes.sphere(8, 512, 512)
+    if name == "c4":
+        return scenes.sphere(256, 256, 256)
+    if name == "c3":
+        return scenes.cube(B=16, H=512, W=512)
+    if name == "c2":
+        return scenes.cube(B=1, H=256, W=256)
+    if name == "soup":
+        return scenes.random_triangles(16, 512, 512, 3, 2000, seed=1, size=0.3)
+    if name == "quad":
+        sc = scenes.kat2_square()
+        sc.pop("expected")
+        sc["vertices"][..., :2] = sc["vertices"][..., :2] * 2 - 1
+        return {k: np.repeat(v, 16, 0) for k, v in sc.items()}
+    raise SystemExit("unknown workload " + name)
+
+
+def main():
+    lib = _lib.load()
+    for name in (sys.argv[1:] or ["headline", "c4", "c3", "c2"]):
+        sc = scene(name)
+        d = {k: torch.from_numpy(np.ascontiguousarray(v)).cuda() for k, v in sc.items()}
+        B, H, W, C = sc["background"].shape
+        V = sc["vertices"].shape[1]
+        g = torch.randn(B, H, W, C, device="cuda")
+
+        def step():
+            px, fid, gb = ops.forward_raw(d["background"], d["vertices"], d["vertex_colors"], d["faces"])
+            return ops.backward_raw(d["faces"], px, g, fid, gb, V)
+
+        for _ in range(3):
+            step()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        n = 10
+        for _ in range(n):
+            step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / n
+        lib.dirt_profile_reset(); lib.dirt_profile_enable(1)
+        for _ in range(5):
+            step(); torch.cuda.synchronize(); lib.dirt_profile_collect()
+        lib.dirt_profile_enable(0)
+        st = {k: m / max(c, 1) for k, (m, c) in _lib.stage_times().items()}
+        print("%-9s B=%d %dx%d F=%d  step %.3f ms  %.0f Mpix/s | %s" % (
+            name, B, H, W, sc["faces"].shape[1], ms, B * H * W / ms / 1e3,
+            " ".join("%s=%.3f" % (k, v) for k, v in st.items())), flush=True)
+
+
+if __name__ == "__main__":
+    main()
