@@ -20,7 +20,7 @@ dirt::StageTimer g_timer;
 double g_stage_ms[dirt::kStageCount] = {};
 uint64_t g_stage_calls[dirt::kStageCount] = {};
 const char *const kStageNames[dirt::kStageCount] = {
-    "clear", "setup", "bin_count", "bin_alloc", "bin_fill", "tile_raster", "resolve", "grad_clear", "grad_assemble"};
+    "clear", "project", "setup", "bin_count", "bin_alloc", "bin_fill", "tile_raster", "resolve", "grad_clear", "grad_assemble"};
 
 int fail(int status, const char *fmt, ...)
 {
@@ -42,7 +42,7 @@ inline size_t align_up(size_t v) { return (v + kAlign - 1) / kAlign * kAlign; }
 
 // Workspace carve-up.  Offsets are a pure function of the shape.
 struct Layout {
-    size_t keys, counters, tile_count, tile_cursor, tile_offset, big, queue, total;
+    size_t keys, proj, counters, tile_count, tile_cursor, tile_offset, big, queue, total;
     size_t zero_bytes;
     uint32_t cap_big;
     unsigned long long cap_queue;
@@ -66,6 +66,7 @@ Layout workspace_layout(const DirtShape &s)
     L.cap_queue = 8ull * ntiles + 4ull * nfaces + 4096ull;
     size_t off = 0;
     L.keys = off;        off = align_up(off + npix * sizeof(unsigned long long));
+    L.proj = off;        off = align_up(off + (size_t)s.batch * s.vertex_count * 16);
     L.counters = off;    off += dirt::kCtrCount * sizeof(uint32_t);
     L.tile_count = off;  off += ntiles * sizeof(uint32_t);
     L.tile_cursor = off; off += ntiles * sizeof(uint32_t);
@@ -169,6 +170,8 @@ int dirt_rasterise_forward(const DirtForwardArgs *a, void *stream)
     p.pixels = a->pixels; p.face_id = a->face_id; p.gbuffer = a->gbuffer;
     char *ws = static_cast<char *>(a->workspace);
     p.keys = reinterpret_cast<unsigned long long *>(ws + L.keys);
+    p.proj = reinterpret_cast<const int4 *>(ws + L.proj);
+    p.proj_bs = a->vertices_bstride == 0 ? 0 : s.vertex_count;
     p.counters = reinterpret_cast<uint32_t *>(ws + L.counters);
     p.tile_count = reinterpret_cast<uint32_t *>(ws + L.tile_count);
     p.tile_cursor = reinterpret_cast<uint32_t *>(ws + L.tile_cursor);

@@ -177,10 +177,8 @@ __global__ void __launch_bounds__(kTileThreads) k_tile_raster(FwdParams p)
                 long long e0, e1, e2;
                 edge_values(t, px, py, e0, e1, e2);
                 if (!covered(t, e0, e1, e2)) continue;
-                float l0, l1, l2;
-                float zw = sample_depth(t, e0, e1, e2, l0, l1, l2);
                 unsigned long long key;
-                if (depth_key(zw, s_ref[j] & ((1u << kSubShift) - 1u), key)) best = min(best, key);
+                if (depth_key(sample_depth(t, px, py), s_ref[j] & ((1u << kSubShift) - 1u), key)) best = min(best, key);
             }
         }
         __syncthreads();
@@ -213,20 +211,21 @@ __global__ void __launch_bounds__(256) k_resolve(FwdParams p)
         const int f = (int)(uint32_t)(key & 0xFFFFFFFFull);
         const int32_t *fp = p.faces + (int64_t)b * p.faces_bs + 3 * (int64_t)f;
         const int i0 = __ldg(fp), i1 = __ldg(fp + 1), i2 = __ldg(fp + 2);
-        const float4 *vp = vertex_ptr(p.vertices, p.vertices_bs, b);
-        const float4 va = __ldg(vp + i0), vb = __ldg(vp + i1), vc = __ldg(vp + i2);
         float B0 = 0.f, B1 = 0.f, wc = 1.f, zw = 1.f;
         TriSetup t;
-        int cls = classify_face(va, vb, vc);
-        if (cls == 1) {
-            setup_face(va, vb, vc, p.W, p.H, t);
+        const int4 *pp = proj_ptr(p, b);
+        bool slow;
+        if (setup_from_proj(__ldg(pp + i0), __ldg(pp + i1), __ldg(pp + i2), p.W, p.H, t, slow)) {
             long long e0, e1, e2;
             edge_values(t, px, py, e0, e1, e2);
             float l0, l1, l2, b2;
-            zw = sample_depth(t, e0, e1, e2, l0, l1, l2);
+            screen_bary(t, e0, e1, e2, l0, l1, l2);
+            zw = sample_depth(t, px, py);
             perspective_weights(t, l0, l1, l2, B0, B1, b2, wc);
-        } else {
+        } else if (slow) {
             // clipped face: find the fan triangle that owns this pixel (exactly one does)
+            const float4 *vp = vertex_ptr(p.vertices, p.vertices_bs, b);
+            const float4 va = __ldg(vp + i0), vb = __ldg(vp + i1), vc = __ldg(vp + i2);
             ClipVert poly[6];
             int n = clip_face(va, vb, vc, poly);
             for (int s = 1; s + 1 < n; ++s) {
@@ -236,8 +235,8 @@ __global__ void __launch_bounds__(256) k_resolve(FwdParams p)
                 edge_values(t, px, py, e0, e1, e2);
                 if (!covered(t, e0, e1, e2)) continue;
                 float l0, l1, l2, b0, b1, b2;
-                zw = sample_depth(t, e0, e1, e2, l0, l1, l2);
-                if (!(zw >= 0.0f && zw <= 1.0f)) continue;
+                screen_bary(t, e0, e1, e2, l0, l1, l2);
+                zw = sample_depth(t, px, py);
                 perspective_weights(t, l0, l1, l2, b0, b1, b2, wc);
                 const ClipVert &q0 = poly[0], &q1 = poly[s], &q2 = poly[s + 1];
                 B0 = fadd(fadd(fmul(b0, q0.b0), fmul(b1, q1.b0)), fmul(b2, q2.b0));
@@ -284,9 +283,7 @@ cudaError_t launch_forward(const FwdParams &p, int sm_count, cudaStream_t stream
     tm.end(kStageClear, stream);
     const long long nfaces = (long long)p.B * p.F;
     if (nfaces > 0) {
-        tm.begin(kStageSetup, stream);
-        launch_setup(p, sm_count, stream);
-        tm.end(kStageSetup, stream);
+        launch_setup(p, sm_count, stream, tm);
         tm.begin(kStageBinCount, stream);
         k_bin<false><<<sm_count * 4, 256, 0, stream>>>(p);
         tm.end(kStageBinCount, stream);
@@ -299,7 +296,7 @@ cudaError_t launch_forward(const FwdParams &p, int sm_count, cudaStream_t stream
         tm.begin(kStageTileRaster, stream);
         k_tile_raster<<<(unsigned)ntiles, kTileThreads, 0, stream>>>(p);
         tm.end(kStageTileRaster, stream);
-        *launches += 5;
+        *launches += 6;
     }
     const int g = grid_for((long long)npix_total, 256, sm_count, 64);
     tm.begin(kStageResolve, stream);

@@ -5,8 +5,9 @@
 
 namespace dirt {
 
-constexpr int kInlineRows = 24;       // bbox height up to which the setup thread walks the rows itself
-constexpr int kSpanDim = 128;         // bbox edge up to which the setup warp walks the rows (lane = row)
+constexpr int kSmallExtent = (1 << 15) - 512;   // sub-pixel extent (126 px) below which edge functions, evaluated up to
+                                                // two pixels outside the bbox, fit in int32: 2 * (e + 512) * e < 2^31
+constexpr int kProjSlow = (int)0x80000000;   // ProjVert.X of a vertex that needs the general (clipping) path
 constexpr int kTile = 16;             // tile edge in pixels
 constexpr int kTileThreads = kTile * kTile;
 constexpr int kChunk = 128;           // queue entries staged per round in tile_raster
@@ -35,6 +36,27 @@ __device__ __forceinline__ bool load_face(const int32_t *faces, int64_t f_bs, co
     return true;
 }
 
+// Projected vertex record written by k_project: snapped window position, window depth, 1/w.
+// X == kProjSlow marks a vertex that is not plainly inside the depth range with w > 0 (or is
+// not finite); faces touching one go through classify_face / clip_face on the clip-space data.
+__device__ __forceinline__ const int4 *proj_ptr(const FwdParams &p, int b)
+{
+    return p.proj + (int64_t)b * p.proj_bs;
+}
+
+// TriSetup from three projected records.  Returns false if culled; `slow` is set when a corner
+// needs the general path (then t is untouched).
+__device__ __forceinline__ bool setup_from_proj(const int4 &a, const int4 &b, const int4 &c, int W, int H,
+                                                TriSetup &t, bool &slow)
+{
+    slow = a.x == kProjSlow || b.x == kProjSlow || c.x == kProjSlow;
+    if (slow) return false;
+    t.X0 = a.x; t.Y0 = a.y; t.zw0 = __int_as_float(a.z); t.rw0 = __int_as_float(a.w);
+    t.X1 = b.x; t.Y1 = b.y; t.zw1 = __int_as_float(b.z); t.rw1 = __int_as_float(b.w);
+    t.X2 = c.x; t.Y2 = c.y; t.zw2 = __int_as_float(c.z); t.rw2 = __int_as_float(c.w);
+    return finish_setup(t, W, H);
+}
+
 // Samples every pixel of t's bbox from one thread and merges into the key buffer.
 __device__ inline void raster_serial(const TriSetup &t, uint32_t face, unsigned long long *keys_elem, int W, int H,
                               int x0, int x1, int y0, int y1)
@@ -46,10 +68,8 @@ __device__ inline void raster_serial(const TriSetup &t, uint32_t face, unsigned 
         long long e0 = r0, e1 = r1, e2 = r2;
         for (int px = x0; px <= x1; ++px) {
             if (covered(t, e0, e1, e2)) {
-                float l0, l1, l2;
-                float zw = sample_depth(t, e0, e1, e2, l0, l1, l2);
                 unsigned long long key;
-                if (depth_key(zw, face, key))
+                if (depth_key(sample_depth(t, px, py), face, key))
                     atomicMin(keys_elem + (size_t)(H - 1 - py) * W + px, key);
             }
             e0 += sx[0]; e1 += sx[1]; e2 += sx[2];
@@ -80,6 +100,15 @@ __device__ inline void push_big(const TriSetup &t, int b, uint32_t face, uint32_
 __device__ inline bool setup_from_ref(const FwdParams &p, int b, uint32_t ref, TriSetup &t)
 {
     uint32_t face = ref & ((1u << kSubShift) - 1u), fan = ref >> kSubShift;
+    if (fan == 0) {
+        const int32_t *fp = p.faces + (int64_t)b * p.faces_bs + 3 * (int64_t)face;
+        const int i0 = __ldg(fp), i1 = __ldg(fp + 1), i2 = __ldg(fp + 2);
+        if ((unsigned)i0 >= (unsigned)p.V || (unsigned)i1 >= (unsigned)p.V || (unsigned)i2 >= (unsigned)p.V) return false;
+        const int4 *pp = proj_ptr(p, b);
+        bool slow;
+        const bool ok = setup_from_proj(__ldg(pp + i0), __ldg(pp + i1), __ldg(pp + i2), p.W, p.H, t, slow);
+        if (!slow) return ok;
+    }
     float4 va, vb, vc;
     if (!load_face(p.faces, p.faces_bs, p.vertices, p.vertices_bs, b, (int)face, p.V, va, vb, vc)) return false;
     if (fan == 0) return setup_face(va, vb, vc, p.W, p.H, t);
@@ -89,6 +118,6 @@ __device__ inline bool setup_from_ref(const FwdParams &p, int b, uint32_t ref, T
     return setup_fan(poly, (int)fan, p.W, p.H, t);
 }
 
-void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream);
+void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, StageTimer &tm);
 
 }  // namespace dirt

@@ -20,6 +20,8 @@ struct FwdParams {
     int32_t *face_id;            // optional (with gbuffer)
     float *gbuffer;
     // workspace carve-up (see workspace_layout in capi.cu)
+    const int4 *proj;            // [mB*V] projected vertices (k_project); mB = 1 when vertices are broadcast
+    int64_t proj_bs;             // V, or 0 when vertices are broadcast
     unsigned long long *keys;    // [B*H*W] depth24 << 32 | face
     uint32_t *counters;          // [kCtrCount]; counters, tile_count, tile_cursor are contiguous
     uint32_t *tile_count;        // [B*tiles]
@@ -45,7 +47,7 @@ struct BwdParams {
 };
 
 enum Stage {
-    kStageClear = 0, kStageSetup, kStageBinCount, kStageBinAlloc, kStageBinFill, kStageTileRaster, kStageResolve,
+    kStageClear = 0, kStageProject, kStageSetup, kStageBinCount, kStageBinAlloc, kStageBinFill, kStageTileRaster, kStageResolve,
     kStageGradClear, kStageGradAssemble, kStageCount
 };
 

@@ -35,6 +35,7 @@ struct TriSetup {
     int X0, Y0, X1, Y1, X2, Y2;   // 1/256 px, y up
     float zw0, zw1, zw2;
     float rw0, rw1, rw2;
+    float zref, dzdx, dzdy;       // depth plane: zw at the centre of pixel (xmin, ymin); step per pixel in x, y
     float rcp_area;               // 1 / |2*area|
     int sign;                     // +1 / -1: sign * edge >= 0 inside
     int bias0, bias1, bias2;      // 0 = edge owns its samples, -1 = it does not
@@ -77,6 +78,32 @@ __device__ __forceinline__ bool project_corner(float x, float y, float z, float 
     return true;
 }
 
+// Window depth is affine in window x, y (OpenGL 3.3 core eq. 3.10).  It is evaluated as a plane
+// through corner 0 (docs/RASTER_SPEC.md section 6): gradients per sub-pixel unit from the two
+// edge vectors, then re-based to the centre of the bbox's first pixel so that a sample costs
+// two multiplies and two adds.  Every operation is individually rounded.
+__device__ __forceinline__ void depth_plane(TriSetup &t, long long area2)
+{
+    const float fA = __ll2float_rn(area2);
+    const float dz1 = fsub(t.zw1, t.zw0), dz2 = fsub(t.zw2, t.zw0);
+    const float dX1 = __int2float_rn(t.X1 - t.X0), dY1 = __int2float_rn(t.Y1 - t.Y0);
+    const float dX2 = __int2float_rn(t.X2 - t.X0), dY2 = __int2float_rn(t.Y2 - t.Y0);
+    const float gx = fdiv(fsub(fmul(dz1, dY2), fmul(dz2, dY1)), fA);
+    const float gy = fdiv(fsub(fmul(dz2, dX1), fmul(dz1, dX2)), fA);
+    const float rx = __int2float_rn(t.xmin * kSubpix + kSubpixHalf - t.X0);
+    const float ry = __int2float_rn(t.ymin * kSubpix + kSubpixHalf - t.Y0);
+    t.zref = fadd(t.zw0, fadd(fmul(gx, rx), fmul(gy, ry)));
+    t.dzdx = fmul(gx, (float)kSubpix);
+    t.dzdy = fmul(gy, (float)kSubpix);
+}
+
+// Window depth at the centre of pixel (px, py), clamped to the depth range.
+__device__ __forceinline__ float plane_depth(float zref, float dzdx, float dzdy, int dx, int dy)
+{
+    float zw = fadd(fadd(zref, fmul(dzdx, __int2float_rn(dx))), fmul(dzdy, __int2float_rn(dy)));
+    return fminf(fmaxf(zw, 0.0f), 1.0f);
+}
+
 // Finish a TriSetup whose corners are already projected.  Returns false if culled.
 __device__ __forceinline__ bool finish_setup(TriSetup &t, int W, int H)
 {
@@ -94,7 +121,9 @@ __device__ __forceinline__ bool finish_setup(TriSetup &t, int W, int H)
     t.xmax = min((maxX - kSubpixHalf) >> kSubpixBits, W - 1);
     t.ymin = max((minY + kSubpixHalf - 1) >> kSubpixBits, 0);
     t.ymax = min((maxY - kSubpixHalf) >> kSubpixBits, H - 1);
-    return t.xmin <= t.xmax && t.ymin <= t.ymax;
+    if (t.xmin > t.xmax || t.ymin > t.ymax) return false;
+    depth_plane(t, area2);
+    return true;
 }
 
 // Frustum classification of a face from its three clip-space corners.
@@ -229,21 +258,25 @@ __device__ __forceinline__ bool covered(const TriSetup &t, long long e0, long lo
     return (e0 + t.bias0 >= 0) && (e1 + t.bias1 >= 0) && (e2 + t.bias2 >= 0);
 }
 
-// Window depth of a covered sample; affine in window space (OpenGL 3.3 core eq. 3.10).
-__device__ __forceinline__ float sample_depth(const TriSetup &t, long long e0, long long e1, long long e2,
-                                              float &l0, float &l1, float &l2)
+// Window depth of the sample at pixel (px, py).
+__device__ __forceinline__ float sample_depth(const TriSetup &t, int px, int py)
+{
+    return plane_depth(t.zref, t.dzdx, t.dzdy, px - t.xmin, py - t.ymin);
+}
+
+// Screen-space barycentrics of a covered sample from its edge values.
+__device__ __forceinline__ void screen_bary(const TriSetup &t, long long e0, long long e1, long long e2,
+                                            float &l0, float &l1, float &l2)
 {
     l0 = fmul(__ll2float_rn(e0), t.rcp_area);
     l1 = fmul(__ll2float_rn(e1), t.rcp_area);
     l2 = fmul(__ll2float_rn(e2), t.rcp_area);
-    return fadd(fadd(fmul(l0, t.zw0), fmul(l1, t.zw1)), fmul(l2, t.zw2));
 }
 
-// Depth test key: depth24 << 32 | face.  Returns false when the fragment is clipped by the
-// depth range or cannot pass GL_LESS against the cleared value 1.0 (rasterise_egl.cpp:449).
+// Depth test key: depth24 << 32 | face (zw already clamped to [0, 1]).  Returns false when the
+// fragment cannot pass GL_LESS against the cleared value 1.0 (rasterise_egl.cpp:449).
 __device__ __forceinline__ bool depth_key(float zw, uint32_t face, unsigned long long &key)
 {
-    if (!(zw >= 0.0f && zw <= 1.0f)) return false;
     uint32_t d = __float2uint_rz(fadd(fmul(zw, 16777215.0f), 0.5f));
     if (d >= kDepthMax) return false;
     key = ((unsigned long long)d << 32) | face;

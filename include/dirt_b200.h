@@ -101,8 +101,8 @@ DIRT_API int dirt_abi_version(void);
 /* Thread-local message of the last failing call on this thread ("" if none). */
 DIRT_API const char *dirt_last_error(void);
 
-/* Scratch the forward pass needs for `shape` (depth|face-id keys, tile counters and queues,
- * large-triangle records).  Replaces the grow-only GL framebuffer / buffers the reference
+/* Scratch the forward pass needs for `shape` (depth|face-id keys, projected vertices, tile counters
+ * and queues, large-triangle records).  Replaces the grow-only GL framebuffer / buffers the reference
  * keeps per GL thread (csrc/rasterise_egl.cpp:73-89, :199-274, :347-354); here the caller
  * owns it, so torch's / TF's caching allocator can. */
 DIRT_API size_t dirt_workspace_bytes(const DirtShape *shape);
@@ -138,7 +138,7 @@ DIRT_API uint64_t dirt_kernel_launch_count(void);
  *                              every stage recorded since the last collect into the totals
  *   dirt_profile_read()     -> cumulative milliseconds and launch counts per stage
  * Stage order: see dirt_profile_stage_name(i), i in [0, DIRT_STAGE_COUNT). */
-#define DIRT_STAGE_COUNT 9
+#define DIRT_STAGE_COUNT 10
 DIRT_API int dirt_profile_enable(int enable);
 DIRT_API int dirt_profile_collect(void);
 DIRT_API int dirt_profile_read(double *total_ms, uint64_t *calls, int n);

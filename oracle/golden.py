@@ -26,8 +26,7 @@ def build(force=False):
 def _load():
     global _lib
     if _lib is None:
-        if not os.path.exists(_SO):
-            build()
+        build()          # no-op when the library is newer than golden_raster.c
         lib = ctypes.CDLL(_SO)
         i32, i64, vp = ctypes.c_int, ctypes.c_int64, ctypes.c_void_p
         lib.golden_rasterise_forward.argtypes = [i32] * 6 + [vp, i64, vp, i64, vp, i64, vp, i64, vp, vp, vp, i32]

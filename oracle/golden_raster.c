@@ -63,6 +63,8 @@ typedef struct {
     int64_t area2;         /* twice the signed area (before sign normalisation)   */
     int sign;              /* +1 / -1 so that sign * edge >= 0 inside             */
     float rcp_area;        /* 1 / |area2| as float                                */
+    float zref, dzdx, dzdy; /* depth plane re-based to the centre of pixel (xmin, ymin);
+                              steps per pixel (docs/RASTER_SPEC.md section 6)       */
     int bias[3];           /* 0 if edge k is inclusive (top-left), else -1        */
     int xmin, xmax, ymin, ymax;   /* inclusive pixel bbox clipped to viewport, y up */
 } SubTri;
@@ -206,6 +208,23 @@ static int setup_subtri(const ClipVert *p0, const ClipVert *p1, const ClipVert *
     if (t->xmax > W - 1) t->xmax = W - 1;
     if (t->ymax > H - 1) t->ymax = H - 1;
     if (t->xmin > t->xmax || t->ymin > t->ymax) return 0;
+    /* window depth is affine in window x,y (OpenGL 3.3 core 3.6.1, eq. 3.10): plane through
+     * corner 0, gradients per sub-pixel unit, every operation individually rounded */
+    {
+        float fA = (float)t->area2;
+        float dz1 = t->zw[1] - t->zw[0], dz2 = t->zw[2] - t->zw[0];
+        float dX1 = (float)(t->X[1] - t->X[0]), dY1 = (float)(t->Y[1] - t->Y[0]);
+        float dX2 = (float)(t->X[2] - t->X[0]), dY2 = (float)(t->Y[2] - t->Y[0]);
+        float a = dz1 * dY2, b = dz2 * dY1, c = dz2 * dX1, d = dz1 * dX2;
+        float gx = (a - b) / fA, gy = (c - d) / fA;
+        float rx = (float)(t->xmin * SUBPIX + SUBPIX_HALF - t->X[0]);
+        float ry = (float)(t->ymin * SUBPIX + SUBPIX_HALF - t->Y[0]);
+        float u = gx * rx, v = gy * ry;
+        float uv = u + v;
+        t->zref = t->zw[0] + uv;
+        t->dzdx = gx * (float)SUBPIX;
+        t->dzdy = gy * (float)SUBPIX;
+    }
     return 1;
 }
 
@@ -223,9 +242,11 @@ static int sample_subtri(const SubTri *t, int px, int py, Sample *s)
     float l0 = (float)e[0] * t->rcp_area;
     float l1 = (float)e[1] * t->rcp_area;
     float l2 = (float)e[2] * t->rcp_area;
-    /* window-space depth is affine in window x,y (OpenGL 3.3 core 3.6.1, eq. 3.10) */
-    float zw = (l0 * t->zw[0] + l1 * t->zw[1]) + l2 * t->zw[2];
-    if (!(zw >= 0.0f && zw <= 1.0f)) return 0;
+    /* depth from the plane; clamped to the depth range (fragments of a clipped polygon lie
+     * inside it up to rounding) */
+    float zx = t->dzdx * (float)(px - t->xmin), zy = t->dzdy * (float)(py - t->ymin);
+    float zw = (t->zref + zx) + zy;
+    zw = fminf(fmaxf(zw, 0.0f), 1.0f);
     /* perspective-correct weights (eq. 3.9): b_k = (l_k / w_k) / sum_m (l_m / w_m) */
     float q0 = l0 * t->rw[0], q1 = l1 * t->rw[1], q2 = l2 * t->rw[2];
     float qs = (q0 + q1) + q2;

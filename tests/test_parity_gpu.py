@@ -39,6 +39,8 @@ def _check_forward(sc, threads=8):
     assert np.array_equal(px_n[~fin], opx[~fin])
     np.testing.assert_allclose(px_n[fin], opx[fin], rtol=ATTR_RTOL, atol=ATTR_ATOL)
     np.testing.assert_allclose(gb_n, ogb, rtol=ATTR_RTOL, atol=ATTR_ATOL)
+    # window depth feeds the depth|face keys: it is specified operation by operation, so bit-exact
+    assert np.array_equal(gb_n[..., 3].view(np.int32), ogb[..., 3].view(np.int32)), "window depth differs in bits"
     return (px, fid, gb, t), (opx, ofid, ogb)
 
 
