@@ -94,6 +94,14 @@ __device__ __forceinline__ int write_record(uint32_t *rec, const TriSetup &t, ui
     return axis ? bw : bh;
 }
 
+// The depth half (high word) of a key.  Cached in L1: staleness is harmless (see sample_line).
+__device__ __forceinline__ uint32_t load_depth_word(const unsigned long long *kp)
+{
+    uint32_t v;
+    asm volatile("ld.global.ca.u32 %0, [%1];" : "=r"(v) : "l"(reinterpret_cast<const uint32_t *>(kp) + 1));
+    return v;
+}
+
 // Samples line `j` of the triangle in `rec` (a row when axis == 0, a column when axis == 1).
 __device__ __forceinline__ void sample_line(const uint32_t *rec, int j, const FwdParams &p)
 {
@@ -132,16 +140,28 @@ __device__ __forceinline__ void sample_line(const uint32_t *rec, int j, const Fw
     unsigned long long *kp = p.keys + ((size_t)rec[rELEM] * p.H + (size_t)(p.H - 1 - py0)) * p.W + px0;
     const long long stride = axis ? -(long long)p.W : 1ll;
     float fi = __int2float_rn(lo);
-    for (int i = lo; i <= hi; ++i) {
-        float zw = axis ? fadd(c1, fmul(dzdy, fi)) : fadd(fadd(zref, fmul(dzdx, fi)), c2);
-        zw = fminf(fmaxf(zw, 0.0f), 1.0f);
-        unsigned long long key;
-        if (depth_key(zw, face, key)) {
-            // keys only ever decrease, so a stale read can only cost a redundant atomic
-            if (key < __ldcg(kp)) atomicMin(kp, key);
+    // Four fragments per round: their current depths are fetched together (independent loads),
+    // so a line pays the memory latency once per four fragments instead of once per fragment.
+    for (int i = lo; i <= hi; i += 4) {
+        const int n = hi - i + 1;
+        uint32_t cur[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            cur[u] = u < n ? load_depth_word(kp + u * stride) : 0u;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (u < n) {
+                float zw = axis ? fadd(c1, fmul(dzdy, fi)) : fadd(fadd(zref, fmul(dzdx, fi)), c2);
+                zw = fminf(fmaxf(zw, 0.0f), 1.0f);
+                const uint32_t d = __float2uint_rz(fadd(fmul(zw, 16777215.0f), 0.5f));
+                // keys only ever decrease, so a stale depth can only cost a redundant atomic;
+                // on equal depth the atomic decides (lowest face index wins)
+                if (d < kDepthMax && d <= cur[u])
+                    atomicMin(kp + u * stride, ((unsigned long long)d << 32) | face);
+                fi += 1.0f;
+            }
         }
-        kp += stride;
-        fi += 1.0f;
+        kp += 4 * stride;
     }
 }
 
