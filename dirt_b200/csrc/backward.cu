@@ -7,200 +7,218 @@
 // [B,V,C] and write grad_background [B,H,W,C].  The gradient definition is
 // docs/GRADIENT_SPEC.md ("filter-based derivatives", README.md:146-147).
 //
-// One thread per pixel.  Contributions to the same vertex are first summed across the warp
-// (__match_any_sync on the vertex index + shuffle tree), so a warp issues one atomic per
-// distinct vertex; the 4-wide position gradient goes out as a single 16-byte vector atomic.
+// One CTA of 16x16 threads per 14x14-pixel output tile; the outer ring of threads is a halo.
+//   phase 0  the 18x18 neighbourhood (pixels, face id, window depth) is staged in shared memory
+//   phase 1  every thread: Sobel response of `pixels` weighted by grad_pixels, then the OWNER of
+//            the x- and of the row-direction change (itself or the occluding neighbour) and a
+//            plain store of the response into the owner's inbox slot -- a pixel has exactly
+//            three possible senders per axis, so no atomics are needed and the sum is
+//            deterministic
+//   phase 2  every covered interior pixel folds its inbox into (d/dx, d/dy, d/dw) of its own
+//            surface point and scatters ONE contribution to its own face's three vertices.
+//            Lanes of a warp that hit the same face are first summed with __match_any_sync +
+//            a shuffle tree (visible faces span many pixels, and a warp is an 8x4 pixel block,
+//            so this removes most atomics); the position gradient goes out as one 16-byte
+//            vector reduction, colours as 8-byte + 4-byte reductions when C == 3.
 #include <cfloat>
 #include "kernels.h"
 
 namespace dirt {
 
 constexpr unsigned kFull = 0xFFFFFFFFu;
+constexpr int kBT = 16;                 // threads per CTA edge
+constexpr int kBI = kBT - 2;            // interior (output) pixels per CTA edge
+constexpr int kBR = kBT + 2;            // staged region edge
+constexpr int kMaxC = 16;
 
-// Sums v[] over the lanes that hold the same key.  Returns true on the lane that ends up
-// holding the group's total (the lowest lane of the group).
+__device__ __forceinline__ float finite_or_zero(float v) { return fabsf(v) <= FLT_MAX ? v : 0.0f; }
+
+// Sums v[] over the lanes of `peers` (which contains this lane).  Returns true on the lowest
+// lane of the group, which ends up holding the total.
 template <int NV>
-__device__ __forceinline__ bool peer_reduce(int key, unsigned same_elem, float (&v)[NV])
+__device__ __forceinline__ bool peer_reduce(unsigned peers, float (&v)[NV])
 {
     const int lane = threadIdx.x & 31;
-    const unsigned peers = __match_any_sync(kFull, key) & same_elem;
     int rank = __popc(peers & ((1u << lane) - 1u));
     const bool leader = rank == 0;
-    unsigned above = peers & ~((2u << lane) - 1u);
+    unsigned above = peers & ~((2u << lane) - 1u);      // group members on higher lanes
     while (__any_sync(kFull, above != 0u)) {
-        const int next = __ffs(above) - 1;
+        const int next = __ffs(above) - 1;              // -1: nothing to fetch
 #pragma unroll
         for (int i = 0; i < NV; ++i) {
-            float t = __shfl_sync(kFull, v[i], next & 31);
+            const float t = __shfl_sync(kFull, v[i], next & 31);
             if (next >= 0) v[i] += t;
         }
+        // survivors of this round are the even-ranked members; drop the odd-ranked ones
         above &= __ballot_sync(kFull, (rank & 1) == 0);
+        if (rank & 1) above = 0u;
         rank >>= 1;
     }
     return leader;
 }
 
-__device__ __forceinline__ float finite_or_zero(float v) { return fabsf(v) <= FLT_MAX ? v : 0.0f; }
-
-// Which pixel's surface owns the image change seen at p along one axis (GRADIENT_SPEC 3):
+// Which pixel's surface owns the image change seen at a pixel along one axis (GRADIENT_SPEC 3):
 // a covered neighbour on a different face with strictly smaller window depth is an occluder;
-// the nearer neighbour wins, the lower-coordinate one on a tie.  Returns -1 if nobody does.
-__device__ __forceinline__ long long pick_owner(const int32_t *face_id, const float4 *gbuf,
-                                                long long p, int fp, float zp_self, long long m, long long q)
+// the nearer neighbour wins, the lower-coordinate one (m) on a tie.
+// Returns 0 = nobody, 1 = the lower neighbour m, 2 = the pixel itself, 3 = the upper neighbour q.
+__device__ __forceinline__ int pick_owner(int fp, float zself, int fm, float zm, int fq, float zq)
 {
-    const float zp = fp >= 0 ? zp_self : 2.0f;
-    long long best = fp >= 0 ? p : -1;
+    const float zp = fp >= 0 ? zself : 2.0f;
+    int best = fp >= 0 ? 2 : 0;
     float zbest = zp;
-    if (m >= 0) {
-        int fc = __ldg(face_id + m);
-        if (fc >= 0 && fc != fp) {
-            float zc = __ldg(&gbuf[m].w);
-            if (zc < zp && zc < zbest) { best = m; zbest = zc; }
-        }
-    }
-    if (q >= 0) {
-        int fc = __ldg(face_id + q);
-        if (fc >= 0 && fc != fp) {
-            float zc = __ldg(&gbuf[q].w);
-            if (zc < zp && zc < zbest) { best = q; zbest = zc; }
-        }
-    }
+    if (fm >= 0 && fm != fp && zm < zp && zm < zbest) { best = 1; zbest = zm; }
+    if (fq >= 0 && fq != fp && zq < zp && zq < zbest) { best = 3; zbest = zq; }
     return best;
 }
 
-// Adds (gx, gy, 0, gw) * B_k (+ colour gradients when NCOL > 0) to the three vertices of
-// `face`, warp-aggregated.  Every lane of the warp must call this; lanes with face < 0 only
-// take part in the votes.
-template <int NCOL>
-__device__ __forceinline__ void scatter_face(const BwdParams &p, int b, unsigned same_elem, int face, float B0, float B1,
-                                             float gx, float gy, float gw, const float *gcol, int C)
+// 8-byte / 4-byte reductions for a 3-float colour gradient at a 4-byte aligned address.
+__device__ __forceinline__ void red_add3(float *dst, float a, float b, float c)
 {
-    const int32_t *fp = p.faces + (int64_t)b * p.faces_bs + 3 * (int64_t)(face < 0 ? 0 : face);
-    const float Bk[3] = {B0, B1, (1.0f - B0) - B1};
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        // key: vertex index within this batch element; distinct negative keys for idle lanes.
-        // same_elem keeps lanes of different batch elements apart (a warp straddles two
-        // elements only when H*W is not a multiple of 32).
-        int vi = face >= 0 ? __ldg(fp + k) : -1 - (int)(threadIdx.x & 31);
-        float v[3 + (NCOL > 0 ? NCOL : 1)];
-        v[0] = gx * Bk[k]; v[1] = gy * Bk[k]; v[2] = gw * Bk[k];
-#pragma unroll
-        for (int c = 0; c < NCOL; ++c) v[3 + c] = gcol[c] * Bk[k];
-        bool leader = peer_reduce(vi, same_elem, v);
-        if (leader && face >= 0) {
-            if (v[0] != 0.0f || v[1] != 0.0f || v[2] != 0.0f) {
-                float4 *dst = reinterpret_cast<float4 *>(p.grad_vertices + (int64_t)b * p.grad_vertices_bs) + vi;
-                atomicAdd(dst, make_float4(v[0], v[1], 0.0f, v[2]));
-            }
-            if (NCOL > 0) {
-                float *dc = p.grad_vertex_colors + (int64_t)b * p.grad_vertex_colors_bs + (int64_t)vi * C;
-#pragma unroll
-                for (int c = 0; c < NCOL; ++c) atomicAdd(dc + c, v[3 + c]);
-            }
-        }
-    }
-    (void)C;
-}
-
-// Generic-channel colour scatter (C not 1 or 3): plain atomics, no aggregation.
-__device__ __forceinline__ void scatter_colors_generic(const BwdParams &p, int b, int face, float B0, float B1,
-                                                       const float *g, int C)
-{
-    const int32_t *fp = p.faces + (int64_t)b * p.faces_bs + 3 * (int64_t)face;
-    const float Bk[3] = {B0, B1, (1.0f - B0) - B1};
-    for (int k = 0; k < 3; ++k) {
-        float *dc = p.grad_vertex_colors + (int64_t)b * p.grad_vertex_colors_bs + (int64_t)__ldg(fp + k) * C;
-        for (int c = 0; c < C; ++c) atomicAdd(dc + c, g[c] * Bk[k]);
+    if ((reinterpret_cast<uintptr_t>(dst) & 7u) == 0) {
+        atomicAdd(reinterpret_cast<float2 *>(dst), make_float2(a, b));
+        atomicAdd(dst + 2, c);
+    } else {
+        atomicAdd(dst, a);
+        atomicAdd(reinterpret_cast<float2 *>(dst + 1), make_float2(b, c));
     }
 }
 
 template <int C>
-__global__ void __launch_bounds__(256) k_grad_assemble(BwdParams p)
+__global__ void __launch_bounds__(kBT * kBT) k_grad_assemble(BwdParams p)
 {
+    constexpr int CS = C > 0 ? C : kMaxC;
     const int CC = C > 0 ? C : p.C;
-    const long long npix = (long long)p.H * p.W, total = npix * p.B;
-    const long long total_padded = (total + 31) & ~31ll;     // whole warps stay in the loop together
-    const float4 *gbuf = reinterpret_cast<const float4 *>(p.gbuffer);
-    const float halfW = 0.5f * (float)p.W, halfH = 0.5f * (float)p.H;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total_padded;
-         i += (long long)gridDim.x * blockDim.x) {
-        const bool live = i < total;
-        const int b = live ? (int)(i / npix) : 0;
-        const long long o = live ? i - (long long)b * npix : 0;
-        const int r = (int)(o / p.W), x = (int)(o - (long long)r * p.W);
-        const long long base = (long long)b * npix;
+    __shared__ float s_px[CS][kBR * kBR];
+    __shared__ int s_fid[kBR * kBR];
+    __shared__ float s_zw[kBR * kBR];
+    __shared__ float s_in[2][3][kBT * kBT];
 
-        int fself = -1;
-        float4 gb = make_float4(0.f, 0.f, 1.f, 1.f);
-        float g[C > 0 ? C : 16];
+    const int tid = threadIdx.x;
+    // a warp is an 8x4 pixel block: better odds that its lanes share faces than a 32x1 strip
+    const int warp = tid >> 5, lane = tid & 31;
+    const int lx = (warp & 1) * 8 + (lane & 7), ly = (warp >> 1) * 4 + (lane >> 3);
+    const int W = p.W, H = p.H;
+    const int x = (int)blockIdx.x * kBI - 1 + lx, r = (int)blockIdx.y * kBI - 1 + ly;
+    const float halfW = 0.5f * (float)W, halfH = 0.5f * (float)H;
+    const float4 *gbuf_all = reinterpret_cast<const float4 *>(p.gbuffer);
+
+    for (int b = blockIdx.z; b < p.B; b += gridDim.z) {
+        const size_t base = (size_t)b * H * W;
+        const float *img = p.pixels + base * CC;
+        // ---- phase 0: stage the 18x18 neighbourhood (replicated at the image border) --------
+        for (int i = tid; i < kBR * kBR; i += kBT * kBT) {
+            const int ry = i / kBR, rx = i - ry * kBR;
+            const int gx = (int)blockIdx.x * kBI - 2 + rx, gy = (int)blockIdx.y * kBI - 2 + ry;
+            const bool in = gx >= 0 && gx < W && gy >= 0 && gy < H;
+            const int cx = min(max(gx, 0), W - 1), cy = min(max(gy, 0), H - 1);
+            const size_t o = (size_t)cy * W + cx;
+            for (int c = 0; c < CC; ++c) s_px[c][i] = __ldg(img + o * CC + c);
+            const int f = in ? __ldg(p.face_id + base + o) : -1;
+            s_fid[i] = f;
+            s_zw[i] = f >= 0 ? __ldg(&gbuf_all[base + o].w) : 2.0f;
+        }
+        __syncthreads();
+
+        // ---- phase 1: Sobel response, owners, inbox -----------------------------------------
+        const bool valid = x >= 0 && x < W && r >= 0 && r < H;
+        const bool interior = valid && lx >= 1 && lx <= kBI && ly >= 1 && ly <= kBI;
+        const int ri = (ly + 1) * kBR + (lx + 1);               // own position in the staged region
+        const size_t o = valid ? (size_t)r * W + x : 0;
+        const int fself = s_fid[ri];
+        float g[CS];
         float sx = 0.f, sr = 0.f;
-        if (live) {
-            fself = __ldg(p.face_id + i);
-            if (fself >= 0) gb = __ldg(gbuf + i);
-            const float *gp = p.grad_pixels + i * CC;
-            for (int c = 0; c < CC; ++c) g[c] = __ldg(gp + c);
-            // (1) background: exact
-            if (p.grad_background) {
-                float *gbg = p.grad_background + i * CC;
-                for (int c = 0; c < CC; ++c) gbg[c] = fself < 0 ? g[c] : 0.0f;
-            }
-            // (2) Sobel response of `pixels`, replicate border
-            const int xm = max(x - 1, 0), xp = min(x + 1, p.W - 1), rm = max(r - 1, 0), rp = min(r + 1, p.H - 1);
-            const float *img = p.pixels + base * CC;
+        if (valid) {
+            const float *gp = p.grad_pixels + (base + o) * CC;
             for (int c = 0; c < CC; ++c) {
-#define PX(rr, xx) __ldg(img + ((long long)(rr) * p.W + (xx)) * CC + c)
-                float dx = ((PX(rm, xp) - PX(rm, xm)) + 2.0f * (PX(r, xp) - PX(r, xm)) + (PX(rp, xp) - PX(rp, xm))) * 0.125f;
-                float dr = ((PX(rp, xm) - PX(rm, xm)) + 2.0f * (PX(rp, x) - PX(rm, x)) + (PX(rp, xp) - PX(rm, xp))) * 0.125f;
-#undef PX
+                g[c] = __ldg(gp + c);
+                const float *q = &s_px[c][ri];
+                // rows go down the image: q[-kBR] is the row above
+                const float dx = ((q[-kBR + 1] - q[-kBR - 1]) + 2.0f * (q[1] - q[-1]) + (q[kBR + 1] - q[kBR - 1])) * 0.125f;
+                const float dr = ((q[kBR - 1] - q[-kBR - 1]) + 2.0f * (q[kBR] - q[-kBR]) + (q[kBR + 1] - q[-kBR + 1])) * 0.125f;
                 sx += g[c] * finite_or_zero(dx);
                 sr += g[c] * finite_or_zero(dr);
             }
-        } else {
-            for (int c = 0; c < CC; ++c) g[c] = 0.f;
+            if (interior && p.grad_background) {
+                float *gbg = p.grad_background + (base + o) * CC;
+                for (int c = 0; c < CC; ++c) gbg[c] = fself < 0 ? g[c] : 0.0f;       // exact
+            }
         }
-
-        // (3) owners of the x- and row-direction changes
-        long long ox = -1, orow = -1;
-        if (live && sx != 0.0f)
-            ox = pick_owner(p.face_id + base, gbuf + base, o, fself, gb.w, x > 0 ? o - 1 : -1, x < p.W - 1 ? o + 1 : -1);
-        if (live && sr != 0.0f)
-            orow = pick_owner(p.face_id + base, gbuf + base, o, fself, gb.w, r > 0 ? o - p.W : -1, r < p.H - 1 ? o + p.W : -1);
-
-        // position-gradient coefficients (GRADIENT_SPEC 4): d/dx_clip, d/dy_clip, d/dw_clip per unit B_k
-        float self_gx = 0.f, self_gy = 0.f, self_gw = 0.f;
-        int xface = -1, yface = -1;
-        float4 xg = gb, yg = gb;
-        float x_gx = 0.f, x_gw = 0.f, y_gy = 0.f, y_gw = 0.f;
-        if (ox >= 0) {
-            const float4 og = ox == o ? gb : __ldg(gbuf + base + ox);
-            const int oxx = (int)(ox % p.W);
-            const float xn = ((float)oxx + 0.5f) / halfW - 1.0f;
-            const float a = sx * halfW / og.z;
-            if (ox == o) { self_gx = -a; self_gw += a * xn; }
-            else { xface = __ldg(p.face_id + base + ox); xg = og; x_gx = -a; x_gw = a * xn; }
+        {
+            const float zs = s_zw[ri];
+            const int ox = sx != 0.0f ? pick_owner(fself, zs, s_fid[ri - 1], s_zw[ri - 1], s_fid[ri + 1], s_zw[ri + 1]) : 0;
+            const int oy = sr != 0.0f ? pick_owner(fself, zs, s_fid[ri - kBR], s_zw[ri - kBR], s_fid[ri + kBR], s_zw[ri + kBR]) : 0;
+            const int li = ly * kBT + lx;
+            // candidate c = this pixel + d, d in {-1, 0, +1}; this pixel is sender slot 1 - d of c
+            if (lx > 0) s_in[0][2][li - 1] = ox == 1 ? sx : 0.0f;
+            s_in[0][1][li] = ox == 2 ? sx : 0.0f;
+            if (lx < kBT - 1) s_in[0][0][li + 1] = ox == 3 ? sx : 0.0f;
+            if (ly > 0) s_in[1][2][li - kBT] = oy == 1 ? sr : 0.0f;
+            s_in[1][1][li] = oy == 2 ? sr : 0.0f;
+            if (ly < kBT - 1) s_in[1][0][li + kBT] = oy == 3 ? sr : 0.0f;
         }
-        if (orow >= 0) {
-            const float4 og = orow == o ? gb : __ldg(gbuf + base + orow);
-            const int orr = (int)(orow / p.W);
-            const float yn = ((float)(p.H - 1 - orr) + 0.5f) / halfH - 1.0f;
-            const float a = sr * halfH / og.z;
-            if (orow == o) { self_gy = a; self_gw += -a * yn; }
-            else { yface = __ldg(p.face_id + base + orow); yg = og; y_gy = a; y_gw = -a * yn; }
-        }
+        __syncthreads();
 
-        // (4) scatter: own face (colours + own position part), then the occluders' faces
-        const unsigned same_elem = __match_any_sync(kFull, b);
+        // ---- phase 2: one scatter per covered interior pixel, summed per face across the warp --
+        const bool act = interior && fself >= 0;
+        float B0 = 0.f, B1 = 0.f, gxv = 0.f, gyv = 0.f, gwv = 0.f;
+        if (act) {
+            const int li = ly * kBT + lx;
+            const float4 gb = __ldg(gbuf_all + base + o);
+            B0 = gb.x; B1 = gb.y;
+            const float totx = (s_in[0][0][li] + s_in[0][1][li]) + s_in[0][2][li];
+            const float toty = (s_in[1][0][li] + s_in[1][1][li]) + s_in[1][2][li];
+            // GRADIENT_SPEC 4: a clip-space shift of the surface point by dx moves it by
+            // dx * W / (2 w) pixels; +y_clip moves it UP, towards smaller rows
+            const float xn = ((float)x + 0.5f) / halfW - 1.0f;
+            const float yn = ((float)(H - 1 - r) + 0.5f) / halfH - 1.0f;
+            const float ax = totx * halfW / gb.z, ay = toty * halfH / gb.z;
+            gxv = -ax; gyv = ay; gwv = ax * xn - ay * yn;
+        }
+        const unsigned peers = __match_any_sync(kFull, act ? fself : -1 - lane);
+        const float B2 = (1.0f - B0) - B1;
+        const int32_t *fp = p.faces + (int64_t)b * p.faces_bs + 3 * (int64_t)(act ? fself : 0);
+        float4 *gv = reinterpret_cast<float4 *>(p.grad_vertices + (int64_t)b * p.grad_vertices_bs);
+        float *gc = p.grad_vertex_colors + (int64_t)b * p.grad_vertex_colors_bs;
         if (C == 1 || C == 3) {
-            scatter_face<(C > 0 ? C : 1)>(p, b, same_elem, fself, gb.x, gb.y, self_gx, self_gy, self_gw, g, CC);
+            constexpr int NQ = 3 + (C > 0 ? C : 1);
+            float v[3 * NQ];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const float bk = k == 0 ? B0 : (k == 1 ? B1 : B2);
+                v[k * NQ] = gxv * bk; v[k * NQ + 1] = gyv * bk; v[k * NQ + 2] = gwv * bk;
+#pragma unroll
+                for (int c = 0; c < NQ - 3; ++c) v[k * NQ + 3 + c] = act ? g[c] * bk : 0.0f;
+            }
+            const bool leader = peer_reduce(peers, v);
+            if (leader && act) {
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    const int vi = __ldg(fp + k);
+                    if (v[k * NQ] != 0.0f || v[k * NQ + 1] != 0.0f || v[k * NQ + 2] != 0.0f)
+                        atomicAdd(gv + vi, make_float4(v[k * NQ], v[k * NQ + 1], 0.0f, v[k * NQ + 2]));
+                    if (C == 3) red_add3(gc + (int64_t)vi * 3, v[k * NQ + 3], v[k * NQ + 4], v[k * NQ + 5]);
+                    else atomicAdd(gc + vi, v[k * NQ + 3]);
+                }
+            }
         } else {
-            if (fself >= 0) scatter_colors_generic(p, b, fself, gb.x, gb.y, g, CC);
-            scatter_face<0>(p, b, same_elem, fself, gb.x, gb.y, self_gx, self_gy, self_gw, nullptr, CC);
+            float v[9];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const float bk = k == 0 ? B0 : (k == 1 ? B1 : B2);
+                v[k * 3] = gxv * bk; v[k * 3 + 1] = gyv * bk; v[k * 3 + 2] = gwv * bk;
+            }
+            const bool leader = peer_reduce(peers, v);
+            if (act) {
+                for (int k = 0; k < 3; ++k) {
+                    const int vi = __ldg(fp + k);
+                    const float bk = k == 0 ? B0 : (k == 1 ? B1 : B2);
+                    if (leader && (v[k * 3] != 0.0f || v[k * 3 + 1] != 0.0f || v[k * 3 + 2] != 0.0f))
+                        atomicAdd(gv + vi, make_float4(v[k * 3], v[k * 3 + 1], 0.0f, v[k * 3 + 2]));
+                    for (int c = 0; c < CC; ++c) atomicAdd(gc + (int64_t)vi * CC + c, g[c] * bk);
+                }
+            }
         }
-        if (__any_sync(kFull, xface >= 0))
-            scatter_face<0>(p, b, same_elem, xface, xg.x, xg.y, x_gx, 0.f, x_gw, nullptr, CC);
-        if (__any_sync(kFull, yface >= 0))
-            scatter_face<0>(p, b, same_elem, yface, yg.x, yg.y, 0.f, y_gy, y_gw, nullptr, CC);
+        __syncthreads();        // the staged region is about to be overwritten
     }
 }
 
@@ -212,16 +230,20 @@ cudaError_t launch_backward(const BwdParams &p, int sm_count, cudaStream_t strea
     if ((e = cudaMemsetAsync(p.grad_vertices, 0, nbv * p.V * 4 * sizeof(float), stream)) != cudaSuccess) return e;
     if ((e = cudaMemsetAsync(p.grad_vertex_colors, 0, nbc * p.V * p.C * sizeof(float), stream)) != cudaSuccess) return e;
     tm.end(kStageGradClear, stream);
-    const long long total = (long long)p.B * p.H * p.W;
-    if (total == 0) return cudaSuccess;
-    long long g = (total + 255) / 256;
+    if ((long long)p.B * p.H * p.W == 0) return cudaSuccess;
+    // each CTA walks several batch elements: tiles are small, and a grid of ~32 CTAs per SM is
+    // enough to balance without paying a block launch per 196 pixels
+    const long long tiles = (long long)((p.W + kBI - 1) / kBI) * ((p.H + kBI - 1) / kBI);
+    long long gz = ((long long)sm_count * 32 + tiles - 1) / tiles;
+    if (gz > p.B) gz = p.B;
+    if (gz > 65535) gz = 65535;
+    if (gz < 1) gz = 1;
+    const dim3 grid((p.W + kBI - 1) / kBI, (p.H + kBI - 1) / kBI, (unsigned)gz);
     tm.begin(kStageGradAssemble, stream);
-    const long long cap = (long long)sm_count * 64;
-    if (g > cap) g = cap;
     switch (p.C) {
-        case 1: k_grad_assemble<1><<<(int)g, 256, 0, stream>>>(p); break;
-        case 3: k_grad_assemble<3><<<(int)g, 256, 0, stream>>>(p); break;
-        default: k_grad_assemble<0><<<(int)g, 256, 0, stream>>>(p); break;
+        case 1: k_grad_assemble<1><<<grid, kBT * kBT, 0, stream>>>(p); break;
+        case 3: k_grad_assemble<3><<<grid, kBT * kBT, 0, stream>>>(p); break;
+        default: k_grad_assemble<0><<<grid, kBT * kBT, 0, stream>>>(p); break;
     }
     tm.end(kStageGradAssemble, stream);
     *launches += 1;

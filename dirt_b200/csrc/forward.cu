@@ -186,21 +186,53 @@ __global__ void __launch_bounds__(kTileThreads) k_tile_raster(FwdParams p)
     if (in_image && best < orig) *keyp = best;
 }
 
-// S4: one thread per pixel.
+// Barycentrics of pixel (px, py) on a face that went through the clipper (rare): finds the
+// fan triangle that owns the pixel (exactly one does) and folds the fan weights back onto the
+// face's own corners.
+static __device__ __noinline__ void resolve_clipped(const FwdParams &p, int b, int i0, int i1, int i2, int px, int py,
+                                                    float &B0, float &B1, float &wc)
+{
+    const float4 *vp = vertex_ptr(p.vertices, p.vertices_bs, b);
+    const float4 va = __ldg(vp + i0), vb = __ldg(vp + i1), vc = __ldg(vp + i2);
+    ClipVert poly[6];
+    const int n = clip_face(va, vb, vc, poly);
+    TriSetup t;
+    for (int s = 1; s + 1 < n; ++s) {
+        if (!setup_fan(poly, s, p.W, p.H, t)) continue;
+        if (px < t.xmin || px > t.xmax || py < t.ymin || py > t.ymax) continue;
+        long long e0, e1, e2;
+        edge_values(t, px, py, e0, e1, e2);
+        if (!covered(t, e0, e1, e2)) continue;
+        float l0, l1, l2, b0, b1, b2;
+        screen_bary(t, e0, e1, e2, l0, l1, l2);
+        perspective_weights(t, l0, l1, l2, b0, b1, b2, wc);
+        const ClipVert &q0 = poly[0], &q1 = poly[s], &q2 = poly[s + 1];
+        B0 = fadd(fadd(fmul(b0, q0.b0), fmul(b1, q1.b0)), fmul(b2, q2.b0));
+        B1 = fadd(fadd(fmul(b0, q0.b1), fmul(b1, q1.b1)), fmul(b2, q2.b1));
+        return;
+    }
+}
+
+constexpr int kResolvePix = 8;
+
+// S4: one thread per pixel (kResolvePix of them in turn); blockIdx.y walks the batch.
 template <int C>
 __global__ void __launch_bounds__(256) k_resolve(FwdParams p)
 {
-    const size_t npix = (size_t)p.H * p.W, total = npix * p.B;
-    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
-        const int b = (int)(i / npix);
-        const size_t o = i - (size_t)b * npix;
-        const int row = (int)(o / p.W), px = (int)(o - (size_t)row * p.W), py = p.H - 1 - row;
-        const int CC = C > 0 ? C : p.C;
+    const int CC = C > 0 ? C : p.C;
+    const int npix = p.H * p.W;
+    // kResolvePix pixels per thread: a CTA that resolves only 256 pixels is launch-rate bound
+    for (int j = 0; j < kResolvePix; ++j)
+    for (int b = blockIdx.y; b < p.B; b += gridDim.y) {
+        const int o = (int)((blockIdx.x * kResolvePix + j) * blockDim.x + threadIdx.x);
+        if (o >= npix) break;
+        const int row = o / p.W, px = o - row * p.W, py = p.H - 1 - row;
+        const size_t i = (size_t)b * npix + o;
         float *out = p.pixels + i * CC;
         const unsigned long long key = p.keys[i];
         if (key == kKeyEmpty) {
             // the reference never clears the colour buffer: background shows through
-            const float *bg = p.background + (int64_t)b * p.background_bs + o * CC;
+            const float *bg = p.background + (int64_t)b * p.background_bs + (size_t)o * CC;
             for (int c = 0; c < CC; ++c) out[c] = __ldg(bg + c);
             if (p.face_id) {
                 p.face_id[i] = -1;
@@ -211,50 +243,39 @@ __global__ void __launch_bounds__(256) k_resolve(FwdParams p)
         const int f = (int)(uint32_t)(key & 0xFFFFFFFFull);
         const int32_t *fp = p.faces + (int64_t)b * p.faces_bs + 3 * (int64_t)f;
         const int i0 = __ldg(fp), i1 = __ldg(fp + 1), i2 = __ldg(fp + 2);
-        float B0 = 0.f, B1 = 0.f, wc = 1.f, zw = 1.f;
-        TriSetup t;
         const int4 *pp = proj_ptr(p, b);
-        bool slow;
-        if (setup_from_proj(__ldg(pp + i0), __ldg(pp + i1), __ldg(pp + i2), p.W, p.H, t, slow)) {
+        const int4 ra = __ldg(pp + i0), rb = __ldg(pp + i1), rc = __ldg(pp + i2);
+        float B0 = 0.f, B1 = 0.f, wc = 1.f;
+        if (ra.x != kProjSlow && rb.x != kProjSlow && rc.x != kProjSlow) {
+            // the pixel is known to be covered: only the sign and 1/area of the setup are needed
+            TriSetup t;
+            t.X0 = ra.x; t.Y0 = ra.y; t.rw0 = __int_as_float(ra.w);
+            t.X1 = rb.x; t.Y1 = rb.y; t.rw1 = __int_as_float(rb.w);
+            t.X2 = rc.x; t.Y2 = rc.y; t.rw2 = __int_as_float(rc.w);
+            const long long area2 = orient2d(t.X0, t.Y0, t.X1, t.Y1, t.X2, t.Y2);
+            t.sign = area2 > 0 ? 1 : -1;
+            t.rcp_area = fdiv(1.0f, __ll2float_rn(area2 > 0 ? area2 : -area2));
             long long e0, e1, e2;
             edge_values(t, px, py, e0, e1, e2);
             float l0, l1, l2, b2;
             screen_bary(t, e0, e1, e2, l0, l1, l2);
-            zw = sample_depth(t, px, py);
             perspective_weights(t, l0, l1, l2, B0, B1, b2, wc);
-        } else if (slow) {
-            // clipped face: find the fan triangle that owns this pixel (exactly one does)
-            const float4 *vp = vertex_ptr(p.vertices, p.vertices_bs, b);
-            const float4 va = __ldg(vp + i0), vb = __ldg(vp + i1), vc = __ldg(vp + i2);
-            ClipVert poly[6];
-            int n = clip_face(va, vb, vc, poly);
-            for (int s = 1; s + 1 < n; ++s) {
-                if (!setup_fan(poly, s, p.W, p.H, t)) continue;
-                if (px < t.xmin || px > t.xmax || py < t.ymin || py > t.ymax) continue;
-                long long e0, e1, e2;
-                edge_values(t, px, py, e0, e1, e2);
-                if (!covered(t, e0, e1, e2)) continue;
-                float l0, l1, l2, b0, b1, b2;
-                screen_bary(t, e0, e1, e2, l0, l1, l2);
-                zw = sample_depth(t, px, py);
-                perspective_weights(t, l0, l1, l2, b0, b1, b2, wc);
-                const ClipVert &q0 = poly[0], &q1 = poly[s], &q2 = poly[s + 1];
-                B0 = fadd(fadd(fmul(b0, q0.b0), fmul(b1, q1.b0)), fmul(b2, q2.b0));
-                B1 = fadd(fadd(fmul(b0, q0.b1), fmul(b1, q1.b1)), fmul(b2, q2.b1));
-                break;
-            }
+        } else {
+            resolve_clipped(p, b, i0, i1, i2, px, py, B0, B1, wc);
         }
         const float *cp = p.vertex_colors + (int64_t)b * p.vertex_colors_bs;
         const float *c0 = cp + (int64_t)i0 * CC, *c1 = cp + (int64_t)i1 * CC, *c2 = cp + (int64_t)i2 * CC;
         for (int c = 0; c < CC; ++c) {
             // smooth varying (csrc/shaders.cpp:23,29), arranged so constant colours are exact
-            float k2 = __ldg(c2 + c);
-            float t0 = fsub(__ldg(c0 + c), k2), t1 = fsub(__ldg(c1 + c), k2);
+            const float k2 = __ldg(c2 + c);
+            const float t0 = fsub(__ldg(c0 + c), k2), t1 = fsub(__ldg(c1 + c), k2);
             out[c] = fadd(fadd(k2, fmul(B0, t0)), fmul(B1, t1));
         }
         if (p.face_id) {
             p.face_id[i] = f;
-            reinterpret_cast<float4 *>(p.gbuffer)[i] = make_float4(B0, B1, wc, zw);
+            // 4th component: the window depth as the 24-bit depth buffer holds it
+            const float zq = fmul(__uint2float_rn((uint32_t)(key >> 32)), kDepthScaleInv);
+            reinterpret_cast<float4 *>(p.gbuffer)[i] = make_float4(B0, B1, wc, zq);
         }
     }
 }
@@ -298,7 +319,7 @@ cudaError_t launch_forward(const FwdParams &p, int sm_count, cudaStream_t stream
         tm.end(kStageTileRaster, stream);
         *launches += 6;
     }
-    const int g = grid_for((long long)npix_total, 256, sm_count, 64);
+    const dim3 g((unsigned)(((long long)p.H * p.W + 256 * kResolvePix - 1) / (256 * kResolvePix)), (unsigned)(p.B < 65535 ? p.B : 65535));
     tm.begin(kStageResolve, stream);
     switch (p.C) {
         case 1: k_resolve<1><<<g, 256, 0, stream>>>(p); break;

@@ -22,6 +22,7 @@ constexpr int kSubpixHalf = kSubpix / 2;
 constexpr float kGuardPx = 2097152.0f;        // 2^21 px clamp on window coordinates
 constexpr uint32_t kDepthMax = 16777215u;     // 2^24 - 1 (GL_DEPTH24_STENCIL8, rasterise_egl.cpp:248)
 constexpr unsigned long long kKeyEmpty = 0xFFFFFFFFFFFFFFFFull;
+constexpr float kDepthScaleInv = 1.0f / 16777215.0f;   // depth24 -> [0, 1]; the product is individually rounded
 
 __device__ __forceinline__ float fadd(float a, float b) { return __fadd_rn(a, b); }
 __device__ __forceinline__ float fsub(float a, float b) { return __fsub_rn(a, b); }

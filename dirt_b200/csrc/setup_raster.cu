@@ -25,6 +25,7 @@ namespace dirt {
 
 constexpr unsigned kFullMask = 0xFFFFFFFFu;
 constexpr int kWarpsPerCta = 8;
+constexpr float kLineRcpAreaMin = 1.0f / (2.0f * 65536.0f * 1024.0f);   // 1 / |2 area| of a 1024 px triangle: fatter ones go to the tile path
 
 // ---------------------------------------------------------------------------------------
 // S0b: vertex projection
@@ -187,7 +188,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) k_setup(FwdParams p)
                 if (setup_from_proj(__ldg(pp + i0), __ldg(pp + i1), __ldg(pp + i2), p.W, p.H, t, slow)) {
                     const int ex = max(t.X0, max(t.X1, t.X2)) - min(t.X0, min(t.X1, t.X2));
                     const int ey = max(t.Y0, max(t.Y1, t.Y2)) - min(t.Y0, min(t.Y1, t.Y2));
-                    if (ex < kSmallExtent && ey < kSmallExtent)
+                    // few-but-fat triangles are better off pixel-parallel in the tile path
+                    if (ex < kSmallExtent && ey < kSmallExtent && (t.rcp_area > kLineRcpAreaMin || (t.xmax - t.xmin + 1) * (t.ymax - t.ymin + 1) <= 256))
                         nlines = write_record(recs + lane * kRecWords, t, (uint32_t)f, (uint32_t)b);
                     else
                         push_big(t, b, (uint32_t)f, 0u, p);

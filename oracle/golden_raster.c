@@ -299,7 +299,9 @@ static void forward_element(int H, int W, int C, int V, int F,
                     if (k < key[o]) {
                         key[o] = k;
                         samp[4 * o + 0] = sm.B0; samp[4 * o + 1] = sm.B1;
-                        samp[4 * o + 2] = sm.w_clip; samp[4 * o + 3] = sm.zw;
+                        samp[4 * o + 2] = sm.w_clip;
+                        /* the window depth as the 24-bit depth buffer holds it */
+                        samp[4 * o + 3] = (float)d * (1.0f / 16777215.0f);
                     }
                 }
         }
