@@ -8,7 +8,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libdirt_b200.so")
+# DIRT_B200_LIB selects an alternative build of the same library (kernel tuning experiments)
+LIB_PATH = os.environ.get("DIRT_B200_LIB") or os.path.join(_HERE, "libdirt_b200.so")
 
 STATUS_NAMES = {0: "OK", -1: "INVALID_ARGUMENT", -2: "CUDA_ERROR", -3: "WORKSPACE_TOO_SMALL", -4: "UNSUPPORTED"}
 MAX_CHANNELS = 16

@@ -25,6 +25,14 @@ namespace dirt {
 
 constexpr unsigned kFullMask = 0xFFFFFFFFu;
 constexpr int kWarpsPerCta = 8;
+#ifndef KCTAS
+#define KCTAS 6
+#endif
+#ifndef KFRAG
+#define KFRAG 4
+#endif
+constexpr int kCtasPerSm = KCTAS;                     // the kernel waits on depth loads: occupancy over registers
+constexpr int kFragRound = KFRAG;                     // spans are 1-2 pixels on 3 lines out of 4 (profiles/r1_setup_notes.md)
 constexpr float kLineRcpAreaMin = 1.0f / (2.0f * 65536.0f * 1024.0f);   // 1 / |2 area| of a 1024 px triangle: fatter ones go to the tile path
 
 // ---------------------------------------------------------------------------------------
@@ -141,16 +149,16 @@ __device__ __forceinline__ void sample_line(const uint32_t *rec, int j, const Fw
     unsigned long long *kp = p.keys + ((size_t)rec[rELEM] * p.H + (size_t)(p.H - 1 - py0)) * p.W + px0;
     const long long stride = axis ? -(long long)p.W : 1ll;
     float fi = __int2float_rn(lo);
-    // Four fragments per round: their current depths are fetched together (independent loads),
-    // so a line pays the memory latency once per four fragments instead of once per fragment.
-    for (int i = lo; i <= hi; i += 4) {
+    // kFragRound fragments per round: their current depths are fetched together (independent
+    // loads), so a line pays the memory latency once per round instead of once per fragment.
+    for (int i = lo; i <= hi; i += kFragRound) {
         const int n = hi - i + 1;
-        uint32_t cur[4];
+        uint32_t cur[kFragRound];
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
+        for (int u = 0; u < kFragRound; ++u)
             cur[u] = u < n ? load_depth_word(kp + u * stride) : 0u;
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
+        for (int u = 0; u < kFragRound; ++u) {
             if (u < n) {
                 float zw = axis ? fadd(c1, fmul(dzdy, fi)) : fadd(fadd(zref, fmul(dzdx, fi)), c2);
                 zw = fminf(fmaxf(zw, 0.0f), 1.0f);
@@ -162,11 +170,30 @@ __device__ __forceinline__ void sample_line(const uint32_t *rec, int j, const Fw
                 fi += 1.0f;
             }
         }
-        kp += 4 * stride;
+        kp += kFragRound * stride;
     }
 }
 
-__global__ void __launch_bounds__(kWarpsPerCta * 32) k_setup(FwdParams p)
+// Rare path: a corner of the face is outside the depth range or behind the eye.  Clips the
+// face and samples the fan triangles serially / via the large-triangle list.
+static __device__ __noinline__ void setup_clipped(const FwdParams &p, int b, int f, int i0, int i1, int i2)
+{
+    const float4 *vp = vertex_ptr(p.vertices, p.vertices_bs, b);
+    const float4 va = __ldg(vp + i0), vb = __ldg(vp + i1), vc = __ldg(vp + i2);
+    if (classify_face(va, vb, vc) != 2) return;
+    ClipVert poly[6];
+    const int n = clip_face(va, vb, vc, poly);
+    TriSetup t;
+    for (int s = 1; s + 1 < n; ++s) {
+        if (!setup_fan(poly, s, p.W, p.H, t)) continue;
+        if ((t.xmax - t.xmin + 1) * (t.ymax - t.ymin + 1) <= 64)
+            raster_serial(t, (uint32_t)f, p.keys + (size_t)b * p.H * p.W, p.W, p.H, t.xmin, t.xmax, t.ymin, t.ymax);
+        else
+            push_big(t, b, (uint32_t)f, (uint32_t)s, p);
+    }
+}
+
+__global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdParams p)
 {
     __shared__ uint32_t s_recs[kWarpsPerCta][32 * kRecWords];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -194,20 +221,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32) k_setup(FwdParams p)
                     else
                         push_big(t, b, (uint32_t)f, 0u, p);
                 } else if (slow) {
-                    // rare: a corner is outside the depth range or behind the eye
-                    const float4 *vp = vertex_ptr(p.vertices, p.vertices_bs, b);
-                    const float4 va = __ldg(vp + i0), vb = __ldg(vp + i1), vc = __ldg(vp + i2);
-                    if (classify_face(va, vb, vc) == 2) {
-                        ClipVert poly[6];
-                        const int n = clip_face(va, vb, vc, poly);
-                        for (int s = 1; s + 1 < n; ++s) {
-                            if (!setup_fan(poly, s, p.W, p.H, t)) continue;
-                            if ((t.xmax - t.xmin + 1) * (t.ymax - t.ymin + 1) <= 64)
-                                raster_serial(t, (uint32_t)f, p.keys + (size_t)b * p.H * p.W, p.W, p.H, t.xmin, t.xmax, t.ymin, t.ymax);
-                            else
-                                push_big(t, b, (uint32_t)f, (uint32_t)s, p);
-                        }
-                    }
+                    setup_clipped(p, b, f, i0, i1, i2);
                 }
             }
         }
