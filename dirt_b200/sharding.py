@@ -1,0 +1,79 @@
+"""Multi-GPU host logic for the rasterise path: one process per GPU, batch elements sharded
+across ranks, and -- only when the mesh is shared by all elements -- one packed allreduce of the
+vertex / colour gradients.
+
+The reference's multi-GPU story is independent per-device ops (tests/multi_gpu_test.py:22-29;
+per-CUcontext state csrc/gl_dispatcher.h:27, :101-108): batch elements never interact
+(csrc/rasterise_egl.cpp:440-458), so the forward needs no collective at all.  For an inverse-
+rendering loop over frames of one mesh (tests/optimize_sequence.py:293-352) every rank holds
+gradients w.r.t. the same [V,*] arrays; they are summed with a single torch.distributed
+all_reduce over one contiguous [V, 4+C] buffer (NCCL over NVLink on GPUs, gloo in the CPU tests).
+Nothing here touches pixels: torch.distributed is plumbing, the kernels are libdirt_b200.so.
+"""
+import torch
+import torch.distributed as dist
+
+
+def shard_range(batch, rank, world):
+    """Contiguous shard [lo, hi) of `batch` elements for `rank` of `world`; sizes differ by at
+    most one and earlier ranks take the larger shards."""
+    if world <= 0 or not (0 <= rank < world):
+        raise ValueError("rank %r out of range for world size %r" % (rank, world))
+    base, extra = divmod(int(batch), world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def shard_batch(tensors, rank, world):
+    """Slices every tensor of `tensors` (dict or sequence) on dim 0 to this rank's shard.  A leading
+    dim of 1 is a broadcast input (shared mesh / shared background) and is passed through."""
+    items = tensors.items() if isinstance(tensors, dict) else enumerate(tensors)
+    batch = max(int(t.shape[0]) for _, t in items)
+    lo, hi = shard_range(batch, rank, world)
+    cut = lambda t: t if t.shape[0] == 1 and batch > 1 else t[lo:hi]
+    if isinstance(tensors, dict):
+        return {k: cut(t) for k, t in tensors.items()}
+    return type(tensors)(cut(t) for t in tensors)
+
+
+def pack_shared_gradients(grad_vertices, grad_vertex_colors):
+    """[1|.,V,4] + [1|.,V,C] -> one contiguous [V, 4+C] buffer (summing a leading batch dim)."""
+    gv = grad_vertices.reshape(-1, grad_vertices.shape[-2], 4).sum(0)
+    gc = grad_vertex_colors.reshape(-1, grad_vertex_colors.shape[-2], grad_vertex_colors.shape[-1]).sum(0)
+    return torch.cat([gv, gc], dim=1).contiguous()
+
+
+def allreduce_shared_gradients(grad_vertices, grad_vertex_colors, group=None, async_op=False):
+    """Sums the shared-mesh gradients over all ranks with ONE collective.
+    Returns (grad_vertices [V,4], grad_vertex_colors [V,C]) -- or, with async_op=True,
+    (work, finish) where finish() waits and returns that pair, so the collective can overlap
+    whatever the caller still has to do (e.g. the grad_background copy)."""
+    packed = pack_shared_gradients(grad_vertices, grad_vertex_colors)
+    world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+
+    def split():
+        return packed[:, :4].contiguous(), packed[:, 4:].contiguous()
+
+    if world == 1:
+        return (None, split) if async_op else split()
+    work = dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
+    if async_op:
+        def finish():
+            work.wait()
+            return split()
+        return work, finish
+    return split()
+
+
+def rasterise_batch_sharded(background, vertices, vertex_colors, faces, rank=None, world=None):
+    """`rasterise_batch` on this rank's shard of the batch (no collective; outputs stay sharded,
+    as the reference's per-device graphs do).  Returns (pixels_shard, (lo, hi))."""
+    from . import rasterise_ops
+    if rank is None:
+        rank = dist.get_rank() if dist.is_initialized() else 0
+    if world is None:
+        world = dist.get_world_size() if dist.is_initialized() else 1
+    batch = max(int(t.shape[0]) for t in (background, vertices, vertex_colors, faces))
+    lo, hi = shard_range(batch, rank, world)
+    bg, v, c, f = shard_batch((background, vertices, vertex_colors, faces), rank, world)
+    return rasterise_ops.rasterise_batch(bg, v, c, f), (lo, hi)

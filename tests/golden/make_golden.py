@@ -1,0 +1,53 @@
+"""Writes the committed golden fixtures tests/golden/*.npz.
+
+    python tests/golden/make_golden.py
+
+Two kinds of fixture:
+  kat1.npz, kat2.npz    ANALYTIC expectations of the reference's own known-answer cases
+                        (README.md:46-70 / README.md:104, tests/multi_gpu_test.py:8-17): inputs
+                        and the expected image, written down from the reference text -- these
+                        pin the oracle AND the CUDA path to the reference.
+  cylinder.npz, cube.npz, clip.npz
+                        outputs of the oracle (oracle/golden_raster.c) on the reference's
+                        deterministic scenes that store no expectation (tests/rasterise_tests.py:
+                        11-89, samples/simple.py:15-74) and on a near-plane-crossing scene.
+                        The reference cannot run here (no TensorFlow, no GL), so these are
+                        regression pins of the written spec (docs/RASTER_SPEC.md,
+                        docs/GRADIENT_SPEC.md), not reference outputs; parity of attribute values
+                        and gradients with the reference stays "unpinned".
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path[:0] = [ROOT, os.path.join(ROOT, "tests")]
+import scenes  # noqa: E402
+from oracle import golden  # noqa: E402
+
+
+def oracle_case(sc, seed):
+    px, fid, gb = golden.forward(sc["background"], sc["vertices"], sc["vertex_colors"], sc["faces"])
+    g = np.random.RandomState(seed).randn(*px.shape).astype(np.float32)
+    gv, gc, gbg = golden.backward(sc["faces"], px, g, fid, gb, sc["vertices"].shape[1])
+    out = {k: v for k, v in sc.items() if k != "expected"}
+    out.update(pixels=px, face_id=fid, gbuffer=gb, grad_pixels=g, grad_vertices=gv, grad_vertex_colors=gc,
+               grad_background=gbg)
+    return out
+
+
+def main():
+    for name, sc in (("kat1", scenes.kat1_square()), ("kat2", scenes.kat2_square())):
+        np.savez_compressed(os.path.join(HERE, name + ".npz"), **sc)
+    np.savez_compressed(os.path.join(HERE, "cylinder.npz"), **oracle_case(scenes.cylinder(), 0))
+    np.savez_compressed(os.path.join(HERE, "cube.npz"), **oracle_case(scenes.cube(B=2, H=64, W=64), 1))
+    np.savez_compressed(os.path.join(HERE, "clip.npz"), **oracle_case(scenes.near_crossing(B=1, H=48, W=64), 2))
+    for f in sorted(os.listdir(HERE)):
+        if f.endswith(".npz"):
+            print(f, os.path.getsize(os.path.join(HERE, f)), "bytes")
+
+
+if __name__ == "__main__":
+    main()
