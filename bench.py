@@ -40,20 +40,29 @@ WORKLOADS = {
     "c4": dict(B=256, H=256, W=256, C=3, n_lat=224, n_lon=224,
                desc="B=256 per GPU, 256x256x3, sphere F=99,904"),
     "small": dict(B=4, H=128, W=128, C=3, n_lat=48, n_lon=48, desc="debug size"),
+    # config c5: one heightfield mesh shared by all frames; vertex / colour gradients are folded to
+    # the shared arrays and (N > 1) summed with one packed NCCL allreduce
+    "c5": dict(B=4, H=1024, W=1024, C=3, hill_n=708, shared=True,
+               desc="4 frames per GPU, 1024x1024x3, shared hill heightfield F=999,698 V=501,264, grads allreduced"),
+    "c5small": dict(B=2, H=256, W=256, C=3, hill_n=96, shared=True, desc="debug size of c5"),
 }
 
 
 def build_scene(wl, B, seed_shift=0):
     import scenes
+    if wl.get("shared"):
+        return scenes.hill(B, wl["H"], wl["W"], wl["C"], n=wl["hill_n"], seed=seed_shift)
     return scenes.sphere(B, wl["H"], wl["W"], wl["C"], wl["n_lat"], wl["n_lon"],
                          seeds=(1, 2 + seed_shift, 3 + seed_shift, 4 + seed_shift))
 
 
-def algorithmic_bytes(B, H, W, C, V, F):
+def algorithmic_bytes(B, H, W, C, V, F, shared=False):
     """BASELINE.md section 3 / SURVEY.md 8(d): every input read once, every output written once;
-    aux buffers and workspace not counted.  Returns per-kernel and total figures."""
+    aux buffers and workspace not counted.  Returns per-kernel and total figures.  `shared`:
+    faces and colours are broadcast over the batch (multiplicity 1), vertices are per frame."""
     img = 4 * B * H * W * C
-    mesh_v, mesh_c, mesh_f = 16 * B * V, 4 * C * B * V, 12 * B * F
+    mc = 1 if shared else B
+    mesh_v, mesh_c, mesh_f = 16 * B * V, 4 * C * mc * V, 12 * mc * F
     per_kernel = {
         "setup": mesh_v + mesh_f,                       # vertices + faces read once
         "resolve": 2 * img + mesh_c,                    # background read, pixels written, colours read
@@ -119,7 +128,7 @@ def cpu_baseline_run(wl, target_seconds, threads=None):
     threads = threads or min(golden.max_threads(), os.cpu_count() or 1)
     H, W = wl["H"], wl["W"]
     # calibrate on `threads` elements, then size the sample for ~target_seconds
-    nb = threads
+    nb = threads if not wl.get("shared") else min(threads, wl["B"])
     sc = build_scene(wl, nb)
     g = np.random.RandomState(0).randn(nb, H, W, wl["C"]).astype(np.float32)
     V = sc["vertices"].shape[1]
@@ -127,7 +136,7 @@ def cpu_baseline_run(wl, target_seconds, threads=None):
     def once(sc, g):
         t0 = time.perf_counter()
         px, fid, gb = golden.forward(sc["background"], sc["vertices"], sc["vertex_colors"], sc["faces"], threads=threads)
-        golden.backward(sc["faces"], px, g, fid, gb, V, threads=threads)
+        golden.backward(sc["faces"], px, g, fid, gb, V, shared_colors=bool(wl.get("shared")), threads=threads)
         return time.perf_counter() - t0
 
     t = once(sc, g)
@@ -150,8 +159,11 @@ def hbm_peak():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def ncu_traffic(kernel):
-    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture, or None."""
+def ncu_traffic(kernel, workload):
+    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture of the headline
+    workload (profiles/roofline_traffic.json, written by tools/ncu_summary.py), or None."""
+    if workload != "headline":
+        return None
     try:
         with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
             return json.load(f).get(kernel)
@@ -201,7 +213,15 @@ def run_ours(args, wl, rank, world, local_rank):
     lib = _lib.load()
 
     B, H, W, C = wl["B"], wl["H"], wl["W"], wl["C"]
-    sc = build_scene(wl, B, seed_shift=10 * rank)
+    shared = bool(wl.get("shared"))
+    sc = build_scene(wl, B, seed_shift=0 if shared else 10 * rank)     # a shared mesh is the same on every rank
+    if shared:
+        # each rank renders its own frames of the camera path
+        from dirt_b200 import sharding
+        full = build_scene(wl, B * world)
+        lo, hi = sharding.shard_range(B * world, rank, world)
+        sc = {k: (v if k in ("faces", "vertex_colors", "world") else v[lo:hi]) for k, v in full.items()}
+        del full
     V, F = sc["vertices"].shape[1], sc["faces"].shape[1]
     host = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for k, v in sc.items()}
     host["target"] = torch.from_numpy(np.random.RandomState(7 + rank).uniform(0, 1, (B, H, W, C)).astype(np.float32)).pin_memory()
@@ -210,7 +230,14 @@ def run_ours(args, wl, rank, world, local_rank):
 
     def step():
         px, fid, gb = ops.forward_raw(d["background"], d["vertices"], d["vertex_colors"], d["faces"], want_aux=True)
-        return ops.backward_raw(d["faces"], px, grad_pixels, fid, gb, V)
+        if not shared:
+            return ops.backward_raw(d["faces"], px, grad_pixels, fid, gb, V)
+        # shared mesh: colour gradients are summed over the frames by the kernel (stride 0); the
+        # clip-space vertex gradients are folded to world space with each frame's matrix, then
+        # ONE packed allreduce sums vertex + colour gradients over the ranks
+        gv, gc, gbg = ops.backward_raw(d["faces"], px, grad_pixels, fid, gb, V, shared_colors=True)
+        gworld = torch.einsum("bvj,bij->vi", gv, d["matrices"])
+        return sharding.allreduce_shared_gradients(gworld, gc)
 
     def barrier():
         if world > 1:
@@ -253,20 +280,20 @@ def run_ours(args, wl, rank, world, local_rank):
         _lib.check(lib.dirt_profile_collect())
     _lib.check(lib.dirt_profile_enable(0))
     stages = {k: (ms / n if n else 0.0) for k, (ms, n) in _lib.stage_times().items()}
-    per_kernel, fwd_bytes, bwd_bytes = algorithmic_bytes(B, H, W, C, V, F)
+    per_kernel, fwd_bytes, bwd_bytes = algorithmic_bytes(B, H, W, C, V, F, shared)
     dominant = max(per_kernel, key=lambda k: stages.get(k, 0.0))
     peak, peak_src = hbm_peak()
     achieved = per_kernel[dominant] / (stages[dominant] * 1e-3) / 1e9 if stages[dominant] > 0 else 0.0
     roofline = {"bound": "hbm", "kernel": "k_" + dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": ncu_traffic("k_" + dominant), "peak_source": peak_src,
+                "frac": achieved / peak, "traffic": ncu_traffic("k_" + dominant, args.workload), "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": per_kernel[dominant], "kernel_ms": stages[dominant],
                 "step_algorithmic_bytes": fwd_bytes + bwd_bytes,
                 "step_achieved_GBps": (fwd_bytes + bwd_bytes) / (ms_step * 1e-3) / 1e9,
                 "step_frac": (fwd_bytes + bwd_bytes) / (ms_step * 1e-3) / 1e9 / peak}
 
     # ---- e2e: public API, pinned host inputs, H2D + D2H inside the timed region -------------
-    out_gv = torch.empty((B, V, 4), dtype=torch.float32).pin_memory()
-    out_gc = torch.empty((B, V, C), dtype=torch.float32).pin_memory()
+    out_gv = torch.empty((1 if shared else B, V, 4), dtype=torch.float32).pin_memory()
+    out_gc = torch.empty((1 if shared else B, V, C), dtype=torch.float32).pin_memory()
 
     def e2e_step():
         bg = host["background"].to(dev, non_blocking=True).requires_grad_(True)
@@ -277,8 +304,13 @@ def run_ours(args, wl, rank, world, local_rank):
         px = dirt_b200.rasterise_batch(bg, v, c, f)
         loss = 0.5 * ((px - tgt) ** 2).sum()
         loss.backward()
-        out_gv.copy_(v.grad, non_blocking=True)
-        out_gc.copy_(c.grad, non_blocking=True)
+        if shared:
+            gw, gcs = sharding.allreduce_shared_gradients(torch.einsum("bvj,bij->vi", v.grad, d["matrices"]), c.grad)
+            out_gv[0].copy_(gw, non_blocking=True)
+            out_gc[0].copy_(gcs, non_blocking=True)
+        else:
+            out_gv.copy_(v.grad, non_blocking=True)
+            out_gc.copy_(c.grad, non_blocking=True)
         return float(loss.item())          # D2H of the scalar; also a stream sync
 
     e2e_steps = max(1, min(args.steps, 5))
@@ -310,7 +342,9 @@ def run_ours(args, wl, rank, world, local_rank):
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": args.workload + ": " + wl["desc"], "batch_per_gpu": B, "height": H, "width": W, "channels": C,
-                   "vertices": V, "faces": F, "sharding": "batch elements across ranks, no data-path collective",
+                   "vertices": V, "faces": F,
+                   "sharding": ("frames across ranks; one packed all_reduce of [V,4+C] shared-mesh gradients per step" if shared
+                                else "batch elements across ranks, no data-path collective"),
                    "l2": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2; no explicit flush" % ((fwd_bytes + bwd_bytes) / 1e6)},
         "roofline": roofline, "stages_ms": stages, "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": int(launches),
         "clocks": clock_info}))

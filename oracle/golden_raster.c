@@ -515,7 +515,7 @@ int golden_rasterise_backward(int B, int H, int W, int C, int V, int F,
 int golden_num_threads(void)
 {
 #ifdef _OPENMP
-    return omp_get_max_threads();
+    return omp_get_num_procs();      /* not omp_get_max_threads(): torchrun exports OMP_NUM_THREADS=1 */
 #else
     return 1;
 #endif

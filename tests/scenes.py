@@ -215,3 +215,51 @@ def near_crossing(B=2, H=96, W=128, C=3, seed=5):
     cols = rng.uniform(0, 1, size=(B, len(verts), C))
     bg = rng.uniform(0, 1, size=(B, H, W, C))
     return _pack(bg, vs, cols, np.broadcast_to(faces, (B,) + faces.shape))
+
+
+def _value_noise(x, z, seed=0, octaves=5):
+    """Fractal value noise in [0, 1] (the kind of terrain function the fork's hill shader uses,
+    csrc/shaders.cpp:188-269, restated with numpy's generator -- not the shader's hash)."""
+    rng = np.random.RandomState(seed)
+    table = rng.uniform(0, 1, size=(256, 256))
+    out = np.zeros_like(x, dtype=np.float64)
+    amp, freq, norm = 0.5, 0.25, 0.0
+    for _ in range(octaves):
+        xs, zs = x * freq, z * freq
+        x0, z0 = np.floor(xs).astype(np.int64), np.floor(zs).astype(np.int64)
+        fx, fz = xs - x0, zs - z0
+        fx, fz = fx * fx * (3 - 2 * fx), fz * fz * (3 - 2 * fz)
+        t = lambda i, j: table[i & 255, j & 255]
+        v = (t(x0, z0) * (1 - fx) + t(x0 + 1, z0) * fx) * (1 - fz) + (t(x0, z0 + 1) * (1 - fx) + t(x0 + 1, z0 + 1) * fx) * fz
+        out += amp * v
+        norm += amp
+        amp *= 0.5
+        freq *= 2.0
+    return out / norm
+
+
+def hill(B, H, W, C=3, n=708, seed=0):
+    """Config c5: one heightfield mesh shared by B frames on a smooth camera path
+    (SURVEY.md 8(d)): n x n vertices over x in [-14, 14], z in [-25, -5] (the camera looks along
+    -z, dirt/matrices.py:86-116), height = noise * 10.3 - 6.1 (csrc/shaders.cpp:222-236); pinhole
+    focal 0.85 W (csrc/shaders.cpp:469-471).  n = 708 gives V = 501,264, F = 999,698.
+    faces and vertex_colors have batch dim 1 (broadcast); returns also `world` [V,4] and
+    `matrices` [B,4,4] so that clip-space vertex gradients can be folded back to world space."""
+    xs, zs = np.meshgrid(np.linspace(-14, 14, n), np.linspace(-25, -5, n), indexing="ij")
+    h = _value_noise(xs + 40.0, zs + 40.0, seed) * 10.3 - 6.1
+    world = np.stack([xs, h * 0.35 - 1.0, zs, np.ones_like(xs)], -1).reshape(-1, 4)
+    i, j = np.meshgrid(np.arange(n - 1), np.arange(n - 1), indexing="ij")
+    a, b_, c, d = i * n + j, i * n + j + 1, (i + 1) * n + j, (i + 1) * n + j + 1
+    faces = np.concatenate([np.stack([a, b_, c], -1).reshape(-1, 3), np.stack([b_, d, c], -1).reshape(-1, 3)], 0)
+    near = 0.1
+    P = perspective_projection(near, 60., near * 0.5 / 0.85, H / W)
+    Ms = np.stack([pad_3x3_to_4x4(rodrigues([0.0, 0.02 * (b - B / 2.0), 0.0])) @ translation([0.05 * b, -1.5, 0.0]) @ P
+                   for b in range(B)])
+    vs = np.einsum("vi,bij->bvj", world, Ms)
+    rng = np.random.RandomState(seed + 1)
+    cols = rng.uniform(0, 1, size=(1, len(world), C))
+    bg = rng.uniform(0, 1, size=(B, H, W, C))
+    sc = _pack(bg, vs, cols, faces[None])
+    sc["world"] = world.astype(np.float32)
+    sc["matrices"] = Ms.astype(np.float32)
+    return sc

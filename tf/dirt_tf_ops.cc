@@ -1,0 +1,146 @@
+// dirt_tf_ops.cc -- TensorFlow shim: re-registers ops "Rasterise" and "RasteriseGrad" on top of
+// libdirt_b200.so's C ABI (include/dirt_b200.h), with the attrs / input order / output of the
+// reference registration (csrc/rasterise_egl.cpp:33-53, :520; csrc/rasterise_grad_egl.cpp:33-53),
+// so that `tf.load_op_library` in dirt/rasterise_ops.py:6-7 keeps working unchanged.
+//
+// NOT BUILT OR TESTED IN THIS REPOSITORY: the build image has no TensorFlow headers.  It is kept
+// paper-thin (shape checks are done by the C ABI; this file only unpacks tensors) so that the
+// torch-driven tests cover everything but this glue.  Build (on a machine with TF):
+//   g++ -std=c++17 -shared -fPIC tf/dirt_tf_ops.cc -Iinclude $(python -c "import tensorflow as tf; \
+//       print(' '.join(tf.sysconfig.get_compile_flags() + tf.sysconfig.get_link_flags()))") \
+//       -Ldirt_b200 -ldirt_b200 -o librasterise.so
+#include "tensorflow/core/framework/op.h"
+#include "tensorflow/core/framework/op_kernel.h"
+#include "tensorflow/core/framework/shape_inference.h"
+#include "tensorflow/core/common_runtime/gpu/gpu_event_mgr.h"
+#include "tensorflow/core/platform/stream_executor.h"
+
+#include "dirt_b200.h"
+
+using namespace tensorflow;
+
+namespace {
+
+Status status_from(int rc)
+{
+    if (rc == DIRT_STATUS_OK) return Status::OK();
+    if (rc == DIRT_STATUS_INVALID_ARGUMENT) return errors::InvalidArgument(dirt_last_error());
+    return errors::Internal(dirt_last_error());
+}
+
+void *cuda_stream_of(OpKernelContext *ctx)
+{
+    // the reference takes TF's compute stream the same way (csrc/rasterise_egl.cpp:359-361)
+    return *reinterpret_cast<void **>(ctx->op_device_context()->stream()->implementation()->GpuStreamMemberHack());
+}
+
+DirtShape shape_of(const Tensor &background, const Tensor &vertices, const Tensor &faces, int channels)
+{
+    DirtShape s;
+    s.batch = static_cast<int32_t>(vertices.dim_size(0));
+    s.height = static_cast<int32_t>(background.dim_size(1));
+    s.width = static_cast<int32_t>(background.dim_size(2));
+    s.channels = channels;
+    s.vertex_count = static_cast<int32_t>(vertices.dim_size(1));
+    s.face_count = static_cast<int32_t>(faces.dim_size(1));
+    return s;
+}
+
+}  // namespace
+
+// Same registration as csrc/rasterise_egl.cpp:33-53, plus two optional outputs the gradient needs.
+REGISTER_OP("Rasterise")
+    .Attr("height: int").Attr("width: int").Attr("channels: int = 3")
+    .Input("background: float32").Input("vertices: float32").Input("vertex_colors: float32")
+    .Input("faces: int32").Input("camera_pos: float32")
+    .Output("pixels: float32").Output("face_id: int32").Output("gbuffer: float32")
+    .SetShapeFn([](shape_inference::InferenceContext *c) {
+        int h, w, ch;
+        TF_RETURN_IF_ERROR(c->GetAttr("height", &h));
+        TF_RETURN_IF_ERROR(c->GetAttr("width", &w));
+        TF_RETURN_IF_ERROR(c->GetAttr("channels", &ch));
+        auto b = c->Dim(c->input(1), 0);
+        c->set_output(0, c->MakeShape({b, h, w, ch}));
+        c->set_output(1, c->MakeShape({b, h, w}));
+        c->set_output(2, c->MakeShape({b, h, w, 4}));
+        return Status::OK();
+    });
+
+class RasteriseOpB200 : public OpKernel {
+public:
+    explicit RasteriseOpB200(OpKernelConstruction *c) : OpKernel(c)
+    {
+        OP_REQUIRES_OK(c, c->GetAttr("height", &height_));
+        OP_REQUIRES_OK(c, c->GetAttr("width", &width_));
+        OP_REQUIRES_OK(c, c->GetAttr("channels", &channels_));
+    }
+    void Compute(OpKernelContext *ctx) override
+    {
+        const Tensor &bg = ctx->input(0), &v = ctx->input(1), &col = ctx->input(2), &f = ctx->input(3);
+        // rank checks of csrc/rasterise_egl.cpp:310-321 (the C ABI re-checks extents and strides)
+        OP_REQUIRES(ctx, bg.dims() == 4 && bg.dim_size(1) == height_ && bg.dim_size(2) == width_ && bg.dim_size(3) == channels_,
+                    errors::InvalidArgument("Rasterise expects background_tensor to be 4D, and bgcolor.shape == [None, height, width, channels]"));
+        OP_REQUIRES(ctx, v.dims() == 3 && v.dim_size(2) == 4, errors::InvalidArgument("Rasterise expects vertices to be 3D, and vertices.shape[2] == 4"));
+        OP_REQUIRES(ctx, col.dims() == 3 && col.dim_size(1) == v.dim_size(1) && col.dim_size(2) == channels_,
+                    errors::InvalidArgument("Rasterise expects vertex_colors to be 3D, and vertex_colors.shape == [None, vertices.shape[1], channels]"));
+        OP_REQUIRES(ctx, f.dims() == 3 && f.dim_size(2) == 3, errors::InvalidArgument("Rasterise expects faces to be 3D, and faces.shape[2] == 3"));
+        DirtForwardArgs a = {};
+        a.shape = shape_of(bg, v, f, channels_);
+        const int64 B = a.shape.batch;
+        auto stride = [B](const Tensor &t) -> int64_t { return t.dim_size(0) == 1 && B > 1 ? 0 : t.NumElements() / std::max<int64>(t.dim_size(0), 1); };
+        a.background = bg.flat<float>().data();        a.background_bstride = stride(bg);
+        a.vertices = v.flat<float>().data();           a.vertices_bstride = stride(v);
+        a.vertex_colors = col.flat<float>().data();    a.vertex_colors_bstride = stride(col);
+        a.faces = f.flat<int32>().data();              a.faces_bstride = stride(f);
+        Tensor *pixels, *face_id, *gbuffer, ws;
+        OP_REQUIRES_OK(ctx, ctx->allocate_output(0, {B, height_, width_, channels_}, &pixels));
+        OP_REQUIRES_OK(ctx, ctx->allocate_output(1, {B, height_, width_}, &face_id));
+        OP_REQUIRES_OK(ctx, ctx->allocate_output(2, {B, height_, width_, 4}, &gbuffer));
+        a.workspace_bytes = dirt_workspace_bytes(&a.shape);
+        OP_REQUIRES_OK(ctx, ctx->allocate_temp(DT_UINT8, {static_cast<int64>(a.workspace_bytes)}, &ws));
+        a.pixels = pixels->flat<float>().data();
+        a.face_id = face_id->flat<int32>().data();
+        a.gbuffer = gbuffer->flat<float>().data();
+        a.workspace = ws.flat<uint8>().data();
+        OP_REQUIRES_OK(ctx, status_from(dirt_rasterise_forward(&a, cuda_stream_of(ctx))));
+    }
+private:
+    int height_, width_, channels_;
+};
+REGISTER_KERNEL_BUILDER(Name("Rasterise").Device(DEVICE_GPU), RasteriseOpB200);   // GPU only, as csrc/rasterise_egl.cpp:520
+
+// The intended backward (csrc/rasterise_grad_common.h:19-24): G-buffer + pixels + grad_pixels in,
+// grad_vertices / grad_vertex_colors / grad_background out.
+REGISTER_OP("RasteriseGrad")
+    .Input("faces: int32").Input("pixels: float32").Input("grad_pixels: float32")
+    .Input("face_id: int32").Input("gbuffer: float32").Input("vertices: float32")
+    .Output("grad_background: float32").Output("grad_vertices: float32").Output("grad_vertex_colors: float32");
+
+class RasteriseGradOpB200 : public OpKernel {
+public:
+    using OpKernel::OpKernel;
+    void Compute(OpKernelContext *ctx) override
+    {
+        const Tensor &f = ctx->input(0), &px = ctx->input(1), &g = ctx->input(2), &fid = ctx->input(3), &gb = ctx->input(4),
+                     &v = ctx->input(5);
+        OP_REQUIRES(ctx, px.dims() == 4 && g.shape() == px.shape(), errors::InvalidArgument("RasteriseGrad expects pixels and grad_pixels of one 4D shape"));
+        DirtBackwardArgs a = {};
+        a.shape = shape_of(px, v, f, static_cast<int>(px.dim_size(3)));
+        a.shape.batch = static_cast<int32_t>(px.dim_size(0));
+        const int64 B = a.shape.batch, V = a.shape.vertex_count, C = a.shape.channels;
+        a.faces = f.flat<int32>().data();
+        a.faces_bstride = f.dim_size(0) == 1 && B > 1 ? 0 : int64_t(a.shape.face_count) * 3;
+        a.pixels = px.flat<float>().data(); a.grad_pixels = g.flat<float>().data();
+        a.face_id = fid.flat<int32>().data(); a.gbuffer = gb.flat<float>().data();
+        const int64 Bv = v.dim_size(0);            // 1 = shared mesh: gradients summed over the batch
+        Tensor *gbg, *gv, *gc;
+        OP_REQUIRES_OK(ctx, ctx->allocate_output(0, px.shape(), &gbg));
+        OP_REQUIRES_OK(ctx, ctx->allocate_output(1, {Bv, V, 4}, &gv));
+        OP_REQUIRES_OK(ctx, ctx->allocate_output(2, {Bv, V, C}, &gc));
+        a.grad_background = gbg->flat<float>().data();
+        a.grad_vertices = gv->flat<float>().data();            a.grad_vertices_bstride = Bv == 1 && B > 1 ? 0 : V * 4;
+        a.grad_vertex_colors = gc->flat<float>().data();       a.grad_vertex_colors_bstride = Bv == 1 && B > 1 ? 0 : V * C;
+        OP_REQUIRES_OK(ctx, status_from(dirt_rasterise_backward(&a, cuda_stream_of(ctx))));
+    }
+};
+REGISTER_KERNEL_BUILDER(Name("RasteriseGrad").Device(DEVICE_GPU), RasteriseGradOpB200);
