@@ -53,6 +53,8 @@ EXPORTS = {
     "dirt_rasterise_forward_host": (ctypes.c_int, [ctypes.POINTER(DirtForwardArgs)]),
     "dirt_rasterise_backward_host": (ctypes.c_int, [ctypes.POINTER(DirtBackwardArgs)]),
     "dirt_release_host_staging": (ctypes.c_int, []),
+    "dirt_dilate_silhouette": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p] + [ctypes.c_int] * 4 + [ctypes.c_void_p]),
+    "dirt_dilate_silhouette_grad": (ctypes.c_int, [ctypes.c_void_p] * 3 + [ctypes.c_int] * 4 + [ctypes.c_void_p]),
     "dirt_kernel_launch_count": (ctypes.c_uint64, []),
     "dirt_profile_enable": (ctypes.c_int, [ctypes.c_int]),
     "dirt_profile_collect": (ctypes.c_int, []),

@@ -221,6 +221,31 @@ int dirt_rasterise_backward(const DirtBackwardArgs *a, void *stream)
     return DIRT_STATUS_OK;
 }
 
+int dirt_dilate_silhouette(const float *x, float *out, int batch, int height, int width, int channels, void *stream)
+{
+    if (batch < 0 || height <= 0 || width <= 0 || channels <= 0) return fail(DIRT_STATUS_INVALID_ARGUMENT, "dilate: bad shape");
+    if (batch == 0) return DIRT_STATUS_OK;
+    if (!x || !out) return fail(DIRT_STATUS_INVALID_ARGUMENT, "dilate: null pointer");
+    int sms = 0, rc;
+    if ((rc = current_sm_count(&sms))) return rc;
+    cudaError_t e = dirt::launch_dilate(x, out, batch, height, width, channels, sms, static_cast<cudaStream_t>(stream));
+    g_launches += 1;
+    return e == cudaSuccess ? DIRT_STATUS_OK : cuda_fail(e, "dilate launch");
+}
+
+int dirt_dilate_silhouette_grad(const float *x, const float *grad_out, float *grad_x, int batch, int height, int width,
+                                int channels, void *stream)
+{
+    if (batch < 0 || height <= 0 || width <= 0 || channels <= 0) return fail(DIRT_STATUS_INVALID_ARGUMENT, "dilate: bad shape");
+    if (batch == 0) return DIRT_STATUS_OK;
+    if (!x || !grad_out || !grad_x) return fail(DIRT_STATUS_INVALID_ARGUMENT, "dilate: null pointer");
+    int sms = 0, rc;
+    if ((rc = current_sm_count(&sms))) return rc;
+    cudaError_t e = dirt::launch_dilate_grad(x, grad_out, grad_x, batch, height, width, channels, sms, static_cast<cudaStream_t>(stream));
+    g_launches += 1;
+    return e == cudaSuccess ? DIRT_STATUS_OK : cuda_fail(e, "dilate grad launch");
+}
+
 int dirt_profile_enable(int enable)
 {
     std::lock_guard<std::mutex> lock(g_prof_mu);

@@ -61,6 +61,9 @@ struct StageTimer {
 };
 
 cudaError_t launch_forward(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_t *launches, StageTimer &tm);
+cudaError_t launch_dilate(const float *x, float *out, int B, int H, int W, int C, int sm_count, cudaStream_t stream);
+cudaError_t launch_dilate_grad(const float *x, const float *grad_out, float *grad_x, int B, int H, int W, int C,
+                               int sm_count, cudaStream_t stream);
 cudaError_t launch_backward(const BwdParams &p, int sm_count, cudaStream_t stream, uint64_t *launches, StageTimer &tm);
 
 }  // namespace dirt

@@ -116,6 +116,14 @@ DIRT_API int dirt_rasterise_forward(const DirtForwardArgs *args, void *stream);
  * carries the name; csrc/rasterise_grad_common.h:13-24 the intended kernels). */
 DIRT_API int dirt_rasterise_backward(const DirtBackwardArgs *args, void *stream);
 
+/* Silhouette dilation of deferred G-buffer channels, fused with its masking: replaces the
+ * framework ops of samples/deferred.py:87-91 (mask = x == -inf; 3x3 SAME max-pool; blend).
+ * x, out, grad_*: [batch, height, width, channels] device fp32.  The backward sends a background
+ * pixel's gradient to the first maximal element (row-major) of its 3x3 window. */
+DIRT_API int dirt_dilate_silhouette(const float *x, float *out, int batch, int height, int width, int channels, void *stream);
+DIRT_API int dirt_dilate_silhouette_grad(const float *x, const float *grad_out, float *grad_x, int batch, int height,
+                                         int width, int channels, void *stream);
+
 /* Host-buffer convenience calls: every pointer in `args` is HOST memory (pinned or pageable);
  * the library stages inputs to the current device, runs the kernels and copies the outputs
  * back, then synchronises.  workspace / workspace_bytes are ignored (library-owned, grow-only,
