@@ -5,5 +5,6 @@ The public names mirror the reference package (`import dirt`): dirt/__init__.py:
 dirt/rasterise_ops.py.
 """
 from .rasterise_ops import rasterise, rasterise_batch, rasterise_grad  # noqa: F401
+from .scene_ops import oceanic_horizon, oceanic_horizon_batch  # noqa: F401
 from .deferred import dilate_silhouette, rasterise_gbuffer  # noqa: F401
 from ._lib import DirtError, InvalidArgumentError  # noqa: F401

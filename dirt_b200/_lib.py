@@ -43,6 +43,14 @@ class DirtBackwardArgs(ctypes.Structure):
                 ("grad_background", _f32p)]
 
 
+class DirtSceneArgs(ctypes.Structure):
+    _fields_ = [("shape", DirtShape),
+                ("background", _f32p), ("background_bstride", _i64),
+                ("vertices", _f32p), ("vertices_bstride", _i64),
+                ("faces", _f32p), ("faces_bstride", _i64),
+                ("face_id", _f32p), ("gbuffer", _f32p), ("camera_pos", _f32p), ("pixels", _f32p)]
+
+
 # every symbol include/dirt_b200.h declares: name -> (restype, argtypes)
 EXPORTS = {
     "dirt_abi_version": (ctypes.c_int, []),
@@ -53,6 +61,7 @@ EXPORTS = {
     "dirt_rasterise_forward_host": (ctypes.c_int, [ctypes.POINTER(DirtForwardArgs)]),
     "dirt_rasterise_backward_host": (ctypes.c_int, [ctypes.POINTER(DirtBackwardArgs)]),
     "dirt_release_host_staging": (ctypes.c_int, []),
+    "dirt_scene_oceanic_horizon": (ctypes.c_int, [ctypes.POINTER(DirtSceneArgs), ctypes.c_void_p]),
     "dirt_dilate_silhouette": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p] + [ctypes.c_int] * 4 + [ctypes.c_void_p]),
     "dirt_dilate_silhouette_grad": (ctypes.c_int, [ctypes.c_void_p] * 3 + [ctypes.c_int] * 4 + [ctypes.c_void_p]),
     "dirt_kernel_launch_count": (ctypes.c_uint64, []),

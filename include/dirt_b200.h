@@ -124,6 +124,24 @@ DIRT_API int dirt_dilate_silhouette(const float *x, float *out, int batch, int h
 DIRT_API int dirt_dilate_silhouette_grad(const float *x, const float *grad_out, float *grad_x, int batch, int height,
                                          int width, int channels, void *stream);
 
+/* Procedural scene stage of the fork's own `Rasterise` op: shaders::oceanic_horizon
+ * (csrc/shaders.cpp:1668-1919) evaluated on every pixel the rasteriser covered.  Call after
+ * dirt_rasterise_forward with face_id / gbuffer requested, on the same stream: covered pixels of
+ * `pixels` are overwritten with (sky mask, sun term, 0); uncovered ones keep the background.
+ * camera_pos: DEVICE pointer to >= 8 floats (cam_x, cam_y, cam_z, ang1, ang2, ang3, time,
+ * light_z -- input 4 of the op, csrc/rasterise_egl.cpp:41, :399-433); no host copy is made. */
+typedef struct DirtSceneArgs {
+    DirtShape shape;
+    const float *background;      int64_t background_bstride;    /* [B,H,W,C]: sample jitter      */
+    const float *vertices;        int64_t vertices_bstride;      /* [B,V,4]                       */
+    const int32_t *faces;         int64_t faces_bstride;         /* [B,F,3]                       */
+    const int32_t *face_id;       /* [B,H,W]   from forward                                       */
+    const float *gbuffer;         /* [B,H,W,4] from forward                                       */
+    const float *camera_pos;      /* device, >= 8 floats                                          */
+    float *pixels;                /* in/out [B,H,W,C]                                             */
+} DirtSceneArgs;
+DIRT_API int dirt_scene_oceanic_horizon(const DirtSceneArgs *args, void *stream);
+
 /* Host-buffer convenience calls: every pointer in `args` is HOST memory (pinned or pageable);
  * the library stages inputs to the current device, runs the kernels and copies the outputs
  * back, then synchronises.  workspace / workspace_bytes are ignored (library-owned, grow-only,

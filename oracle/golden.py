@@ -16,10 +16,17 @@ _SO = os.path.join(_HERE, "_build", "libgolden_raster.so")
 _lib = None
 
 
+_SO_SCENE = os.path.join(_HERE, "_build", "libscene_oceanic.so")
+_scene = None
+
+
 def build(force=False):
-    src = os.path.join(_HERE, "golden_raster.c")
-    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(src):
-        subprocess.check_call(["make", "-s", "-C", _HERE] + (["-B"] if force else []))
+    stale = force
+    for so, src in ((_SO, "golden_raster.c"), (_SO_SCENE, "scene_oceanic.c")):
+        src = os.path.join(_HERE, src)
+        stale = stale or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src)
+    if stale:
+        subprocess.check_call(["make", "-s", "-C", _HERE, "all"] + (["-B"] if force else []))
     return _SO
 
 
@@ -106,3 +113,30 @@ def backward(faces, pixels, grad_pixels, face_id, gbuf, V, shared_vertices=False
     if rc != 0:
         raise RuntimeError("golden_rasterise_backward failed: %d" % rc)
     return gv, gc, gbg
+
+
+def oceanic_horizon(background, vertices, faces, camera_pos, threads=1):
+    """The fork's `Rasterise` output (oracle/scene_oceanic.c): rasterises `vertices` / `faces` over
+    `background` [B,H,W,C] for coverage and the interpolated texCoordV (= clip xy), then evaluates
+    shaders::oceanic_horizon on the covered pixels.  Returns pixels [B,H,W,C]."""
+    global _scene
+    build()
+    if _scene is None:
+        _scene = ctypes.CDLL(_SO_SCENE)
+        vp = ctypes.c_void_p
+        _scene.golden_oceanic_horizon.argtypes = [ctypes.c_int] * 4 + [vp] * 5
+        _scene.golden_oceanic_horizon.restype = ctypes.c_int
+    bg = _prep(background, np.float32, 4, "background")
+    v = _prep(vertices, np.float32, 3, "vertices")
+    B = max(bg.shape[0], v.shape[0])
+    _, H, W, C = bg.shape
+    bgB = np.ascontiguousarray(np.broadcast_to(bg, (B, H, W, C)))
+    tc, fid, _ = forward(np.zeros((B, H, W, 2), np.float32), v, v[..., :2], faces, threads=threads)
+    cam = np.ascontiguousarray(camera_pos, np.float32).reshape(-1)
+    assert cam.size >= 8
+    pixels = bgB.copy()
+    rc = _scene.golden_oceanic_horizon(B, H, W, C, tc.ctypes.data, fid.ctypes.data, bgB.ctypes.data, cam.ctypes.data,
+                                       pixels.ctypes.data)
+    if rc != 0:
+        raise RuntimeError("golden_oceanic_horizon failed: %d" % rc)
+    return pixels
