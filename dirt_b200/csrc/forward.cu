@@ -216,8 +216,11 @@ static __device__ __noinline__ void resolve_clipped(const FwdParams &p, int b, i
 constexpr int kResolvePix = 8;
 
 // S4: one thread per pixel (kResolvePix of them in turn); blockIdx.y walks the batch.
+#ifndef KRES_CTAS
+#define KRES_CTAS 4
+#endif
 template <int C>
-__global__ void __launch_bounds__(256) k_resolve(FwdParams p)
+__global__ void __launch_bounds__(256, KRES_CTAS) k_resolve(FwdParams p)
 {
     const int CC = C > 0 ? C : p.C;
     const int npix = p.H * p.W;

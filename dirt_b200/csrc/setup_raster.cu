@@ -61,21 +61,19 @@ __global__ void __launch_bounds__(256) k_project(FwdParams p, int nbatch)
 // ---------------------------------------------------------------------------------------
 // S1: setup + line-parallel sampling
 // ---------------------------------------------------------------------------------------
-// Shared-memory record of a triangle being sampled by the warp (19-word stride: odd, so lanes
-// reading the same field of different records hit different banks).
-enum {
-    rA = 0,         // 3 x int32: sign-normalised edge value at pixel (xmin, ymin) plus tie bias (inside: >= 0)
-    rSX = 3,        // 3 x int32: edge step per +1 pixel in x
-    rSY = 6,        // 3 x int32: edge step per +1 pixel in y
-    rINV = 9,       // 3 x float: 1 / (edge step along the line), 0 when that step is 0
-    rZREF = 12, rDZDX = 13, rDZDY = 14,
-    rORG = 15,      // xmin | ymin << 16
-    rDIMS = 16,     // (bw - 1) | (bh - 1) << 8 | axis << 16   (axis 1: lines are columns)
-    rFACE = 17, rELEM = 18,
-    kRecWords = 19
-};
+// Shared-memory record of a triangle being sampled by the warp: five 16-byte rows, read with
+// LDS.128 (20-word stride: the 8 lanes of a quarter-warp phase hit disjoint bank groups).
+//   row 0: A0 A1 A2 org      A_k = sign-normalised edge value at line 0, position 0, plus the tie
+//                            bias (inside: >= 0); org = xmin | ymin << 16
+//   row 1: sa0 sa1 sa2 dims  sa_k = edge step per +1 position ALONG a line; dims = m1 | axis << 8
+//                            (m1 = last position of a line; axis 1: lines are columns)
+//   row 2: sc0 sc1 sc2 face  sc_k = edge step per +1 line
+//   row 3: inv0 inv1 inv2 elem   inv_k = 1 / sa_k as float (0 when sa_k == 0)
+//   row 4: zref dzdx dzdy -
+constexpr int kRecWords = 20;
 
 // Fills the record of a triangle whose extents are below kSmallExtent (int32 edge math).
+// Returns the number of lines.
 __device__ __forceinline__ int write_record(uint32_t *rec, const TriSetup &t, uint32_t face, uint32_t elem)
 {
     const int cx = t.xmin * kSubpix + kSubpixHalf, cy = t.ymin * kSubpix + kSubpixHalf;
@@ -85,21 +83,24 @@ __device__ __forceinline__ int write_record(uint32_t *rec, const TriSetup &t, ui
     const int bias[3] = {t.bias0, t.bias1, t.bias2};
     const int bw = t.xmax - t.xmin + 1, bh = t.ymax - t.ymin + 1;
     const int axis = bw > bh ? 1 : 0;
+    uint32_t A[3], sa[3], sc[3], inv[3];
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
         const int ex = bx[k] - ax[k], ey = by[k] - ay[k];
         const int e = (ex * (cy - ay[k]) - ey * (cx - ax[k])) * sg;      // orient2d in int32
         const int sx = -ey * sg * kSubpix, sy = ex * sg * kSubpix;
-        rec[rA + k] = (uint32_t)(e + bias[k]);
-        rec[rSX + k] = (uint32_t)sx;
-        rec[rSY + k] = (uint32_t)sy;
-        const int sa = axis ? sy : sx;
-        rec[rINV + k] = __float_as_uint(sa != 0 ? __frcp_rn((float)sa) : 0.0f);
+        const int along = axis ? sy : sx;
+        A[k] = (uint32_t)(e + bias[k]);
+        sa[k] = (uint32_t)along;
+        sc[k] = (uint32_t)(axis ? sx : sy);
+        inv[k] = __float_as_uint(along != 0 ? __frcp_rn((float)along) : 0.0f);
     }
-    rec[rZREF] = __float_as_uint(t.zref); rec[rDZDX] = __float_as_uint(t.dzdx); rec[rDZDY] = __float_as_uint(t.dzdy);
-    rec[rORG] = (uint32_t)t.xmin | ((uint32_t)t.ymin << 16);
-    rec[rDIMS] = (uint32_t)(bw - 1) | ((uint32_t)(bh - 1) << 8) | ((uint32_t)axis << 16);
-    rec[rFACE] = face; rec[rELEM] = elem;
+    uint4 *row = reinterpret_cast<uint4 *>(rec);
+    row[0] = make_uint4(A[0], A[1], A[2], (uint32_t)t.xmin | ((uint32_t)t.ymin << 16));
+    row[1] = make_uint4(sa[0], sa[1], sa[2], (uint32_t)((axis ? bh : bw) - 1) | ((uint32_t)axis << 8));
+    row[2] = make_uint4(sc[0], sc[1], sc[2], face);
+    row[3] = make_uint4(inv[0], inv[1], inv[2], elem);
+    row[4] = make_uint4(__float_as_uint(t.zref), __float_as_uint(t.dzdx), __float_as_uint(t.dzdy), 0u);
     return axis ? bw : bh;
 }
 
@@ -114,21 +115,24 @@ __device__ __forceinline__ uint32_t load_depth_word(const unsigned long long *kp
 // Samples line `j` of the triangle in `rec` (a row when axis == 0, a column when axis == 1).
 __device__ __forceinline__ void sample_line(const uint32_t *rec, int j, const FwdParams &p)
 {
-    const uint32_t dims = rec[rDIMS], org = rec[rORG];
-    const int axis = (int)(dims >> 16);
-    const int bw1 = (int)(dims & 0xFFu), bh1 = (int)((dims >> 8) & 0xFFu);
-    const int m1 = axis ? bh1 : bw1;                 // last position along the line
+    const uint4 *row = reinterpret_cast<const uint4 *>(rec);
+    const uint4 rA = row[0], rSA = row[1], rSC = row[2], rINV = row[3];
+    const uint32_t org = rA.w, face = rSC.w, elem = rINV.w;
+    const int axis = (int)(rSA.w >> 8), m1 = (int)(rSA.w & 0xFFu);      // m1: last position along the line
+    const int A[3] = {(int)rA.x, (int)rA.y, (int)rA.z}, SA[3] = {(int)rSA.x, (int)rSA.y, (int)rSA.z};
+    const int SC[3] = {(int)rSC.x, (int)rSC.y, (int)rSC.z};
+    const float INV[3] = {__uint_as_float(rINV.x), __uint_as_float(rINV.y), __uint_as_float(rINV.z)};
+    const float fj = __int2float_rn(j), fm = __int2float_rn(m1 + 1);
     int lo = 0, hi = m1;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
-        const int sx = (int)rec[rSX + k], sy = (int)rec[rSY + k];
-        const int sa = axis ? sy : sx, sc = axis ? sx : sy;
-        const int a = (int)rec[rA + k] + sc * j;     // edge value (+ bias) at position 0 of this line
+        const int sa = SA[k];
+        const int a = A[k] + SC[k] * j;              // edge value (+ bias) at position 0 of this line
         // float estimate of the crossing, clamped to the line, then one exact correction step
-        const float q = -__int2float_rn(a) * __uint_as_float(rec[rINV + k]);
+        const float q = -__int2float_rn(a) * INV[k];
         const int dir = (sa > 0) - (sa < 0);
         float qc = sa > 0 ? ceilf(q) : floorf(q);
-        qc = fminf(fmaxf(qc, -1.0f), (float)(m1 + 1));
+        qc = fminf(fmaxf(qc, -1.0f), fm);
         int c = (int)qc;
         const int v = a + sa * c;
         const int asa = sa < 0 ? -sa : sa;
@@ -138,15 +142,14 @@ __device__ __forceinline__ void sample_line(const uint32_t *rec, int j, const Fw
         else if (a < 0) hi = -1;
     }
     if (lo > hi) return;
+    const uint4 rZ = row[4];
     const int xmin = (int)(org & 0xFFFFu), ymin = (int)(org >> 16);
-    const float zref = __uint_as_float(rec[rZREF]), dzdx = __uint_as_float(rec[rDZDX]), dzdy = __uint_as_float(rec[rDZDY]);
-    const uint32_t face = rec[rFACE];
-    const float fj = __int2float_rn(j);
+    const float zref = __uint_as_float(rZ.x), dzdx = __uint_as_float(rZ.y), dzdy = __uint_as_float(rZ.z);
     // zw = (zref + dzdx * dx) + dzdy * dy, the operation order of plane_depth()
     const float c1 = fadd(zref, fmul(dzdx, fj));     // axis 1: dx = j is fixed
     const float c2 = fmul(dzdy, fj);                 // axis 0: dy = j is fixed
     const int px0 = axis ? xmin + j : xmin + lo, py0 = axis ? ymin + lo : ymin + j;
-    unsigned long long *kp = p.keys + ((size_t)rec[rELEM] * p.H + (size_t)(p.H - 1 - py0)) * p.W + px0;
+    unsigned long long *kp = p.keys + ((size_t)elem * p.H + (size_t)(p.H - 1 - py0)) * p.W + px0;
     const long long stride = axis ? -(long long)p.W : 1ll;
     float fi = __int2float_rn(lo);
     // kFragRound fragments per round: their current depths are fetched together (independent
@@ -195,7 +198,7 @@ static __device__ __noinline__ void setup_clipped(const FwdParams &p, int b, int
 
 __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdParams p)
 {
-    __shared__ uint32_t s_recs[kWarpsPerCta][32 * kRecWords];
+    __shared__ __align__(16) uint32_t s_recs[kWarpsPerCta][32 * kRecWords];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t *recs = s_recs[warp];
     const long long total = (long long)p.B * p.F;
