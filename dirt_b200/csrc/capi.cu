@@ -42,7 +42,9 @@ inline size_t align_up(size_t v) { return (v + kAlign - 1) / kAlign * kAlign; }
 
 // Workspace carve-up.  Offsets are a pure function of the shape.
 struct Layout {
-    size_t keys, proj, counters, tile_count, tile_cursor, tile_offset, big, queue, total;
+    size_t keys, proj, counters, tile_count, tile_cursor, bucket_count, tile_offset, big, queue, total;
+    size_t order, bucket_of, pivots, bucket_cursor, bucket_base, hiz, work_next;
+    uint32_t hiz_off[dirt::kHizLevels];
     size_t zero_bytes;
     uint32_t cap_big;
     unsigned long long cap_queue;
@@ -70,11 +72,27 @@ Layout workspace_layout(const DirtShape &s)
     L.counters = off;    off += dirt::kCtrCount * sizeof(uint32_t);
     L.tile_count = off;  off += ntiles * sizeof(uint32_t);
     L.tile_cursor = off; off += ntiles * sizeof(uint32_t);
+    L.bucket_count = off; off += (size_t)dirt::kMaxBuckets * s.batch * sizeof(uint32_t);
+    off = (off + 7) & ~(size_t)7;
+    L.work_next = off;   off += dirt::kMaxBuckets * sizeof(unsigned long long);
     L.zero_bytes = off - L.counters;
     off = align_up(off);
     L.tile_offset = off; off = align_up(off + ntiles * sizeof(uint32_t));
     L.big = off;         off = align_up(off + (size_t)L.cap_big * 16);
     L.queue = off;       off = align_up(off + (size_t)(L.cap_queue + 4) * sizeof(uint32_t));
+    // depth-ordered passes (depth_order.cu)
+    size_t hiz_words = 0;
+    for (int l = 0; l < dirt::kHizLevels; ++l) {
+        const int sh = dirt::kHizLog2 + l;
+        L.hiz_off[l] = (uint32_t)hiz_words;
+        hiz_words += (size_t)s.batch * ((s.width + (1 << sh) - 1) >> sh) * ((s.height + (1 << sh) - 1) >> sh);
+    }
+    L.order = off;         off = align_up(off + nfaces * sizeof(uint32_t));
+    L.bucket_of = off;     off = align_up(off + nfaces);
+    L.pivots = off;        off = align_up(off + (size_t)s.batch * dirt::kMaxBuckets * sizeof(float));
+    L.bucket_cursor = off; off = align_up(off + (size_t)dirt::kMaxBuckets * s.batch * sizeof(uint32_t));
+    L.bucket_base = off;   off = align_up(off + (dirt::kMaxBuckets + 1) * sizeof(uint32_t));
+    L.hiz = off;           off = align_up(off + hiz_words * sizeof(uint32_t));
     L.total = off;
     return L;
 }
@@ -179,6 +197,17 @@ int dirt_rasterise_forward(const DirtForwardArgs *a, void *stream)
     p.big = ws + L.big;
     p.queue = reinterpret_cast<uint32_t *>(ws + L.queue);
     p.cap_big = L.cap_big; p.cap_queue = L.cap_queue; p.zero_bytes = L.zero_bytes;
+    // depth-ordered passes pay off on meshes with real depth complexity; flat face numbers are 32-bit
+    const bool ordered = s.face_count >= dirt::kOrderMinFaces && s.batch <= 65535 && (unsigned long long)s.batch * s.face_count < (1ull << 32);
+    p.order = ordered ? reinterpret_cast<uint32_t *>(ws + L.order) : nullptr;
+    p.bucket_of = reinterpret_cast<uint8_t *>(ws + L.bucket_of);
+    p.pivots = reinterpret_cast<float *>(ws + L.pivots);
+    p.bucket_count = reinterpret_cast<uint32_t *>(ws + L.bucket_count);
+    p.work_next = reinterpret_cast<unsigned long long *>(ws + L.work_next);
+    p.bucket_cursor = reinterpret_cast<uint32_t *>(ws + L.bucket_cursor);
+    p.bucket_base = reinterpret_cast<uint32_t *>(ws + L.bucket_base);
+    p.hiz = reinterpret_cast<uint32_t *>(ws + L.hiz);
+    for (int l = 0; l < dirt::kHizLevels; ++l) p.hiz_off[l] = L.hiz_off[l];
 
     uint64_t n = 0;
     cudaError_t e = dirt::launch_forward(p, sms, static_cast<cudaStream_t>(stream), &n, g_timer);

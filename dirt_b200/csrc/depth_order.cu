@@ -1,0 +1,245 @@
+// depth_order.cu -- front-to-back passes with a hierarchical depth buffer, for meshes with depth
+// complexity (the headline mesh draws ~13 fragments per pixel of which one survives).
+//
+// The result of the forward pass is min over fragments of (depth24 << 32 | face), so the ORDER in
+// which faces are sampled cannot change it.  That freedom is used here: the faces of every
+// element are split into a few depth buckets (nearest first), the buckets are sampled one launch
+// after the other, and between launches the key buffer is reduced to the maximum depth of each
+// 8x8 pixel tile.  A triangle of a later bucket whose smallest possible fragment depth is still
+// greater than that maximum in every tile its bounding box touches cannot win a pixel and is
+// dropped before any of its lines is generated (setup_raster.cu).  The bound is exact for the
+// arithmetic actually used: the plane depth of RASTER_SPEC section 6 is monotone in dx and in dy
+// under round-to-nearest, so its minimum over the bounding box is its value at one corner.
+//
+//   k_depth_pivots    256 evenly spaced sample faces per element, sorted by nearest corner depth
+//                     -> the bucket boundaries of the element (sample quantiles)
+//   k_depth_classify  bucket of every face; faces per (bucket, element)
+//   k_depth_offsets   exclusive scan, bucket-major: bucket k of all elements is one contiguous
+//                     range of `order`, so one launch samples bucket k of the whole batch
+//   k_depth_scatter   flat face numbers into their ranges (order inside a range is arbitrary)
+//   k_hiz_build       maxima of the depth words over 8, 16, 32 and 64 px tiles
+#include <cstdlib>
+#include "forward_common.cuh"
+
+namespace dirt {
+
+namespace {
+
+constexpr unsigned kFull = 0xFFFFFFFFu;
+constexpr int kSamples = 256;
+
+// Nearest corner depth of a face; 0 (first bucket, never culled) for faces on the general path.
+__device__ __forceinline__ float face_near_depth(const FwdParams &p, int b, int f)
+{
+    const int32_t *fp = p.faces + (int64_t)b * p.faces_bs + 3 * (int64_t)f;
+    const int i0 = __ldg(fp), i1 = __ldg(fp + 1), i2 = __ldg(fp + 2);
+    if ((unsigned)i0 >= (unsigned)p.V || (unsigned)i1 >= (unsigned)p.V || (unsigned)i2 >= (unsigned)p.V) return 0.0f;
+    const int4 *pp = proj_ptr(p, b);
+    const int4 a = __ldg(pp + i0), c = __ldg(pp + i1), d = __ldg(pp + i2);
+    if (a.x == kProjSlow || c.x == kProjSlow || d.x == kProjSlow) return 0.0f;
+    return fminf(__int_as_float(a.z), fminf(__int_as_float(c.z), __int_as_float(d.z)));
+}
+
+__global__ void __launch_bounds__(kSamples) k_depth_pivots(FwdParams p, BucketPlan plan)
+{
+    __shared__ float s_z[kSamples];
+    const int b = blockIdx.x, t = threadIdx.x;
+    const int f = (int)(((long long)t * p.F) / kSamples);
+    s_z[t] = face_near_depth(p, b, f);
+    __syncthreads();
+    // bitonic sort, ascending
+    for (int k = 2; k <= kSamples; k <<= 1)
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            const int q = t ^ j;
+            if (q > t) {
+                const float x = s_z[t], y = s_z[q];
+                const bool up = (t & k) == 0;
+                if ((x > y) == up) { s_z[t] = y; s_z[q] = x; }
+            }
+            __syncthreads();
+        }
+    if (t < plan.n - 1) {
+        int at = (int)(plan.upto[t] * kSamples);
+        at = at < 0 ? 0 : (at > kSamples - 1 ? kSamples - 1 : at);
+        p.pivots[b * kMaxBuckets + t] = s_z[at];
+    }
+}
+
+__device__ __forceinline__ int bucket_for(const float *pv, int nb, float z)
+{
+    int k = 0;
+    for (int j = 0; j < nb - 1; ++j) k += z >= pv[j] ? 1 : 0;
+    return k;
+}
+
+constexpr int kChunkFaces = 2048;          // faces of ONE element per CTA in classify / scatter
+
+// blockIdx.y = element, blockIdx.x = chunk of kChunkFaces faces.  Counts go through shared
+// memory: kMaxBuckets global reductions per CTA instead of one per warp and bucket.
+__global__ void __launch_bounds__(256) k_depth_classify(FwdParams p, int nb)
+{
+    __shared__ uint32_t s_cnt[kMaxBuckets];
+    __shared__ float s_pv[kMaxBuckets];
+    const int b = blockIdx.y, t = threadIdx.x;
+    if (t < kMaxBuckets) { s_cnt[t] = 0; s_pv[t] = t < nb - 1 ? p.pivots[b * kMaxBuckets + t] : 0.0f; }
+    __syncthreads();
+    const int f0 = blockIdx.x * kChunkFaces, f1 = min(f0 + kChunkFaces, p.F);
+    for (int f = f0 + t; f < f1; f += 256) {
+        const int k = bucket_for(s_pv, nb, face_near_depth(p, b, f));
+        p.bucket_of[(size_t)b * p.F + f] = (uint8_t)k;
+        atomicAdd(&s_cnt[k], 1u);
+    }
+    __syncthreads();
+    if (t < nb && s_cnt[t]) atomicAdd(p.bucket_count + (size_t)t * p.B + b, s_cnt[t]);
+}
+
+// Exclusive scan of bucket_count (bucket-major) -> bucket_cursor; bucket_base[k] = start of bucket k.
+__global__ void __launch_bounds__(1024) k_depth_offsets(FwdParams p, int nb)
+{
+    __shared__ uint32_t s_part[1024];
+    const int n = nb * p.B, t = threadIdx.x;
+    const int per = (n + 1023) / 1024;
+    const int lo = min(t * per, n), hi = min(lo + per, n);
+    uint32_t sum = 0;
+    for (int i = lo; i < hi; ++i) sum += p.bucket_count[i];
+    s_part[t] = sum;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+        const uint32_t v = t >= o ? s_part[t - o] : 0u;
+        __syncthreads();
+        s_part[t] += v;
+        __syncthreads();
+    }
+    uint32_t run = s_part[t] - sum;
+    for (int i = lo; i < hi; ++i) {
+        p.bucket_cursor[i] = run;
+        if (i % p.B == 0) p.bucket_base[i / p.B] = run;
+        run += p.bucket_count[i];
+    }
+    if (t == 1023) p.bucket_base[nb] = s_part[1023];
+}
+
+// Same chunks as k_depth_classify: a CTA reserves one range per bucket and fills it with its
+// flat face numbers (ranks inside the CTA come from shared-memory counters).
+__global__ void __launch_bounds__(256) k_depth_scatter(FwdParams p, int nb)
+{
+    __shared__ uint32_t s_cnt[kMaxBuckets], s_base[kMaxBuckets];
+    const int b = blockIdx.y, t = threadIdx.x;
+    if (t < kMaxBuckets) s_cnt[t] = 0;
+    __syncthreads();
+    const int f0 = blockIdx.x * kChunkFaces, f1 = min(f0 + kChunkFaces, p.F);
+    uint32_t rank[kChunkFaces / 256];
+    uint8_t kk[kChunkFaces / 256];
+#pragma unroll
+    for (int j = 0; j < kChunkFaces / 256; ++j) {
+        const int f = f0 + t + j * 256;
+        if (f < f1) {
+            kk[j] = p.bucket_of[(size_t)b * p.F + f];
+            rank[j] = atomicAdd(&s_cnt[kk[j]], 1u);
+        }
+    }
+    __syncthreads();
+    if (t < nb && s_cnt[t]) s_base[t] = atomicAdd(p.bucket_cursor + (size_t)t * p.B + b, s_cnt[t]);
+    __syncthreads();
+#pragma unroll
+    for (int j = 0; j < kChunkFaces / 256; ++j) {
+        const int f = f0 + t + j * 256;
+        if (f < f1) p.order[s_base[kk[j]] + rank[j]] = (uint32_t)((size_t)b * p.F + f);
+    }
+}
+
+// Depth pyramid of one 64 x 64 pixel block per CTA: warp w reduces pixel rows 8w .. 8w+7 to
+// eight 8x8 tiles, then levels 1..3 are reduced from shared memory.
+__global__ void __launch_bounds__(256) k_hiz_build(FwdParams p)
+{
+    __shared__ uint32_t s_t[8][8], s_u[4][4], s_v[2][2];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int bx = blockIdx.x, by = blockIdx.y, b = blockIdx.z;
+    uint32_t m0 = 0, m1 = 0;
+#pragma unroll
+    for (int dy = 0; dy < 8; ++dy) {
+        const int py = by * 64 + warp * 8 + dy;                      // window row, y up
+        if (py < p.H) {
+            const unsigned long long *row = p.keys + ((size_t)b * p.H + (size_t)(p.H - 1 - py)) * p.W;
+            const int x0 = bx * 64 + lane, x1 = x0 + 32;
+            if (x0 < p.W) m0 = max(m0, reinterpret_cast<const uint32_t *>(row + x0)[1]);
+            if (x1 < p.W) m1 = max(m1, reinterpret_cast<const uint32_t *>(row + x1)[1]);
+        }
+    }
+#pragma unroll
+    for (int o = 1; o < 8; o <<= 1) {
+        m0 = max(m0, __shfl_xor_sync(kFull, m0, o));
+        m1 = max(m1, __shfl_xor_sync(kFull, m1, o));
+    }
+    if ((lane & 7) == 0) { s_t[warp][lane >> 3] = m0; s_t[warp][4 + (lane >> 3)] = m1; }
+    __syncthreads();
+    const int t = threadIdx.x;
+    auto store = [&](int level, int ty, int tx, uint32_t v) {
+        const int sh = kHizLog2 + level;
+        const int ntx = (p.W + (1 << sh) - 1) >> sh, nty = (p.H + (1 << sh) - 1) >> sh;
+        const int gx = (bx << (3 - level)) + tx, gy = (by << (3 - level)) + ty;
+        if (gx < ntx && gy < nty) p.hiz[p.hiz_off[level] + ((size_t)b * nty + gy) * ntx + gx] = v;
+    };
+    if (t < 64) store(0, t >> 3, t & 7, s_t[t >> 3][t & 7]);
+    if (t < 16) {
+        const int y = t >> 2, x = t & 3;
+        const uint32_t v = max(max(s_t[2 * y][2 * x], s_t[2 * y][2 * x + 1]), max(s_t[2 * y + 1][2 * x], s_t[2 * y + 1][2 * x + 1]));
+        s_u[y][x] = v;
+        store(1, y, x, v);
+    }
+    __syncthreads();
+    if (t < 4) {
+        const int y = t >> 1, x = t & 1;
+        const uint32_t v = max(max(s_u[2 * y][2 * x], s_u[2 * y][2 * x + 1]), max(s_u[2 * y + 1][2 * x], s_u[2 * y + 1][2 * x + 1]));
+        s_v[y][x] = v;
+        store(2, y, x, v);
+    }
+    __syncthreads();
+    if (t == 0) store(3, 0, 0, max(max(s_v[0][0], s_v[0][1]), max(s_v[1][0], s_v[1][1])));
+}
+
+}  // namespace
+
+// Cumulative face fractions of the buckets.  DIRT_B200_BUCKETS="0.1,0.3,1" overrides the
+// default (tuning aid); "1" selects a single ordered pass.
+BucketPlan bucket_plan()
+{
+    static const BucketPlan plan = [] {
+        BucketPlan q;
+        q.n = 4; q.upto[0] = 0.0625f; q.upto[1] = 0.1875f; q.upto[2] = 0.4375f; q.upto[3] = 1.0f;
+        if (const char *e = std::getenv("DIRT_B200_BUCKETS")) {
+            BucketPlan r; r.n = 0;
+            float last = 0.0f;
+            while (*e && r.n < kMaxBuckets) {
+                char *end = nullptr;
+                const float v = std::strtof(e, &end);
+                if (end == e) break;
+                if (v > last && v <= 1.0f) { r.upto[r.n++] = v; last = v; }
+                e = (*end == ',') ? end + 1 : end;
+                if (*end != ',' ) break;
+            }
+            if (r.n > 0) { r.upto[r.n - 1] = 1.0f; q = r; }
+        }
+        return q;
+    }();
+    return plan;
+}
+
+void launch_depth_order(const FwdParams &p, const BucketPlan &plan, int sm_count, cudaStream_t stream)
+{
+    (void)sm_count;
+    const dim3 chunks((unsigned)((p.F + kChunkFaces - 1) / kChunkFaces), (unsigned)p.B);
+    k_depth_pivots<<<p.B, kSamples, 0, stream>>>(p, plan);
+    k_depth_classify<<<chunks, 256, 0, stream>>>(p, plan.n);
+    k_depth_offsets<<<1, 1024, 0, stream>>>(p, plan.n);
+    k_depth_scatter<<<chunks, 256, 0, stream>>>(p, plan.n);
+}
+
+void launch_hiz_build(const FwdParams &p, int sm_count, cudaStream_t stream)
+{
+    (void)sm_count;
+    const dim3 g((unsigned)((p.W + 63) / 64), (unsigned)((p.H + 63) / 64), (unsigned)p.B);
+    k_hiz_build<<<g, 256, 0, stream>>>(p);
+}
+
+}  // namespace dirt

@@ -224,15 +224,38 @@ __global__ void __launch_bounds__(256, KRES_CTAS) k_resolve(FwdParams p)
 {
     const int CC = C > 0 ? C : p.C;
     const int npix = p.H * p.W;
-    // kResolvePix pixels per thread: a CTA that resolves only 256 pixels is launch-rate bound
-    for (int j = 0; j < kResolvePix; ++j)
+    // kResolvePix pixels per thread: a CTA that resolves only 256 pixels is launch-rate bound.
+    // The gather chain key -> face -> corners is software-pipelined over those pixels: the key of
+    // pixel j+2 and the corner indices of pixel j+1 are in flight while pixel j is shaded.
     for (int b = blockIdx.y; b < p.B; b += gridDim.y) {
-        const int o = (int)((blockIdx.x * kResolvePix + j) * blockDim.x + threadIdx.x);
+    const int o0 = (int)(blockIdx.x * kResolvePix * blockDim.x + threadIdx.x);
+    const unsigned long long *kb = p.keys + (size_t)b * npix;
+    const int32_t *fb = p.faces + (int64_t)b * p.faces_bs;
+    unsigned long long key_n1 = o0 < npix ? kb[o0] : kKeyEmpty;
+    unsigned long long key_n2 = o0 + (int)blockDim.x < npix ? kb[o0 + blockDim.x] : kKeyEmpty;
+    int n0 = 0, n1 = 0, n2 = 0;
+    if (key_n1 != kKeyEmpty) {
+        const int32_t *fp = fb + 3 * (int64_t)(uint32_t)key_n1;
+        n0 = __ldg(fp); n1 = __ldg(fp + 1); n2 = __ldg(fp + 2);
+    }
+#pragma unroll 1
+    for (int j = 0; j < kResolvePix; ++j) {
+        const int o = o0 + j * (int)blockDim.x;
         if (o >= npix) break;
+        const unsigned long long key = key_n1;
+        const int i0 = n0, i1 = n1, i2 = n2;
+        key_n1 = key_n2;
+        {
+            const int o2 = o + 2 * (int)blockDim.x;
+            key_n2 = (j + 2 < kResolvePix && o2 < npix) ? kb[o2] : kKeyEmpty;
+        }
+        if (key_n1 != kKeyEmpty) {
+            const int32_t *fp = fb + 3 * (int64_t)(uint32_t)key_n1;
+            n0 = __ldg(fp); n1 = __ldg(fp + 1); n2 = __ldg(fp + 2);
+        }
         const int row = o / p.W, px = o - row * p.W, py = p.H - 1 - row;
         const size_t i = (size_t)b * npix + o;
         float *out = p.pixels + i * CC;
-        const unsigned long long key = p.keys[i];
         if (key == kKeyEmpty) {
             // the reference never clears the colour buffer: background shows through
             const float *bg = p.background + (int64_t)b * p.background_bs + (size_t)o * CC;
@@ -244,8 +267,6 @@ __global__ void __launch_bounds__(256, KRES_CTAS) k_resolve(FwdParams p)
             continue;
         }
         const int f = (int)(uint32_t)(key & 0xFFFFFFFFull);
-        const int32_t *fp = p.faces + (int64_t)b * p.faces_bs + 3 * (int64_t)f;
-        const int i0 = __ldg(fp), i1 = __ldg(fp + 1), i2 = __ldg(fp + 2);
         const int4 *pp = proj_ptr(p, b);
         const int4 ra = __ldg(pp + i0), rb = __ldg(pp + i1), rc = __ldg(pp + i2);
         float B0 = 0.f, B1 = 0.f, wc = 1.f;
@@ -264,7 +285,8 @@ __global__ void __launch_bounds__(256, KRES_CTAS) k_resolve(FwdParams p)
             screen_bary(t, e0, e1, e2, l0, l1, l2);
             perspective_weights(t, l0, l1, l2, B0, B1, b2, wc);
         } else {
-            resolve_clipped(p, b, i0, i1, i2, px, py, B0, B1, wc);
+            const FwdParams pc = p;      // keeps the kernel parameter block itself out of local memory
+            resolve_clipped(pc, b, i0, i1, i2, px, py, B0, B1, wc);
         }
         const float *cp = p.vertex_colors + (int64_t)b * p.vertex_colors_bs;
         const float *c0 = cp + (int64_t)i0 * CC, *c1 = cp + (int64_t)i1 * CC, *c2 = cp + (int64_t)i2 * CC;
@@ -280,6 +302,7 @@ __global__ void __launch_bounds__(256, KRES_CTAS) k_resolve(FwdParams p)
             const float zq = fmul(__uint2float_rn((uint32_t)(key >> 32)), kDepthScaleInv);
             reinterpret_cast<float4 *>(p.gbuffer)[i] = make_float4(B0, B1, wc, zq);
         }
+    }
     }
 }
 
@@ -307,7 +330,7 @@ cudaError_t launch_forward(const FwdParams &p, int sm_count, cudaStream_t stream
     tm.end(kStageClear, stream);
     const long long nfaces = (long long)p.B * p.F;
     if (nfaces > 0) {
-        launch_setup(p, sm_count, stream, tm);
+        launch_setup(p, sm_count, stream, launches, tm);
         tm.begin(kStageBinCount, stream);
         k_bin<false><<<sm_count * 4, 256, 0, stream>>>(p);
         tm.end(kStageBinCount, stream);
@@ -320,7 +343,7 @@ cudaError_t launch_forward(const FwdParams &p, int sm_count, cudaStream_t stream
         tm.begin(kStageTileRaster, stream);
         k_tile_raster<<<(unsigned)ntiles, kTileThreads, 0, stream>>>(p);
         tm.end(kStageTileRaster, stream);
-        *launches += 6;
+        *launches += 5;        // k_project is counted here, the setup launches in launch_setup
     }
     const dim3 g((unsigned)(((long long)p.H * p.W + 256 * kResolvePix - 1) / (256 * kResolvePix)), (unsigned)(p.B < 65535 ? p.B : 65535));
     tm.begin(kStageResolve, stream);

@@ -32,7 +32,22 @@ struct FwdParams {
     uint32_t cap_big;
     unsigned long long cap_queue;
     size_t zero_bytes;           // bytes to clear starting at `counters`
+    // depth-ordered passes with a hierarchical depth buffer (depth_order.cu); order == nullptr: off
+    uint32_t *order;             // [B*F] flat face numbers (b * F + f), grouped by depth bucket
+    uint8_t *bucket_of;          // [B*F]
+    float *pivots;               // [B * kMaxBuckets] bucket boundaries per element
+    uint32_t *bucket_count;      // [kMaxBuckets * B], bucket-major; inside the zeroed region
+    unsigned long long *work_next; // [kMaxBuckets] next unclaimed entry of each setup launch; inside the zeroed region
+    uint32_t *bucket_cursor;     // [kMaxBuckets * B]
+    uint32_t *bucket_base;       // [kMaxBuckets + 1] first entry of each bucket in `order`
+    uint32_t *hiz;               // max depth24 per tile (window space, y up); level l has (8 << l)-px tiles and
+    uint32_t hiz_off[4];         // starts at hiz + hiz_off[l], laid out [B][tiles_y(l)][tiles_x(l)]
 };
+
+constexpr int kMaxBuckets = 8;
+constexpr int kHizLog2 = 3;      // hierarchical-depth tile edge at level 0: 8 px
+constexpr int kHizLevels = 4;    // 8, 16, 32, 64 px
+constexpr int kOrderMinFaces = 4096;   // per element; below this one unordered pass is cheaper
 
 struct BwdParams {
     int B, H, W, C, V, F;
@@ -61,6 +76,11 @@ struct StageTimer {
 };
 
 cudaError_t launch_forward(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_t *launches, StageTimer &tm);
+// depth_order.cu
+struct BucketPlan { int n; float upto[kMaxBuckets]; };       // cumulative face fractions, upto[n-1] = 1
+BucketPlan bucket_plan();
+void launch_depth_order(const FwdParams &p, const BucketPlan &plan, int sm_count, cudaStream_t stream);
+void launch_hiz_build(const FwdParams &p, int sm_count, cudaStream_t stream);
 cudaError_t launch_dilate(const float *x, float *out, int B, int H, int W, int C, int sm_count, cudaStream_t stream);
 cudaError_t launch_dilate_grad(const float *x, const float *grad_out, float *grad_x, int B, int H, int W, int C,
                                int sm_count, cudaStream_t stream);

@@ -19,6 +19,7 @@
 //            With depth complexity d only ~H(d) fragments per pixel reach the atomic unit.
 // Triangles wider than 128 px go to the large-triangle list (S2/S3, forward.cu); faces that
 // cross the near / far plane take the general clipping path.
+#include <cstdio>
 #include "forward_common.cuh"
 
 namespace dirt {
@@ -31,6 +32,13 @@ constexpr int kWarpsPerCta = 8;
 #ifndef KFRAG
 #define KFRAG 4
 #endif
+#ifndef KUNITS
+#define KUNITS 0
+#endif
+#ifndef KPRE0
+#define KPRE0 0
+#endif
+constexpr int kUnitsPerWarp = KUNITS;                 // claims per resident warp a launch should offer (tail of the launch)
 constexpr int kCtasPerSm = KCTAS;                     // the kernel waits on depth loads: occupancy over registers
 constexpr int kFragRound = KFRAG;                     // spans are 1-2 pixels on 3 lines out of 4 (profiles/r1_setup_notes.md)
 constexpr float kLineRcpAreaMin = 1.0f / (2.0f * 65536.0f * 1024.0f);   // 1 / |2 area| of a 1024 px triangle: fatter ones go to the tile path
@@ -104,6 +112,12 @@ __device__ __forceinline__ int write_record(uint32_t *rec, const TriSetup &t, ui
     return axis ? bw : bh;
 }
 
+// 64-bit minimum without a return value, explicitly in the global space.
+__device__ __forceinline__ void red_min_key(unsigned long long *kp, unsigned long long key)
+{
+    asm volatile("red.global.min.u64 [%0], %1;" :: "l"(kp), "l"(key) : "memory");
+}
+
 // The depth half (high word) of a key.  Cached in L1: staleness is harmless (see sample_line).
 __device__ __forceinline__ uint32_t load_depth_word(const unsigned long long *kp)
 {
@@ -113,6 +127,7 @@ __device__ __forceinline__ uint32_t load_depth_word(const unsigned long long *kp
 }
 
 // Samples line `j` of the triangle in `rec` (a row when axis == 0, a column when axis == 1).
+template <bool PRELOAD>
 __device__ __forceinline__ void sample_line(const uint32_t *rec, int j, const FwdParams &p)
 {
     const uint4 *row = reinterpret_cast<const uint4 *>(rec);
@@ -159,7 +174,7 @@ __device__ __forceinline__ void sample_line(const uint32_t *rec, int j, const Fw
         uint32_t cur[kFragRound];
 #pragma unroll
         for (int u = 0; u < kFragRound; ++u)
-            cur[u] = u < n ? load_depth_word(kp + u * stride) : 0u;
+            cur[u] = !PRELOAD ? 0xFFFFFFFFu : (u < n ? load_depth_word(kp + u * stride) : 0u);
 #pragma unroll
         for (int u = 0; u < kFragRound; ++u) {
             if (u < n) {
@@ -169,7 +184,7 @@ __device__ __forceinline__ void sample_line(const uint32_t *rec, int j, const Fw
                 // keys only ever decrease, so a stale depth can only cost a redundant atomic;
                 // on equal depth the atomic decides (lowest face index wins)
                 if (d < kDepthMax && d <= cur[u])
-                    atomicMin(kp + u * stride, ((unsigned long long)d << 32) | face);
+                    red_min_key(kp + u * stride, ((unsigned long long)d << 32) | face);
                 fi += 1.0f;
             }
         }
@@ -196,19 +211,62 @@ static __device__ __noinline__ void setup_clipped(const FwdParams &p, int b, int
     }
 }
 
-__global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdParams p)
+// True when no fragment of t can win a pixel: its smallest possible depth is beyond the
+// hierarchical depth buffer in every tile the bounding box touches.  The plane depth is monotone
+// in dx and in dy under round-to-nearest, so its minimum over the box is taken at a corner.
+__device__ __forceinline__ bool hidden_by_hiz(const FwdParams &p, int b, const TriSetup &t)
+{
+    const float dx = t.dzdx >= 0.0f ? 0.0f : __int2float_rn(t.xmax - t.xmin);
+    const float dy = t.dzdy >= 0.0f ? 0.0f : __int2float_rn(t.ymax - t.ymin);
+    float zw = fadd(fadd(t.zref, fmul(t.dzdx, dx)), fmul(t.dzdy, dy));
+    zw = fminf(fmaxf(zw, 0.0f), 1.0f);
+    const uint32_t dmin = __float2uint_rz(fadd(fmul(zw, 16777215.0f), 0.5f));
+    // the level at which the box spans at most 3 x 3 tiles: nine independent loads
+    const int ext = max(t.xmax - t.xmin, t.ymax - t.ymin);
+    int l = 0;
+    while (l < kHizLevels && (ext >> (kHizLog2 + l)) > 1) ++l;
+    if (l == kHizLevels) return false;
+    const int sh = kHizLog2 + l;
+    const int ntx = (p.W + (1 << sh) - 1) >> sh, nty = (p.H + (1 << sh) - 1) >> sh;
+    const int tx0 = t.xmin >> sh, ty0 = t.ymin >> sh, nx = (t.xmax >> sh) - tx0, ny = (t.ymax >> sh) - ty0;
+    const uint32_t *hz = p.hiz + p.hiz_off[l] + ((size_t)b * nty + ty0) * ntx + tx0;
+    uint32_t m = 0;
+#pragma unroll
+    for (int dy = 0; dy < 3; ++dy)
+#pragma unroll
+        for (int dx = 0; dx < 3; ++dx)
+            if (dx <= nx && dy <= ny) m = max(m, __ldg(hz + dy * ntx + dx));
+    return m < dmin;          // equal depth: the face index decides
+}
+
+// ORDERED: the faces of depth bucket `bucket` (depth_order.cu), tested against the hierarchical
+// depth buffer when `use_hiz`; otherwise all faces in index order.
+template <bool ORDERED>
+__global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdParams p, int bucket, int use_hiz, int batch)
 {
     __shared__ __align__(16) uint32_t s_recs[kWarpsPerCta][32 * kRecWords];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t *recs = s_recs[warp];
-    const long long total = (long long)p.B * p.F;
-    const long long total_padded = (total + 31) & ~31ll;       // warps stay together
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total_padded;
-         i += (long long)gridDim.x * blockDim.x) {
+    long long first_entry = 0, total = (long long)p.B * p.F;
+    if (ORDERED) {
+        first_entry = p.bucket_base[bucket];
+        total = (long long)p.bucket_base[bucket + 1] - first_entry;
+    }
+    // Batches of 32 faces are claimed dynamically (their line counts differ by orders of
+    // magnitude); the claim for the next batch is issued before the current one is sampled.
+    unsigned long long *work = p.work_next + bucket;
+    unsigned long long claim = 0;
+    if (lane == 0) claim = atomicAdd(work, (unsigned long long)batch);
+    for (;;) {
+        const long long i0 = (long long)__shfl_sync(kFullMask, claim, 0);
+        if (i0 >= total) break;
+        const long long i = lane < batch ? i0 + lane : total;
+        if (lane == 0) claim = atomicAdd(work, (unsigned long long)batch);
         // ---- setup: one face per lane -------------------------------------------------------
         int nlines = 0;
         if (i < total) {
-            const int b = (int)(i / p.F), f = (int)(i - (long long)b * p.F);
+            const long long flat = ORDERED ? (long long)p.order[first_entry + i] : i;
+            const int b = (int)(flat / p.F), f = (int)(flat - (long long)b * p.F);
             const int32_t *fp = p.faces + (int64_t)b * p.faces_bs + 3 * (int64_t)f;
             const int i0 = __ldg(fp), i1 = __ldg(fp + 1), i2 = __ldg(fp + 2);
             if ((unsigned)i0 < (unsigned)p.V && (unsigned)i1 < (unsigned)p.V && (unsigned)i2 < (unsigned)p.V) {
@@ -218,16 +276,28 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
                 if (setup_from_proj(__ldg(pp + i0), __ldg(pp + i1), __ldg(pp + i2), p.W, p.H, t, slow)) {
                     const int ex = max(t.X0, max(t.X1, t.X2)) - min(t.X0, min(t.X1, t.X2));
                     const int ey = max(t.Y0, max(t.Y1, t.Y2)) - min(t.Y0, min(t.Y1, t.Y2));
-                    // few-but-fat triangles are better off pixel-parallel in the tile path
-                    if (ex < kSmallExtent && ey < kSmallExtent && (t.rcp_area > kLineRcpAreaMin || (t.xmax - t.xmin + 1) * (t.ymax - t.ymin + 1) <= 256))
+                    if (ORDERED && use_hiz && hidden_by_hiz(p, b, t)) {
+                        // dropped: cannot win any pixel
+#ifdef DIRT_STATS
+                        atomicAdd(p.counters + 4, 1u);
+                        atomicAdd(p.counters + 5, (uint32_t)max(t.xmax - t.xmin + 1, t.ymax - t.ymin + 1));
+#endif
+                    } else if (ex < kSmallExtent && ey < kSmallExtent && (t.rcp_area > kLineRcpAreaMin || (t.xmax - t.xmin + 1) * (t.ymax - t.ymin + 1) <= 256))
+                        // few-but-fat triangles are better off pixel-parallel in the tile path
                         nlines = write_record(recs + lane * kRecWords, t, (uint32_t)f, (uint32_t)b);
                     else
                         push_big(t, b, (uint32_t)f, 0u, p);
                 } else if (slow) {
-                    setup_clipped(p, b, f, i0, i1, i2);
+                    // a private copy: taking the address of the kernel parameter block itself would move
+                    // it to local memory for the whole kernel (and make every key atomic a generic one)
+                    const FwdParams pc = p;
+                    setup_clipped(pc, b, f, i0, i1, i2);
                 }
             }
         }
+#ifdef DIRT_STATS
+        if (nlines) { atomicAdd(p.counters + 6, 1u); atomicAdd(p.counters + 7, (uint32_t)nlines); }
+#endif
         // ---- sampling: 32 lines at a time ---------------------------------------------------
         int incl = nlines;
 #pragma unroll
@@ -247,13 +317,17 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
                 if (v <= g) t += s;
             }
             const int first = __shfl_sync(kFullMask, incl - nlines, t & 31);
-            if (g < nall) sample_line(recs + t * kRecWords, g - first, p);
+            if (g < nall) {
+                // nearest bucket: nearly every fragment wins, reading the depth first only adds latency
+                if (KPRE0 == 0 && ORDERED && !use_hiz) sample_line<false>(recs + t * kRecWords, g - first, p);
+                else sample_line<true>(recs + t * kRecWords, g - first, p);
+            }
         }
         __syncwarp();     // the records are about to be overwritten
     }
 }
 
-void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, StageTimer &tm)
+void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_t *launches, StageTimer &tm)
 {
     const long long nfaces = (long long)p.B * p.F;
     const int nbatch = p.vertices_bs == 0 ? 1 : p.B;
@@ -268,10 +342,37 @@ void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, StageTi
     tm.end(kStageProject, stream);
     tm.begin(kStageSetup, stream);
     long long g = (nfaces + kWarpsPerCta * 32 - 1) / (kWarpsPerCta * 32);
-    const long long cap = (long long)sm_count * 32;
+    const long long cap = (long long)sm_count * kCtasPerSm;        // resident CTAs: work is claimed dynamically
     if (g > cap) g = cap;
     if (g < 1) g = 1;
-    k_setup<<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p);
+    // Faces claimed per warp and round: 32 when there is plenty of work, fewer when a launch has
+    // so few faces that whole batches would leave most of the machine idle at its end.
+    auto batch_for = [&](double faces) {
+        int bsz = 32;
+        while (bsz > 4 && faces / bsz < (double)cap * kWarpsPerCta * kUnitsPerWarp) bsz >>= 1;
+        return bsz;
+    };
+    if (p.order) {
+        // front-to-back buckets; the hierarchical depth buffer is refreshed between them
+        const BucketPlan plan = bucket_plan();
+        launch_depth_order(p, plan, sm_count, stream);
+        for (int k = 0; k < plan.n; ++k) {
+            if (k > 0) launch_hiz_build(p, sm_count, stream);
+            const double share = plan.upto[k] - (k > 0 ? plan.upto[k - 1] : 0.0f);
+            k_setup<true><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, k, k > 0, batch_for(share * (double)nfaces));
+#ifdef DIRT_STATS
+            uint32_t c[8], bb[kMaxBuckets + 1];
+            cudaStreamSynchronize(stream);
+            cudaMemcpy(c, p.counters, sizeof(c), cudaMemcpyDeviceToHost);
+            cudaMemcpy(bb, p.bucket_base, sizeof(bb), cudaMemcpyDeviceToHost);
+            printf("bucket %d: faces %u | cumulative: culled tris %u (lines %u), sampled tris %u (lines %u)\n", k, bb[k + 1] - bb[k], c[4], c[5], c[6], c[7]);
+#endif
+        }
+        *launches += 4 + 2 * plan.n - 1;
+    } else {
+        k_setup<false><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, 0, 0, batch_for((double)nfaces));
+        *launches += 1;
+    }
     tm.end(kStageSetup, stream);
 }
 
