@@ -201,13 +201,14 @@ __global__ void __launch_bounds__(256) k_hiz_build(FwdParams p)
 }  // namespace
 
 // Cumulative face fractions of the buckets.  DIRT_B200_BUCKETS="0.1,0.3,1" overrides the
-// default (tuning aid); "1" selects a single ordered pass.
+// default (tuning aid); "1" selects a single ordered pass, "0" the unordered single pass.
 BucketPlan bucket_plan()
 {
     static const BucketPlan plan = [] {
         BucketPlan q;
-        q.n = 4; q.upto[0] = 0.0625f; q.upto[1] = 0.1875f; q.upto[2] = 0.4375f; q.upto[3] = 1.0f;
+        q.n = 3; q.upto[0] = 0.1f; q.upto[1] = 0.3f; q.upto[2] = 1.0f;
         if (const char *e = std::getenv("DIRT_B200_BUCKETS")) {
+            if (e[0] == '0' && e[1] == 0) { q.n = 0; return q; }
             BucketPlan r; r.n = 0;
             float last = 0.0f;
             while (*e && r.n < kMaxBuckets) {

@@ -5,8 +5,11 @@
 
 namespace dirt {
 
-constexpr int kSmallExtent = (1 << 15) - 512;   // sub-pixel extent (126 px) below which edge functions, evaluated up to
-                                                // two pixels outside the bbox, fit in int32: 2 * (e + 512) * e < 2^31
+constexpr int kSmallExtent = (1 << 15) - 512;   // sub-pixel extent (126 px) below which a triangle is line-sampled.  Edge
+                                                // functions fit in int32 (two products below 2^30 each), and at a point
+                                                // of the bounding box |e| <= extent_x * extent_y < 2^30 (twice the area of
+                                                // a triangle inside a rectangle), which the exact float crossing of
+                                                // setup_raster.cu relies on: |e| / 256 < 2^22
 constexpr int kProjSlow = (int)0x80000000;   // ProjVert.X of a vertex that needs the general (clipping) path
 constexpr int kTile = 16;             // tile edge in pixels
 constexpr int kTileThreads = kTile * kTile;

@@ -5,19 +5,19 @@
 //            1/256 px, window depth, 1/w -> a 16-byte record.  A vertex is projected once
 //            instead of once per incident face (~6x fewer divides on a closed mesh).
 // k_setup    lane t of a warp sets up face t of a group of 32 faces from three gathered
-//            records (int32 edge functions: every triangle on this path fits in 128 px).
+//            records (int32 edge functions: every triangle on this path fits in 126 px).
 //            Sampling is then re-distributed inside the warp, because "one lane walks one
 //            triangle" leaves most lanes idle on long thin triangles
 //            (profiles/r1_setup_notes.md): the unit of work is a scan LINE of a triangle --
 //            a row or a column, whichever makes the lines' spans short (slivers are scanned
 //            across their narrow side).  A warp prefix sum over the lines per triangle and a
 //            5-step shuffle search hand 32 lines at a time to the 32 lanes.  Each lane
-//            computes its line's EXACT covered span (float estimate of each edge crossing,
-//            one integer correction step against the exact edge value, so float arithmetic
-//            never decides coverage) and walks it: plane depth, depth|face key, a plain load
+//            computes its line's EXACT covered span (each edge crossing is a ceiling division
+//            evaluated in float in a form that is provably exact for these operand ranges, so
+//            coverage stays an integer decision) and walks it: plane depth, depth|face key, a plain load
 //            of the current key, and a 64-bit atomicMin only when the fragment would win.
 //            With depth complexity d only ~H(d) fragments per pixel reach the atomic unit.
-// Triangles wider than 128 px go to the large-triangle list (S2/S3, forward.cu); faces that
+// Triangles wider than 126 px go to the large-triangle list (S2/S3, forward.cu); faces that
 // cross the near / far plane take the general clipping path.
 #include <cstdio>
 #include "forward_common.cuh"
@@ -76,7 +76,7 @@ __global__ void __launch_bounds__(256) k_project(FwdParams p, int nbatch)
 //   row 1: sa0 sa1 sa2 dims  sa_k = edge step per +1 position ALONG a line; dims = m1 | axis << 8
 //                            (m1 = last position of a line; axis 1: lines are columns)
 //   row 2: sc0 sc1 sc2 face  sc_k = edge step per +1 line
-//   row 3: inv0 inv1 inv2 elem   inv_k = 1 / sa_k as float (0 when sa_k == 0)
+//   row 3: inv0 inv1 inv2 elem   inv_k = 256 / |sa_k| as float (0 when sa_k == 0)
 //   row 4: zref dzdx dzdy -
 constexpr int kRecWords = 20;
 
@@ -101,7 +101,8 @@ __device__ __forceinline__ int write_record(uint32_t *rec, const TriSetup &t, ui
         A[k] = (uint32_t)(e + bias[k]);
         sa[k] = (uint32_t)along;
         sc[k] = (uint32_t)(axis ? sx : sy);
-        inv[k] = __float_as_uint(along != 0 ? __frcp_rn((float)along) : 0.0f);
+        const int mag = (along < 0 ? -along : along) >> 8;           // |ey| or |ex|
+        inv[k] = __float_as_uint(mag != 0 ? __frcp_rn((float)mag) : 0.0f);
     }
     uint4 *row = reinterpret_cast<uint4 *>(rec);
     row[0] = make_uint4(A[0], A[1], A[2], (uint32_t)t.xmin | ((uint32_t)t.ymin << 16));
@@ -137,23 +138,22 @@ __device__ __forceinline__ void sample_line(const uint32_t *rec, int j, const Fw
     const int A[3] = {(int)rA.x, (int)rA.y, (int)rA.z}, SA[3] = {(int)rSA.x, (int)rSA.y, (int)rSA.z};
     const int SC[3] = {(int)rSC.x, (int)rSC.y, (int)rSC.z};
     const float INV[3] = {__uint_as_float(rINV.x), __uint_as_float(rINV.y), __uint_as_float(rINV.z)};
-    const float fj = __int2float_rn(j), fm = __int2float_rn(m1 + 1);
+    const float fj = __int2float_rn(j);
     int lo = 0, hi = m1;
 #pragma unroll
     for (int k = 0; k < 3; ++k) {
+        // Edge k along the line: a + sa * c >= 0 with sa = +-256 * s.  The bound on c is
+        // ceil(na / s) with na = ceil(-a / 256) (nested ceilings), and
+        // ceil((float(na) - 0.5) * (1 / s)) evaluates it EXACTLY in floating point: |na| < 2^22
+        // (kSmallExtent) keeps the rounding error below the 0.5 / s that separates the shifted
+        // quotient from the nearest integers (checked exhaustively-at-random in tests/test_span_math.py),
+        // so coverage is still decided by integer arithmetic alone.
         const int sa = SA[k];
         const int a = A[k] + SC[k] * j;              // edge value (+ bias) at position 0 of this line
-        // float estimate of the crossing, clamped to the line, then one exact correction step
-        const float q = -__int2float_rn(a) * INV[k];
-        const int dir = (sa > 0) - (sa < 0);
-        float qc = sa > 0 ? ceilf(q) : floorf(q);
-        qc = fminf(fmaxf(qc, -1.0f), fm);
-        int c = (int)qc;
-        const int v = a + sa * c;
-        const int asa = sa < 0 ? -sa : sa;
-        c += v < 0 ? dir : (v - asa >= 0 ? -dir : 0);
-        if (sa > 0) lo = max(lo, c);
-        else if (sa < 0) hi = min(hi, c);
+        const int na = (255 - a) >> 8;
+        const int m = __float2int_ru(fmul(fadd(__int2float_rn(na), -0.5f), INV[k]));
+        if (sa > 0) lo = max(lo, m);                 // smallest c inside
+        else if (sa < 0) hi = min(hi, -m);           // largest c inside
         else if (a < 0) hi = -1;
     }
     if (lo > hi) return;
@@ -352,9 +352,9 @@ void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_
         while (bsz > 4 && faces / bsz < (double)cap * kWarpsPerCta * kUnitsPerWarp) bsz >>= 1;
         return bsz;
     };
-    if (p.order) {
+    const BucketPlan plan = bucket_plan();
+    if (p.order && plan.n > 0) {
         // front-to-back buckets; the hierarchical depth buffer is refreshed between them
-        const BucketPlan plan = bucket_plan();
         launch_depth_order(p, plan, sm_count, stream);
         for (int k = 0; k < plan.n; ++k) {
             if (k > 0) launch_hiz_build(p, sm_count, stream);
