@@ -95,9 +95,12 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.time(), line.strip()))
 
-    def stop(self):
+    def count_since(self, t0):
+        return sum(1 for t, _ in self.lines if t >= t0)
+
+    def stop(self, t0=0.0, window="timed region"):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
@@ -107,7 +110,9 @@ class ClockSampler:
             self.proc.kill()
         sm, smax, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        for t, ln in self.lines:
+            if t < t0:
+                continue
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 9:
                 continue
@@ -119,7 +124,7 @@ class ClockSampler:
                 if v.lower().startswith("active"):
                     reasons.add(n)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+                "reasons": sorted(reasons), "samples": len(sm), "window": window}
 
 
 def cpu_baseline_run(wl, target_seconds, threads=None):
@@ -160,8 +165,9 @@ def hbm_peak():
 
 
 def ncu_traffic(kernel, workload):
-    """DRAM bytes per launch of `kernel` from the committed ncu --set full capture of the headline
-    workload (profiles/roofline_traffic.json, written by tools/ncu_summary.py), or None."""
+    """DRAM bytes of `kernel` summed over the launches of ONE step, from the committed ncu --set full
+    capture of the headline workload (profiles/roofline_traffic.json, written by
+    tools/ncu_summary.py), or None."""
     if workload != "headline":
         return None
     try:
@@ -251,15 +257,16 @@ def run_ours(args, wl, rank, world, local_rank):
             return float(t.item())
         return ms
 
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()                      # nvidia-smi needs ~1 s to deliver its first sample
     for _ in range(max(args.warmup, 3)):
         step()
     barrier()
-    clocks = ClockSampler(local_rank)
-    if rank == 0:
-        clocks.start()
     n0 = _lib.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
+    t_timed = time.time()
     ev0.record()
     for _ in range(args.steps):
         step()
@@ -267,26 +274,42 @@ def run_ours(args, wl, rank, world, local_rank):
     barrier()
     ms_total = max_over_ranks(ev0.elapsed_time(ev1))
     launches = _lib.launch_count() - n0
-    clock_info = clocks.stop() if rank == 0 else None
+    # A timed region shorter than a few sampling periods (100 ms each) yields no clock samples:
+    # keep the same load running, untimed, until some have arrived (all ranks, to stay in step).
+    window = "timed region"
+    if ms_total < 1500.0:
+        window = "timed region + untimed continuation of the same steps (timed region shorter than the sampling period)"
+        for _ in range(int(min(5000, 1500.0 / max(ms_total / args.steps, 1e-3)))):    # same count on every rank
+            step()
+        barrier()
+    clock_info = clocks.stop(t_timed, window) if rank == 0 else None
     ms_step = ms_total / args.steps
     value = world * B * H * W / (ms_step * 1e-3) / 1e6
 
     # ---- per-kernel durations, measured live with CUDA events inside the library -------------
     _lib.check(lib.dirt_profile_reset())
     _lib.check(lib.dirt_profile_enable(1))
-    for _ in range(min(args.steps, 10)):
+    nprof = min(args.steps, 10)
+    for _ in range(nprof):
         step()
         torch.cuda.synchronize()
         _lib.check(lib.dirt_profile_collect())
     _lib.check(lib.dirt_profile_enable(0))
-    stages = {k: (ms / n if n else 0.0) for k, (ms, n) in _lib.stage_times().items()}
+    times = _lib.stage_times()
+    stages = {k: ms / nprof for k, (ms, n) in times.items()}                      # per step
+    per_step_launches = {k: n / nprof for k, (ms, n) in times.items()}
     per_kernel, fwd_bytes, bwd_bytes = algorithmic_bytes(B, H, W, C, V, F, shared)
     dominant = max(per_kernel, key=lambda k: stages.get(k, 0.0))
     peak, peak_src = hbm_peak()
+    # A kernel launched several times per step (k_setup: once per depth bucket) is reported per
+    # launch: its algorithmic bytes and its measured time are both divided by the launch count.
+    nl = max(per_step_launches.get(dominant, 1.0), 1.0)
     achieved = per_kernel[dominant] / (stages[dominant] * 1e-3) / 1e9 if stages[dominant] > 0 else 0.0
+    traffic = ncu_traffic("k_" + dominant, args.workload)
     roofline = {"bound": "hbm", "kernel": "k_" + dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": ncu_traffic("k_" + dominant, args.workload), "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": per_kernel[dominant], "kernel_ms": stages[dominant],
+                "frac": achieved / peak, "traffic": traffic / nl if traffic else None, "peak_source": peak_src,
+                "launches_per_step": nl, "algorithmic_bytes_per_launch": per_kernel[dominant] / nl,
+                "kernel_ms": stages[dominant] / nl,
                 "step_algorithmic_bytes": fwd_bytes + bwd_bytes,
                 "step_achieved_GBps": (fwd_bytes + bwd_bytes) / (ms_step * 1e-3) / 1e9,
                 "step_frac": (fwd_bytes + bwd_bytes) / (ms_step * 1e-3) / 1e9 / peak}

@@ -71,7 +71,7 @@ EXPORTS = {
     "dirt_profile_reset": (ctypes.c_int, []),
     "dirt_profile_stage_name": (ctypes.c_char_p, [ctypes.c_int]),
 }
-STAGE_COUNT = 10
+STAGE_COUNT = 12
 
 _lib = None
 

@@ -84,7 +84,10 @@ __device__ __forceinline__ void red_add3(float *dst, float a, float b, float c)
 }
 
 template <int C>
-__global__ void __launch_bounds__(kBT * kBT) k_grad_assemble(BwdParams p)
+#ifndef KBWD_CTAS
+#define KBWD_CTAS 5
+#endif
+__global__ void __launch_bounds__(kBT * kBT, KBWD_CTAS) k_grad_assemble(BwdParams p)
 {
     constexpr int CS = C > 0 ? C : kMaxC;
     const int CC = C > 0 ? C : p.C;

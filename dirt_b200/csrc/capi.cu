@@ -20,7 +20,8 @@ dirt::StageTimer g_timer;
 double g_stage_ms[dirt::kStageCount] = {};
 uint64_t g_stage_calls[dirt::kStageCount] = {};
 const char *const kStageNames[dirt::kStageCount] = {
-    "clear", "project", "setup", "bin_count", "bin_alloc", "bin_fill", "tile_raster", "resolve", "grad_clear", "grad_assemble"};
+    "clear", "project", "depth_order", "setup", "hiz_build", "bin_count", "bin_alloc", "bin_fill", "tile_raster", "resolve",
+    "grad_clear", "grad_assemble"};
 
 int fail(int status, const char *fmt, ...)
 {
@@ -278,12 +279,13 @@ int dirt_dilate_silhouette_grad(const float *x, const float *grad_out, float *gr
 int dirt_profile_enable(int enable)
 {
     std::lock_guard<std::mutex> lock(g_prof_mu);
-    if (enable && !g_timer.ev[0][0]) {
+    if (enable && !g_timer.ev[0][0][0]) {
         for (int s = 0; s < dirt::kStageCount; ++s)
-            for (int k = 0; k < 2; ++k) {
-                cudaError_t e = cudaEventCreate(&g_timer.ev[s][k]);
-                if (e != cudaSuccess) return cuda_fail(e, "cudaEventCreate");
-            }
+            for (int r = 0; r < dirt::StageTimer::kSlots; ++r)
+                for (int k = 0; k < 2; ++k) {
+                    cudaError_t e = cudaEventCreate(&g_timer.ev[s][r][k]);
+                    if (e != cudaSuccess) return cuda_fail(e, "cudaEventCreate");
+                }
     }
     g_timer.enabled = enable != 0;
     return DIRT_STATUS_OK;
@@ -293,13 +295,15 @@ int dirt_profile_collect(void)
 {
     std::lock_guard<std::mutex> lock(g_prof_mu);
     for (int s = 0; s < dirt::kStageCount; ++s) {
-        if (!g_timer.pending[s]) continue;
-        float ms = 0.f;
-        cudaError_t e = cudaEventElapsedTime(&ms, g_timer.ev[s][0], g_timer.ev[s][1]);
-        if (e != cudaSuccess) return cuda_fail(e, "cudaEventElapsedTime (synchronise the stream before dirt_profile_collect)");
-        g_stage_ms[s] += ms;
-        g_stage_calls[s] += 1;
-        g_timer.pending[s] = false;
+        if (!g_timer.used[s]) continue;
+        for (int r = 0; r < g_timer.used[s]; ++r) {
+            float ms = 0.f;
+            cudaError_t e = cudaEventElapsedTime(&ms, g_timer.ev[s][r][0], g_timer.ev[s][r][1]);
+            if (e != cudaSuccess) return cuda_fail(e, "cudaEventElapsedTime (synchronise the stream before dirt_profile_collect)");
+            g_stage_ms[s] += ms;
+        }
+        g_stage_calls[s] += (uint64_t)g_timer.used[s];   // timed runs of the stage (the depth-bucket launches count separately)
+        g_timer.used[s] = 0;
     }
     return DIRT_STATUS_OK;
 }
@@ -317,7 +321,7 @@ int dirt_profile_read(double *total_ms, uint64_t *calls, int n)
 int dirt_profile_reset(void)
 {
     std::lock_guard<std::mutex> lock(g_prof_mu);
-    for (int s = 0; s < dirt::kStageCount; ++s) { g_stage_ms[s] = 0; g_stage_calls[s] = 0; g_timer.pending[s] = false; }
+    for (int s = 0; s < dirt::kStageCount; ++s) { g_stage_ms[s] = 0; g_stage_calls[s] = 0; g_timer.used[s] = 0; }
     return DIRT_STATUS_OK;
 }
 

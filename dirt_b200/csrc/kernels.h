@@ -62,17 +62,19 @@ struct BwdParams {
 };
 
 enum Stage {
-    kStageClear = 0, kStageProject, kStageSetup, kStageBinCount, kStageBinAlloc, kStageBinFill, kStageTileRaster, kStageResolve,
-    kStageGradClear, kStageGradAssemble, kStageCount
+    kStageClear = 0, kStageProject, kStageDepthOrder, kStageSetup, kStageHizBuild, kStageBinCount, kStageBinAlloc, kStageBinFill,
+    kStageTileRaster, kStageResolve, kStageGradClear, kStageGradAssemble, kStageCount
 };
 
-// Records a CUDA event pair around each stage when enabled (capi.cu owns the storage).
+// Records CUDA event pairs around each stage when enabled (capi.cu owns the storage).  A stage
+// may run several times per call (the depth-bucket launches): each run takes the next slot.
 struct StageTimer {
+    static constexpr int kSlots = 8;
     bool enabled = false;
-    cudaEvent_t ev[kStageCount][2] = {};
-    bool pending[kStageCount] = {};
-    void begin(int s, cudaStream_t st) { if (enabled) cudaEventRecord(ev[s][0], st); }
-    void end(int s, cudaStream_t st) { if (enabled) { cudaEventRecord(ev[s][1], st); pending[s] = true; } }
+    cudaEvent_t ev[kStageCount][kSlots][2] = {};
+    int used[kStageCount] = {};
+    void begin(int s, cudaStream_t st) { if (enabled && used[s] < kSlots) cudaEventRecord(ev[s][used[s]][0], st); }
+    void end(int s, cudaStream_t st) { if (enabled && used[s] < kSlots) { cudaEventRecord(ev[s][used[s]][1], st); ++used[s]; } }
 };
 
 cudaError_t launch_forward(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_t *launches, StageTimer &tm);

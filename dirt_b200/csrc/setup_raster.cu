@@ -32,13 +32,9 @@ constexpr int kWarpsPerCta = 8;
 #ifndef KFRAG
 #define KFRAG 4
 #endif
-#ifndef KUNITS
-#define KUNITS 0
-#endif
 #ifndef KPRE0
 #define KPRE0 0
 #endif
-constexpr int kUnitsPerWarp = KUNITS;                 // claims per resident warp a launch should offer (tail of the launch)
 constexpr int kCtasPerSm = KCTAS;                     // the kernel waits on depth loads: occupancy over registers
 constexpr int kFragRound = KFRAG;                     // spans are 1-2 pixels on 3 lines out of 4 (profiles/r1_setup_notes.md)
 constexpr float kLineRcpAreaMin = 1.0f / (2.0f * 65536.0f * 1024.0f);   // 1 / |2 area| of a 1024 px triangle: fatter ones go to the tile path
@@ -242,7 +238,7 @@ __device__ __forceinline__ bool hidden_by_hiz(const FwdParams &p, int b, const T
 // ORDERED: the faces of depth bucket `bucket` (depth_order.cu), tested against the hierarchical
 // depth buffer when `use_hiz`; otherwise all faces in index order.
 template <bool ORDERED>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdParams p, int bucket, int use_hiz, int batch)
+__global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdParams p, int bucket, int use_hiz)
 {
     __shared__ __align__(16) uint32_t s_recs[kWarpsPerCta][32 * kRecWords];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -254,14 +250,16 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
     }
     // Batches of 32 faces are claimed dynamically (their line counts differ by orders of
     // magnitude); the claim for the next batch is issued before the current one is sampled.
+    // Smaller batches shorten the tail of a launch but repeat the latency-bound setup phase more
+    // often: 16 and 8 faces per claim measured slower (profiles/r1_setup_notes.md).
     unsigned long long *work = p.work_next + bucket;
     unsigned long long claim = 0;
-    if (lane == 0) claim = atomicAdd(work, (unsigned long long)batch);
+    if (lane == 0) claim = atomicAdd(work, 32ull);
     for (;;) {
         const long long i0 = (long long)__shfl_sync(kFullMask, claim, 0);
         if (i0 >= total) break;
-        const long long i = lane < batch ? i0 + lane : total;
-        if (lane == 0) claim = atomicAdd(work, (unsigned long long)batch);
+        const long long i = i0 + lane;
+        if (lane == 0) claim = atomicAdd(work, 32ull);
         // ---- setup: one face per lane -------------------------------------------------------
         int nlines = 0;
         if (i < total) {
@@ -340,26 +338,25 @@ void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_
         k_project<<<(int)gv, 256, 0, stream>>>(p, nbatch);
     }
     tm.end(kStageProject, stream);
-    tm.begin(kStageSetup, stream);
     long long g = (nfaces + kWarpsPerCta * 32 - 1) / (kWarpsPerCta * 32);
     const long long cap = (long long)sm_count * kCtasPerSm;        // resident CTAs: work is claimed dynamically
     if (g > cap) g = cap;
     if (g < 1) g = 1;
-    // Faces claimed per warp and round: 32 when there is plenty of work, fewer when a launch has
-    // so few faces that whole batches would leave most of the machine idle at its end.
-    auto batch_for = [&](double faces) {
-        int bsz = 32;
-        while (bsz > 4 && faces / bsz < (double)cap * kWarpsPerCta * kUnitsPerWarp) bsz >>= 1;
-        return bsz;
-    };
     const BucketPlan plan = bucket_plan();
     if (p.order && plan.n > 0) {
         // front-to-back buckets; the hierarchical depth buffer is refreshed between them
+        tm.begin(kStageDepthOrder, stream);
         launch_depth_order(p, plan, sm_count, stream);
+        tm.end(kStageDepthOrder, stream);
         for (int k = 0; k < plan.n; ++k) {
-            if (k > 0) launch_hiz_build(p, sm_count, stream);
-            const double share = plan.upto[k] - (k > 0 ? plan.upto[k - 1] : 0.0f);
-            k_setup<true><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, k, k > 0, batch_for(share * (double)nfaces));
+            if (k > 0) {
+                tm.begin(kStageHizBuild, stream);
+                launch_hiz_build(p, sm_count, stream);
+                tm.end(kStageHizBuild, stream);
+            }
+            tm.begin(kStageSetup, stream);
+            k_setup<true><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, k, k > 0);
+            tm.end(kStageSetup, stream);
 #ifdef DIRT_STATS
             uint32_t c[8], bb[kMaxBuckets + 1];
             cudaStreamSynchronize(stream);
@@ -370,10 +367,11 @@ void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_
         }
         *launches += 4 + 2 * plan.n - 1;
     } else {
-        k_setup<false><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, 0, 0, batch_for((double)nfaces));
+        tm.begin(kStageSetup, stream);
+        k_setup<false><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, 0, 0);
+        tm.end(kStageSetup, stream);
         *launches += 1;
     }
-    tm.end(kStageSetup, stream);
 }
 
 }  // namespace dirt

@@ -162,9 +162,11 @@ DIRT_API uint64_t dirt_kernel_launch_count(void);
  *   dirt_profile_enable(1)  -> subsequent forward/backward calls record events per stage
  *   dirt_profile_collect()  -> call after synchronising the stream: folds the elapsed time of
  *                              every stage recorded since the last collect into the totals
- *   dirt_profile_read()     -> cumulative milliseconds and launch counts per stage
+ *   dirt_profile_read()     -> cumulative milliseconds and timed runs per stage (a stage that
+ *                              runs several times per call, e.g. one setup launch per depth
+ *                              bucket, counts each run)
  * Stage order: see dirt_profile_stage_name(i), i in [0, DIRT_STAGE_COUNT). */
-#define DIRT_STAGE_COUNT 10
+#define DIRT_STAGE_COUNT 12
 DIRT_API int dirt_profile_enable(int enable);
 DIRT_API int dirt_profile_collect(void);
 DIRT_API int dirt_profile_read(double *total_ms, uint64_t *calls, int n);

@@ -199,10 +199,9 @@ def random_triangles(B, H, W, C, F, seed, size=0.5, depth_ties=False, w_range=(0
     return _pack(bg, v, cols, faces)
 
 
-def near_crossing(B=2, H=96, W=128, C=3, seed=5):
+def near_crossing(B=2, H=96, W=128, C=3, seed=5, n=24):
     """A ground-plane grid the camera stands on: many faces cross the near plane or lie behind
     the camera (w <= 0), the config-c5 situation."""
-    n = 24
     xs, zs = np.meshgrid(np.linspace(-6, 6, n), np.linspace(-12, 3, n), indexing="ij")
     rng = np.random.RandomState(seed)
     verts = np.stack([xs, -0.7 + 0.15 * rng.randn(n, n), zs], -1).reshape(-1, 3)

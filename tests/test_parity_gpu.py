@@ -229,3 +229,31 @@ def test_host_buffer_entry_points():
     assert np.abs(gv - ogv).max() <= GRAD_RTOL * np.abs(ogv).max()
     assert np.abs(gc - ogc).max() <= GRAD_RTOL * np.abs(ogc).max()
     _lib.check(lib.dirt_release_host_staging())
+
+
+_PLAN_CHECK = """
+import sys
+sys.path[:0] = [{root!r}, {tests!r}]
+import scenes, test_parity_gpu as t
+t._check_forward(scenes.sphere(2, 192, 160, n_lat=80, n_lon=80))
+t._check_forward(scenes.random_triangles(2, 200, 136, 3, 6000, seed=11, size=0.12, depth_ties=True))
+t._check_forward(scenes.near_crossing(n=56))      # 6050 faces, many clipped by the near / far plane
+print("plan ok")
+"""
+
+
+@pytest.mark.parametrize("plan", ["0", "1", "0.5,1", "0.05,0.1,0.2,0.3,0.4,0.6,0.8,1"])
+def test_depth_bucket_plans_do_not_change_the_result(plan):
+    """Meshes of >= 4096 faces are sampled front to back in depth buckets, with triangles hidden
+    behind the depth pyramid dropped (dirt_b200/csrc/depth_order.cu).  The cull is conservative by
+    construction, so every plan -- unordered ("0"), one ordered pass, two and eight buckets --
+    must reproduce the oracle bit for bit (face ids, window depth), depth ties included.  The
+    plan is read once per process, hence the subprocess."""
+    import os
+    import subprocess
+    import sys
+    tests = os.path.dirname(os.path.abspath(__file__))
+    env = dict(os.environ, DIRT_B200_BUCKETS=plan)
+    r = subprocess.run([sys.executable, "-c", _PLAN_CHECK.format(root=os.path.dirname(tests), tests=tests)],
+                       env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and "plan ok" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]

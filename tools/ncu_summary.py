@@ -20,6 +20,13 @@ METRICS = [
 UNIT_BYTES = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
 
 
+def short_name(full):
+    """`void dirt::<unnamed>::k_setup<1>(dirt::FwdParams, int)` -> `k_setup<1>`; library kernels keep their name."""
+    base = full.split("(")[0].replace("void ", "")
+    i = base.find("k_")
+    return base[i:] if i >= 0 and not base.startswith("at::") else base
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--rep")
@@ -35,7 +42,7 @@ def main():
         for r in csv.DictReader(l for l in open(a.launches) if l.startswith('"')):
             if r.get("Metric Name") != "gpu__time_duration.sum":
                 continue
-            k = r["Kernel Name"].split("(")[0].replace("dirt::", "").replace("void ", "")
+            k = short_name(r["Kernel Name"])
             t = tot.setdefault(k, [0, 0.0])
             t[0] += 1
             t[1] += float(r["Metric Value"].replace(",", "")) * {"ns": 1e-3, "us": 1.0, "ms": 1e3}.get(r["Metric Unit"], 1e-3)
@@ -49,9 +56,9 @@ def main():
         raw = subprocess.run(["ncu", "-i", a.rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
         rows = list(csv.reader(io.StringIO(raw)))
         hdr, units = rows[0], rows[1]
-        lines += ["## `ncu --set full --clock-control none` (one launch per kernel)", ""]
+        lines += ["## `ncu --set full --clock-control none` (the launches of one step)", ""]
         for r in rows[2:]:
-            name = r[hdr.index("Kernel Name")].split("(")[0].replace("dirt::", "").replace("void ", "")
+            name = short_name(r[hdr.index("Kernel Name")])
             lines += ["### `%s`" % name, "", "| metric | value | unit |", "|---|---:|---|"]
             rd = wr = 0.0
             for m in METRICS:
@@ -62,7 +69,8 @@ def main():
                         rd = float(r[i].replace(",", "")) * UNIT_BYTES.get(units[i], 1)
                     if m == "dram__bytes_write.sum":
                         wr = float(r[i].replace(",", "")) * UNIT_BYTES.get(units[i], 1)
-            traffic["k_" + name.split("<")[0].replace("k_", "")] = rd + wr
+            key = "k_" + name.split("<")[0].replace("k_", "")
+            traffic[key] = traffic.get(key, 0.0) + rd + wr          # capture one step: launches of a kernel add up
             lines.append("")
     open(a.out, "w").write("\n".join(lines) + "\n")
     if a.traffic:

@@ -61,7 +61,7 @@ def main():
         for _ in range(5):
             step(); torch.cuda.synchronize(); lib.dirt_profile_collect()
         lib.dirt_profile_enable(0)
-        st = {k: m / max(c, 1) for k, (m, c) in _lib.stage_times().items()}
+        st = {k: m / 5 for k, (m, c) in _lib.stage_times().items()}      # per step
         print("%-9s B=%d %dx%d F=%d  step %.3f ms  %.0f Mpix/s | %s" % (
             name, B, H, W, sc["faces"].shape[1], ms, B * H * W / ms / 1e3,
             " ".join("%s=%.3f" % (k, v) for k, v in st.items())), flush=True)
