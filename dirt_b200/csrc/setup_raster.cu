@@ -67,18 +67,24 @@ __global__ void __launch_bounds__(256) k_project(FwdParams p, int nbatch)
 // ---------------------------------------------------------------------------------------
 // Shared-memory record of a triangle being sampled by the warp: five 16-byte rows, read with
 // LDS.128 (20-word stride: the 8 lanes of a quarter-warp phase hit disjoint bank groups).
-//   row 0: A0 A1 A2 org      A_k = sign-normalised edge value at line 0, position 0, plus the tie
-//                            bias (inside: >= 0); org = xmin | ymin << 16
+// The three edges are stored in SLOT order: slot 0 is an edge whose value grows along a line
+// (it bounds the span from below), slot 1 one that falls (bounds it from above), slot 2 the
+// remaining edge of either kind -- the steps of a triangle's edges along any direction sum to
+// zero, so a non-degenerate triangle always has one of each.
+//   row 0: A0 A1 A2 base_lo  A_k = sign-normalised edge value at line 0, position 0, plus the tie
+//                            bias (inside: >= 0); base = key index of pixel (xmin, ymin)
 //   row 1: sa0 sa1 sa2 dims  sa_k = edge step per +1 position ALONG a line; dims = m1 | axis << 8
 //                            (m1 = last position of a line; axis 1: lines are columns)
 //   row 2: sc0 sc1 sc2 face  sc_k = edge step per +1 line
-//   row 3: inv0 inv1 inv2 elem   inv_k = 256 / |sa_k| as float (0 when sa_k == 0)
+//   row 3: inv0 inv1 inv2 base_hi   inv_k = 256 / |sa_k| as float (0 when sa_k == 0)
 //   row 4: zref dzdx dzdy -
 constexpr int kRecWords = 20;
 
+__device__ __forceinline__ uint32_t pick3(const uint32_t (&v)[3], int i) { return i == 0 ? v[0] : (i == 1 ? v[1] : v[2]); }
+
 // Fills the record of a triangle whose extents are below kSmallExtent (int32 edge math).
 // Returns the number of lines.
-__device__ __forceinline__ int write_record(uint32_t *rec, const TriSetup &t, uint32_t face, uint32_t elem)
+__device__ __forceinline__ int write_record(uint32_t *rec, const TriSetup &t, uint32_t face, uint32_t elem, int H, int W)
 {
     const int cx = t.xmin * kSubpix + kSubpixHalf, cy = t.ymin * kSubpix + kSubpixHalf;
     const int sg = t.sign;
@@ -100,11 +106,15 @@ __device__ __forceinline__ int write_record(uint32_t *rec, const TriSetup &t, ui
         const int mag = (along < 0 ? -along : along) >> 8;           // |ey| or |ex|
         inv[k] = __float_as_uint(mag != 0 ? __frcp_rn((float)mag) : 0.0f);
     }
+    const int up = (int)sa[0] > 0 ? 0 : ((int)sa[1] > 0 ? 1 : 2);        // slot 0: a rising edge
+    const int dn = (int)sa[0] < 0 ? 0 : ((int)sa[1] < 0 ? 1 : 2);        // slot 1: a falling edge
+    const int re = 3 - up - dn;
+    const unsigned long long base = ((unsigned long long)elem * H + (unsigned)(H - 1 - t.ymin)) * W + (unsigned)t.xmin;
     uint4 *row = reinterpret_cast<uint4 *>(rec);
-    row[0] = make_uint4(A[0], A[1], A[2], (uint32_t)t.xmin | ((uint32_t)t.ymin << 16));
-    row[1] = make_uint4(sa[0], sa[1], sa[2], (uint32_t)((axis ? bh : bw) - 1) | ((uint32_t)axis << 8));
-    row[2] = make_uint4(sc[0], sc[1], sc[2], face);
-    row[3] = make_uint4(inv[0], inv[1], inv[2], elem);
+    row[0] = make_uint4(pick3(A, up), pick3(A, dn), pick3(A, re), (uint32_t)base);
+    row[1] = make_uint4(pick3(sa, up), pick3(sa, dn), pick3(sa, re), (uint32_t)((axis ? bh : bw) - 1) | ((uint32_t)axis << 8));
+    row[2] = make_uint4(pick3(sc, up), pick3(sc, dn), pick3(sc, re), face);
+    row[3] = make_uint4(pick3(inv, up), pick3(inv, dn), pick3(inv, re), (uint32_t)(base >> 32));
     row[4] = make_uint4(__float_as_uint(t.zref), __float_as_uint(t.dzdx), __float_as_uint(t.dzdy), 0u);
     return axis ? bw : bh;
 }
@@ -129,38 +139,39 @@ __device__ __forceinline__ void sample_line(const uint32_t *rec, int j, const Fw
 {
     const uint4 *row = reinterpret_cast<const uint4 *>(rec);
     const uint4 rA = row[0], rSA = row[1], rSC = row[2], rINV = row[3];
-    const uint32_t org = rA.w, face = rSC.w, elem = rINV.w;
+    const uint32_t face = rSC.w;
     const int axis = (int)(rSA.w >> 8), m1 = (int)(rSA.w & 0xFFu);      // m1: last position along the line
-    const int A[3] = {(int)rA.x, (int)rA.y, (int)rA.z}, SA[3] = {(int)rSA.x, (int)rSA.y, (int)rSA.z};
-    const int SC[3] = {(int)rSC.x, (int)rSC.y, (int)rSC.z};
-    const float INV[3] = {__uint_as_float(rINV.x), __uint_as_float(rINV.y), __uint_as_float(rINV.z)};
     const float fj = __int2float_rn(j);
-    int lo = 0, hi = m1;
-#pragma unroll
-    for (int k = 0; k < 3; ++k) {
-        // Edge k along the line: a + sa * c >= 0 with sa = +-256 * s.  The bound on c is
-        // ceil(na / s) with na = ceil(-a / 256) (nested ceilings), and
-        // ceil((float(na) - 0.5) * (1 / s)) evaluates it EXACTLY in floating point: |na| < 2^22
-        // (kSmallExtent) keeps the rounding error below the 0.5 / s that separates the shifted
-        // quotient from the nearest integers (checked exhaustively-at-random in tests/test_span_math.py),
-        // so coverage is still decided by integer arithmetic alone.
-        const int sa = SA[k];
-        const int a = A[k] + SC[k] * j;              // edge value (+ bias) at position 0 of this line
+    // Edge along the line: a + sa * c >= 0 with sa = +-256 * s.  The bound on c is
+    // ceil(na / s) with na = ceil(-a / 256) (nested ceilings), and
+    // ceil((float(na) - 0.5) * (1 / s)) evaluates it EXACTLY in floating point: |na| < 2^22
+    // (kSmallExtent) keeps the rounding error below the 0.5 / s that separates the shifted
+    // quotient from the nearest integers (checked exhaustively-at-random in tests/test_span_math.py),
+    // so coverage is still decided by integer arithmetic alone.
+    auto bound = [&](uint32_t A, uint32_t SC, uint32_t INV, int &a) {
+        a = (int)A + (int)SC * j;                    // edge value (+ bias) at position 0 of this line
         const int na = (255 - a) >> 8;
-        const int m = __float2int_ru(fmul(fadd(__int2float_rn(na), -0.5f), INV[k]));
-        if (sa > 0) lo = max(lo, m);                 // smallest c inside
-        else if (sa < 0) hi = min(hi, -m);           // largest c inside
-        else if (a < 0) hi = -1;
+        return __float2int_ru(fmul(fadd(__int2float_rn(na), -0.5f), __uint_as_float(INV)));
+    };
+    int a0, a1, a2;
+    int lo = max(0, bound(rA.x, rSC.x, rINV.x, a0));         // slot 0 rises: smallest c inside
+    int hi = min(m1, -bound(rA.y, rSC.y, rINV.y, a1));       // slot 1 falls: largest c inside
+    {
+        const int sa = (int)rSA.z, m = bound(rA.z, rSC.z, rINV.z, a2);
+        if (sa > 0) lo = max(lo, m);
+        else if (sa < 0) hi = min(hi, -m);
+        else if (a2 < 0) hi = -1;
     }
     if (lo > hi) return;
     const uint4 rZ = row[4];
-    const int xmin = (int)(org & 0xFFFFu), ymin = (int)(org >> 16);
     const float zref = __uint_as_float(rZ.x), dzdx = __uint_as_float(rZ.y), dzdy = __uint_as_float(rZ.z);
     // zw = (zref + dzdx * dx) + dzdy * dy, the operation order of plane_depth()
     const float c1 = fadd(zref, fmul(dzdx, fj));     // axis 1: dx = j is fixed
     const float c2 = fmul(dzdy, fj);                 // axis 0: dy = j is fixed
-    const int px0 = axis ? xmin + j : xmin + lo, py0 = axis ? ymin + lo : ymin + j;
-    unsigned long long *kp = p.keys + ((size_t)elem * p.H + (size_t)(p.H - 1 - py0)) * p.W + px0;
+    // pixel (xmin + dx, ymin + dy) has key index base + dx - dy * W (tensor rows run downwards)
+    const long long base = (long long)(((unsigned long long)rINV.w << 32) | rA.w);
+    const int off = axis ? j - lo * p.W : lo - j * p.W;
+    unsigned long long *kp = p.keys + (base + off);
     const long long stride = axis ? -(long long)p.W : 1ll;
     float fi = __int2float_rn(lo);
     // kFragRound fragments per round: their current depths are fetched together (independent
@@ -282,7 +293,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
 #endif
                     } else if (ex < kSmallExtent && ey < kSmallExtent && (t.rcp_area > kLineRcpAreaMin || (t.xmax - t.xmin + 1) * (t.ymax - t.ymin + 1) <= 256))
                         // few-but-fat triangles are better off pixel-parallel in the tile path
-                        nlines = write_record(recs + lane * kRecWords, t, (uint32_t)f, (uint32_t)b);
+                        nlines = write_record(recs + lane * kRecWords, t, (uint32_t)f, (uint32_t)b, p.H, p.W);
                     else
                         push_big(t, b, (uint32_t)f, 0u, p);
                 } else if (slow) {
