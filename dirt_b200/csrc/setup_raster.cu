@@ -73,8 +73,8 @@ __global__ void __launch_bounds__(256) k_project(FwdParams p, int nbatch)
 // zero, so a non-degenerate triangle always has one of each.
 //   row 0: A0 A1 A2 base_lo  A_k = sign-normalised edge value at line 0, position 0, plus the tie
 //                            bias (inside: >= 0); base = key index of pixel (xmin, ymin)
-//   row 1: sa0 sa1 sa2 dims  sa_k = edge step per +1 position ALONG a line; dims = m1 | axis << 8
-//                            (m1 = last position of a line; axis 1: lines are columns)
+//   row 1: sa0 sa1 sa2 dims  sa_k = edge step per +1 position ALONG a line; dims = m1 | axis << 8 |
+//                            first_line << 9 (m1 = last position of a line; axis 1: lines are columns)
 //   row 2: sc0 sc1 sc2 face  sc_k = edge step per +1 line
 //   row 3: inv0 inv1 inv2 base_hi   inv_k = 256 / |sa_k| as float (0 when sa_k == 0)
 //   row 4: zref dzdx dzdy -
@@ -82,9 +82,9 @@ constexpr int kRecWords = 20;
 
 __device__ __forceinline__ uint32_t pick3(const uint32_t (&v)[3], int i) { return i == 0 ? v[0] : (i == 1 ? v[1] : v[2]); }
 
-// Fills the record of a triangle whose extents are below kSmallExtent (int32 edge math).
-// Returns the number of lines.
-__device__ __forceinline__ int write_record(uint32_t *rec, const TriSetup &t, uint32_t face, uint32_t elem, int H, int W)
+// Fills the record of a triangle whose extents are below kSmallExtent (int32 edge math) and
+// returns its dims word; the caller adds first_line once the warp's line counts are summed.
+__device__ __forceinline__ uint32_t write_record(uint32_t *rec, const TriSetup &t, uint32_t face, uint32_t elem, int H, int W)
 {
     const int cx = t.xmin * kSubpix + kSubpixHalf, cy = t.ymin * kSubpix + kSubpixHalf;
     const int sg = t.sign;
@@ -112,11 +112,12 @@ __device__ __forceinline__ int write_record(uint32_t *rec, const TriSetup &t, ui
     const unsigned long long base = ((unsigned long long)elem * H + (unsigned)(H - 1 - t.ymin)) * W + (unsigned)t.xmin;
     uint4 *row = reinterpret_cast<uint4 *>(rec);
     row[0] = make_uint4(pick3(A, up), pick3(A, dn), pick3(A, re), (uint32_t)base);
-    row[1] = make_uint4(pick3(sa, up), pick3(sa, dn), pick3(sa, re), (uint32_t)((axis ? bh : bw) - 1) | ((uint32_t)axis << 8));
+    const uint32_t dims = (uint32_t)((axis ? bh : bw) - 1) | ((uint32_t)axis << 8);
+    row[1] = make_uint4(pick3(sa, up), pick3(sa, dn), pick3(sa, re), dims);
     row[2] = make_uint4(pick3(sc, up), pick3(sc, dn), pick3(sc, re), face);
     row[3] = make_uint4(pick3(inv, up), pick3(inv, dn), pick3(inv, re), (uint32_t)(base >> 32));
     row[4] = make_uint4(__float_as_uint(t.zref), __float_as_uint(t.dzdx), __float_as_uint(t.dzdy), 0u);
-    return axis ? bw : bh;
+    return dims;
 }
 
 // 64-bit minimum without a return value, explicitly in the global space.
@@ -133,14 +134,16 @@ __device__ __forceinline__ uint32_t load_depth_word(const unsigned long long *kp
     return v;
 }
 
-// Samples line `j` of the triangle in `rec` (a row when axis == 0, a column when axis == 1).
+// Samples line `g` of the warp's batch, a line of the triangle in `rec` (a row when axis == 0,
+// a column when axis == 1).
 template <bool PRELOAD>
-__device__ __forceinline__ void sample_line(const uint32_t *rec, int j, const FwdParams &p)
+__device__ __forceinline__ void sample_line(const uint32_t *rec, int g, const FwdParams &p)
 {
     const uint4 *row = reinterpret_cast<const uint4 *>(rec);
     const uint4 rA = row[0], rSA = row[1], rSC = row[2], rINV = row[3];
     const uint32_t face = rSC.w;
-    const int axis = (int)(rSA.w >> 8), m1 = (int)(rSA.w & 0xFFu);      // m1: last position along the line
+    const int axis = (int)(rSA.w >> 8) & 1, m1 = (int)(rSA.w & 0xFFu);      // m1: last position along the line
+    const int j = g - (int)(rSA.w >> 9);
     const float fj = __int2float_rn(j);
     // Edge along the line: a + sa * c >= 0 with sa = +-256 * s.  The bound on c is
     // ceil(na / s) with na = ceil(-a / 256) (nested ceilings), and
@@ -252,8 +255,10 @@ template <bool ORDERED>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdParams p, int bucket, int use_hiz)
 {
     __shared__ __align__(16) uint32_t s_recs[kWarpsPerCta][32 * kRecWords];
+    __shared__ uint8_t s_owner[kWarpsPerCta][32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t *recs = s_recs[warp];
+    uint8_t *owner_lane = s_owner[warp];
     long long first_entry = 0, total = (long long)p.B * p.F;
     if (ORDERED) {
         first_entry = p.bucket_base[bucket];
@@ -272,7 +277,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
         const long long i = i0 + lane;
         if (lane == 0) claim = atomicAdd(work, 32ull);
         // ---- setup: one face per lane -------------------------------------------------------
-        int nlines = 0;
+        int nlines = 0;                  // > 0: this lane's face is line-sampled by the warp
+        uint32_t dims = 0;
         if (i < total) {
             const long long flat = ORDERED ? (long long)p.order[first_entry + i] : i;
             const int b = (int)(flat / p.F), f = (int)(flat - (long long)b * p.F);
@@ -292,9 +298,10 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
                         atomicAdd(p.counters + 5, (uint32_t)max(t.xmax - t.xmin + 1, t.ymax - t.ymin + 1));
 #endif
                     } else if (ex < kSmallExtent && ey < kSmallExtent && (t.rcp_area > kLineRcpAreaMin || (t.xmax - t.xmin + 1) * (t.ymax - t.ymin + 1) <= 256))
-                        // few-but-fat triangles are better off pixel-parallel in the tile path
-                        nlines = write_record(recs + lane * kRecWords, t, (uint32_t)f, (uint32_t)b, p.H, p.W);
-                    else
+                    {   // few-but-fat triangles are better off pixel-parallel in the tile path
+                        nlines = max(t.xmax - t.xmin, t.ymax - t.ymin) + 1;     // the longer side of the bounding box
+                        dims = write_record(recs + lane * kRecWords, t, (uint32_t)f, (uint32_t)b, p.H, p.W);
+                    } else
                         push_big(t, b, (uint32_t)f, 0u, p);
                 } else if (slow) {
                     // a private copy: taking the address of the kernel parameter block itself would move
@@ -304,10 +311,14 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
                 }
             }
         }
+        // the r-th line-sampled face of the batch, in lane order, is the face of lane owner_lane[r]
+        const bool sampled = nlines > 0;
+        const unsigned owners = __ballot_sync(kFullMask, sampled);
+        if (sampled) owner_lane[__popc(owners & ((1u << lane) - 1u))] = (uint8_t)lane;
 #ifdef DIRT_STATS
         if (nlines) { atomicAdd(p.counters + 6, 1u); atomicAdd(p.counters + 7, (uint32_t)nlines); }
 #endif
-        // ---- sampling: 32 lines at a time ---------------------------------------------------
+        // running sum of the line counts over the warp: record r owns lines excl .. excl + nlines - 1
         int incl = nlines;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -315,21 +326,24 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
             if (lane >= o) incl += n;
         }
         const int nall = __shfl_sync(kFullMask, incl, 31);
+        const int excl = incl - nlines;
+        if (sampled) recs[lane * kRecWords + 7] = dims | ((uint32_t)excl << 9);
         __syncwarp();
+        // ---- sampling: 32 lines at a time ---------------------------------------------------
+        // Line g belongs to the last record that starts at or before g.  Records start at
+        // distinct lines (every record has at least one), so one OR-reduction of "my record
+        // starts at line base + d" bits and two population counts find the owner of every lane.
+        const unsigned upto_lane = (2u << lane) - 1u;
         for (int base = 0; base < nall; base += 32) {
+            const int d = excl - base;
+            const unsigned starts = __reduce_or_sync(kFullMask, (sampled && (unsigned)d < 32u) ? 1u << d : 0u);
+            const int before = __popc(__ballot_sync(kFullMask, sampled && d < 0));
             const int g = base + lane;
-            // owner of line g: the number of lanes whose inclusive count is <= g
-            int t = 0;
-#pragma unroll
-            for (int s = 16; s >= 1; s >>= 1) {
-                const int v = __shfl_sync(kFullMask, incl, (t + s - 1) & 31);
-                if (v <= g) t += s;
-            }
-            const int first = __shfl_sync(kFullMask, incl - nlines, t & 31);
             if (g < nall) {
+                const uint32_t *rec = recs + owner_lane[before + __popc(starts & upto_lane) - 1] * kRecWords;
                 // nearest bucket: nearly every fragment wins, reading the depth first only adds latency
-                if (KPRE0 == 0 && ORDERED && !use_hiz) sample_line<false>(recs + t * kRecWords, g - first, p);
-                else sample_line<true>(recs + t * kRecWords, g - first, p);
+                if (KPRE0 == 0 && ORDERED && !use_hiz) sample_line<false>(rec, g, p);
+                else sample_line<true>(rec, g, p);
             }
         }
         __syncwarp();     // the records are about to be overwritten
