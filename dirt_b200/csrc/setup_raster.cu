@@ -30,7 +30,7 @@ constexpr int kWarpsPerCta = 8;
 #define KCTAS 6
 #endif
 #ifndef KFRAG
-#define KFRAG 4
+#define KFRAG 2
 #endif
 #ifndef KPRE0
 #define KPRE0 0
@@ -168,9 +168,12 @@ __device__ __forceinline__ void sample_line(const uint32_t *rec, int g, const Fw
     if (lo > hi) return;
     const uint4 rZ = row[4];
     const float zref = __uint_as_float(rZ.x), dzdx = __uint_as_float(rZ.y), dzdy = __uint_as_float(rZ.z);
-    // zw = (zref + dzdx * dx) + dzdy * dy, the operation order of plane_depth()
-    const float c1 = fadd(zref, fmul(dzdx, fj));     // axis 1: dx = j is fixed
-    const float c2 = fmul(dzdy, fj);                 // axis 0: dy = j is fixed
+    // zw = (zref + dzdx * dx) + dzdy * dy, the operation order of plane_depth(), written for both
+    // axes as (zp + zq * fi) + zr with fi the position along the line: rows have dy = j fixed,
+    // columns dx = j (adding zr = 0 is exact).
+    const float zp = axis ? fadd(zref, fmul(dzdx, fj)) : zref;
+    const float zq = axis ? dzdy : dzdx;
+    const float zr = axis ? 0.0f : fmul(dzdy, fj);
     // pixel (xmin + dx, ymin + dy) has key index base + dx - dy * W (tensor rows run downwards)
     const long long base = (long long)(((unsigned long long)rINV.w << 32) | rA.w);
     const int off = axis ? j - lo * p.W : lo - j * p.W;
@@ -188,7 +191,7 @@ __device__ __forceinline__ void sample_line(const uint32_t *rec, int g, const Fw
 #pragma unroll
         for (int u = 0; u < kFragRound; ++u) {
             if (u < n) {
-                float zw = axis ? fadd(c1, fmul(dzdy, fi)) : fadd(fadd(zref, fmul(dzdx, fi)), c2);
+                float zw = fadd(fadd(zp, fmul(zq, fi)), zr);
                 zw = fminf(fmaxf(zw, 0.0f), 1.0f);
                 const uint32_t d = __float2uint_rz(fadd(fmul(zw, 16777215.0f), 0.5f));
                 // keys only ever decrease, so a stale depth can only cost a redundant atomic;
