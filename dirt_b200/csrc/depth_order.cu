@@ -29,24 +29,44 @@ constexpr unsigned kFull = 0xFFFFFFFFu;
 constexpr int kSamples = 256;
 
 // Nearest corner depth of a face; 0 (first bucket, never culled) for faces on the general path.
-__device__ __forceinline__ float face_near_depth(const FwdParams &p, int b, int f)
+// `frags` (optional) receives an estimate of the fragments the face generates.
+__device__ __forceinline__ float face_near_depth(const FwdParams &p, int b, int f, float *frags = nullptr)
 {
+    if (frags) *frags = 0.0f;
     const int32_t *fp = p.faces + (int64_t)b * p.faces_bs + 3 * (int64_t)f;
     const int i0 = __ldg(fp), i1 = __ldg(fp + 1), i2 = __ldg(fp + 2);
     if ((unsigned)i0 >= (unsigned)p.V || (unsigned)i1 >= (unsigned)p.V || (unsigned)i2 >= (unsigned)p.V) return 0.0f;
     const int4 *pp = proj_ptr(p, b);
     const int4 a = __ldg(pp + i0), c = __ldg(pp + i1), d = __ldg(pp + i2);
     if (a.x == kProjSlow || c.x == kProjSlow || d.x == kProjSlow) return 0.0f;
+    if (frags) {
+        TriSetup t;
+        bool slow;
+        if (setup_from_proj(a, c, d, p.W, p.H, t, slow)) {
+            // area in pixels, but no more than the part of the bounding box inside the image
+            const float area = 0.5f / (t.rcp_area * (float)(kSubpix * kSubpix));
+            *frags = fminf(area, (float)((t.xmax - t.xmin + 1) * (t.ymax - t.ymin + 1)));
+        }
+    }
     return fminf(__int_as_float(a.z), fminf(__int_as_float(c.z), __int_as_float(d.z)));
 }
 
 __global__ void __launch_bounds__(kSamples) k_depth_pivots(FwdParams p, BucketPlan plan)
 {
     __shared__ float s_z[kSamples];
+    __shared__ float s_frags;
     const int b = blockIdx.x, t = threadIdx.x;
     const int f = (int)(((long long)t * p.F) / kSamples);
-    s_z[t] = face_near_depth(p, b, f);
+    if (t == 0) s_frags = 0.0f;
     __syncthreads();
+    float frags;
+    s_z[t] = face_near_depth(p, b, f, &frags);
+    for (int o = 16; o >= 1; o >>= 1) frags += __shfl_xor_sync(kFull, frags, o);
+    if ((t & 31) == 0) atomicAdd(&s_frags, frags);
+    __syncthreads();
+    // fragments per pixel of this element, extrapolated from the sample; summed over the batch
+    if (t == 0)
+        atomicAdd(reinterpret_cast<float *>(p.counters + kCtrOverdraw), s_frags * ((float)p.F / kSamples) / ((float)p.H * (float)p.W));
     // bitonic sort, ascending
     for (int k = 2; k <= kSamples; k <<= 1)
         for (int j = k >> 1; j > 0; j >>= 1) {
@@ -76,8 +96,9 @@ constexpr int kChunkFaces = 2048;          // faces of ONE element per CTA in cl
 
 // blockIdx.y = element, blockIdx.x = chunk of kChunkFaces faces.  Counts go through shared
 // memory: kMaxBuckets global reductions per CTA instead of one per warp and bucket.
-__global__ void __launch_bounds__(256) k_depth_classify(FwdParams p, int nb)
+__global__ void __launch_bounds__(256) k_depth_classify(FwdParams p, int nb, float min_overdraw)
 {
+    if (!plan_is_ordered(p, min_overdraw)) return;
     __shared__ uint32_t s_cnt[kMaxBuckets];
     __shared__ float s_pv[kMaxBuckets];
     const int b = blockIdx.y, t = threadIdx.x;
@@ -94,8 +115,9 @@ __global__ void __launch_bounds__(256) k_depth_classify(FwdParams p, int nb)
 }
 
 // Exclusive scan of bucket_count (bucket-major) -> bucket_cursor; bucket_base[k] = start of bucket k.
-__global__ void __launch_bounds__(1024) k_depth_offsets(FwdParams p, int nb)
+__global__ void __launch_bounds__(1024) k_depth_offsets(FwdParams p, int nb, float min_overdraw)
 {
+    if (!plan_is_ordered(p, min_overdraw)) return;
     __shared__ uint32_t s_part[1024];
     const int n = nb * p.B, t = threadIdx.x;
     const int per = (n + 1023) / 1024;
@@ -121,8 +143,9 @@ __global__ void __launch_bounds__(1024) k_depth_offsets(FwdParams p, int nb)
 
 // Same chunks as k_depth_classify: a CTA reserves one range per bucket and fills it with its
 // flat face numbers (ranks inside the CTA come from shared-memory counters).
-__global__ void __launch_bounds__(256) k_depth_scatter(FwdParams p, int nb)
+__global__ void __launch_bounds__(256) k_depth_scatter(FwdParams p, int nb, float min_overdraw)
 {
+    if (!plan_is_ordered(p, min_overdraw)) return;
     __shared__ uint32_t s_cnt[kMaxBuckets], s_base[kMaxBuckets];
     const int b = blockIdx.y, t = threadIdx.x;
     if (t < kMaxBuckets) s_cnt[t] = 0;
@@ -150,8 +173,9 @@ __global__ void __launch_bounds__(256) k_depth_scatter(FwdParams p, int nb)
 
 // Depth pyramid of one 64 x 64 pixel block per CTA: warp w reduces pixel rows 8w .. 8w+7 to
 // eight 8x8 tiles, then levels 1..3 are reduced from shared memory.
-__global__ void __launch_bounds__(256) k_hiz_build(FwdParams p)
+__global__ void __launch_bounds__(256) k_hiz_build(FwdParams p, float min_overdraw)
 {
+    if (!plan_is_ordered(p, min_overdraw)) return;
     __shared__ uint32_t s_t[8][8], s_u[4][4], s_v[2][2];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int bx = blockIdx.x, by = blockIdx.y, b = blockIdx.z;
@@ -202,14 +226,18 @@ __global__ void __launch_bounds__(256) k_hiz_build(FwdParams p)
 
 // Cumulative face fractions of the buckets.  DIRT_B200_BUCKETS="0.1,0.3,1" overrides the
 // default (tuning aid); "1" selects a single ordered pass, "0" the unordered single pass.
+// DIRT_B200_MIN_OVERDRAW overrides the estimated fragments-per-pixel threshold below which the
+// kernels of an ordered plan fall back to one unordered pass (0 = always ordered).
 BucketPlan bucket_plan()
 {
     static const BucketPlan plan = [] {
         BucketPlan q;
-        q.n = 3; q.upto[0] = 0.1f; q.upto[1] = 0.3f; q.upto[2] = 1.0f;
+        q.min_overdraw = 4.0f;
+        if (const char *e = std::getenv("DIRT_B200_MIN_OVERDRAW")) q.min_overdraw = std::strtof(e, nullptr);
+        q.n = 2; q.upto[0] = 0.35f; q.upto[1] = 1.0f;       // measured best on the 100k-face workloads (profiles/r1_setup_notes.md)
         if (const char *e = std::getenv("DIRT_B200_BUCKETS")) {
             if (e[0] == '0' && e[1] == 0) { q.n = 0; return q; }
-            BucketPlan r; r.n = 0;
+            BucketPlan r; r.n = 0; r.min_overdraw = q.min_overdraw;
             float last = 0.0f;
             while (*e && r.n < kMaxBuckets) {
                 char *end = nullptr;
@@ -231,16 +259,16 @@ void launch_depth_order(const FwdParams &p, const BucketPlan &plan, int sm_count
     (void)sm_count;
     const dim3 chunks((unsigned)((p.F + kChunkFaces - 1) / kChunkFaces), (unsigned)p.B);
     k_depth_pivots<<<p.B, kSamples, 0, stream>>>(p, plan);
-    k_depth_classify<<<chunks, 256, 0, stream>>>(p, plan.n);
-    k_depth_offsets<<<1, 1024, 0, stream>>>(p, plan.n);
-    k_depth_scatter<<<chunks, 256, 0, stream>>>(p, plan.n);
+    k_depth_classify<<<chunks, 256, 0, stream>>>(p, plan.n, plan.min_overdraw);
+    k_depth_offsets<<<1, 1024, 0, stream>>>(p, plan.n, plan.min_overdraw);
+    k_depth_scatter<<<chunks, 256, 0, stream>>>(p, plan.n, plan.min_overdraw);
 }
 
-void launch_hiz_build(const FwdParams &p, int sm_count, cudaStream_t stream)
+void launch_hiz_build(const FwdParams &p, const BucketPlan &plan, int sm_count, cudaStream_t stream)
 {
     (void)sm_count;
     const dim3 g((unsigned)((p.W + 63) / 64), (unsigned)((p.H + 63) / 64), (unsigned)p.B);
-    k_hiz_build<<<g, 256, 0, stream>>>(p);
+    k_hiz_build<<<g, 256, 0, stream>>>(p, plan.min_overdraw);
 }
 
 }  // namespace dirt

@@ -47,6 +47,14 @@ __device__ __forceinline__ const int4 *proj_ptr(const FwdParams &p, int b)
     return p.proj + (int64_t)b * p.proj_bs;
 }
 
+// The depth-ordered passes (depth_order.cu) pay off only where faces hide one another.
+// k_depth_pivots leaves the batch sum of the per-element estimates of fragments per pixel in
+// counters[kCtrOverdraw]; every later kernel of the forward pass reads the same verdict.
+__device__ __forceinline__ bool plan_is_ordered(const FwdParams &p, float min_overdraw)
+{
+    return __uint_as_float(p.counters[kCtrOverdraw]) >= min_overdraw * (float)p.B;
+}
+
 // TriSetup from three projected records.  Returns false if culled; `slow` is set when a corner
 // needs the general path (then t is untouched).
 __device__ __forceinline__ bool setup_from_proj(const int4 &a, const int4 &b, const int4 &c, int W, int H,

@@ -7,7 +7,7 @@
 
 namespace dirt {
 
-enum { kCtrBig = 0, kCtrQueue = 1, kCtrCount = 8 };
+enum { kCtrBig = 0, kCtrQueue = 1, kCtrOverdraw = 2, kCtrCount = 8 };   // kCtrOverdraw: float bits, see depth_order.cu
 
 struct FwdParams {
     int B, H, W, C, V, F;
@@ -79,10 +79,13 @@ struct StageTimer {
 
 cudaError_t launch_forward(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_t *launches, StageTimer &tm);
 // depth_order.cu
-struct BucketPlan { int n; float upto[kMaxBuckets]; };       // cumulative face fractions, upto[n-1] = 1
+struct BucketPlan {
+    int n; float upto[kMaxBuckets];      // cumulative face fractions, upto[n-1] = 1
+    float min_overdraw;                  // estimated fragments per pixel below which ordering does not pay
+};
 BucketPlan bucket_plan();
 void launch_depth_order(const FwdParams &p, const BucketPlan &plan, int sm_count, cudaStream_t stream);
-void launch_hiz_build(const FwdParams &p, int sm_count, cudaStream_t stream);
+void launch_hiz_build(const FwdParams &p, const BucketPlan &plan, int sm_count, cudaStream_t stream);
 cudaError_t launch_dilate(const float *x, float *out, int B, int H, int W, int C, int sm_count, cudaStream_t stream);
 cudaError_t launch_dilate_grad(const float *x, const float *grad_out, float *grad_x, int B, int H, int W, int C,
                                int sm_count, cudaStream_t stream);

@@ -255,15 +255,22 @@ __device__ __forceinline__ bool hidden_by_hiz(const FwdParams &p, int b, const T
 // ORDERED: the faces of depth bucket `bucket` (depth_order.cu), tested against the hierarchical
 // depth buffer when `use_hiz`; otherwise all faces in index order.
 template <bool ORDERED>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdParams p, int bucket, int use_hiz)
+__global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdParams p, int bucket, float min_overdraw)
 {
     __shared__ __align__(16) uint32_t s_recs[kWarpsPerCta][32 * kRecWords];
     __shared__ uint8_t s_owner[kWarpsPerCta][32];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t *recs = s_recs[warp];
     uint8_t *owner_lane = s_owner[warp];
+    // ORDERED launches check the verdict of k_depth_pivots: without enough overdraw the launch of
+    // bucket 0 samples every face in index order and the other buckets' launches do nothing.
+    const bool ordered = ORDERED && plan_is_ordered(p, min_overdraw);
+    if (ORDERED && !ordered && bucket > 0) return;
+    const bool use_hiz = ordered && bucket > 0;
+    const bool preload = !ordered || bucket > 0 || KPRE0 != 0;     // nearest bucket: nearly every fragment wins,
+                                                                    // reading the depth first only adds latency
     long long first_entry = 0, total = (long long)p.B * p.F;
-    if (ORDERED) {
+    if (ordered) {
         first_entry = p.bucket_base[bucket];
         total = (long long)p.bucket_base[bucket + 1] - first_entry;
     }
@@ -283,7 +290,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
         int nlines = 0;                  // > 0: this lane's face is line-sampled by the warp
         uint32_t dims = 0;
         if (i < total) {
-            const long long flat = ORDERED ? (long long)p.order[first_entry + i] : i;
+            const long long flat = ordered ? (long long)p.order[first_entry + i] : i;
             const int b = (int)(flat / p.F), f = (int)(flat - (long long)b * p.F);
             const int32_t *fp = p.faces + (int64_t)b * p.faces_bs + 3 * (int64_t)f;
             const int i0 = __ldg(fp), i1 = __ldg(fp + 1), i2 = __ldg(fp + 2);
@@ -294,7 +301,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
                 if (setup_from_proj(__ldg(pp + i0), __ldg(pp + i1), __ldg(pp + i2), p.W, p.H, t, slow)) {
                     const int ex = max(t.X0, max(t.X1, t.X2)) - min(t.X0, min(t.X1, t.X2));
                     const int ey = max(t.Y0, max(t.Y1, t.Y2)) - min(t.Y0, min(t.Y1, t.Y2));
-                    if (ORDERED && use_hiz && hidden_by_hiz(p, b, t)) {
+                    if (use_hiz && hidden_by_hiz(p, b, t)) {
                         // dropped: cannot win any pixel
 #ifdef DIRT_STATS
                         atomicAdd(p.counters + 4, 1u);
@@ -344,9 +351,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
             const int g = base + lane;
             if (g < nall) {
                 const uint32_t *rec = recs + owner_lane[before + __popc(starts & upto_lane) - 1] * kRecWords;
-                // nearest bucket: nearly every fragment wins, reading the depth first only adds latency
-                if (KPRE0 == 0 && ORDERED && !use_hiz) sample_line<false>(rec, g, p);
-                else sample_line<true>(rec, g, p);
+                if (preload) sample_line<true>(rec, g, p);
+                else sample_line<false>(rec, g, p);
             }
         }
         __syncwarp();     // the records are about to be overwritten
@@ -379,11 +385,11 @@ void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_
         for (int k = 0; k < plan.n; ++k) {
             if (k > 0) {
                 tm.begin(kStageHizBuild, stream);
-                launch_hiz_build(p, sm_count, stream);
+                launch_hiz_build(p, plan, sm_count, stream);
                 tm.end(kStageHizBuild, stream);
             }
             tm.begin(kStageSetup, stream);
-            k_setup<true><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, k, k > 0);
+            k_setup<true><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, k, plan.min_overdraw);
             tm.end(kStageSetup, stream);
 #ifdef DIRT_STATS
             uint32_t c[8], bb[kMaxBuckets + 1];
@@ -396,7 +402,7 @@ void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_
         *launches += 4 + 2 * plan.n - 1;
     } else {
         tm.begin(kStageSetup, stream);
-        k_setup<false><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, 0, 0);
+        k_setup<false><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, 0, 0.0f);
         tm.end(kStageSetup, stream);
         *launches += 1;
     }
