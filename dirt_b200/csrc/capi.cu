@@ -44,7 +44,7 @@ inline size_t align_up(size_t v) { return (v + kAlign - 1) / kAlign * kAlign; }
 // Workspace carve-up.  Offsets are a pure function of the shape.
 struct Layout {
     size_t keys, proj, counters, tile_count, tile_cursor, bucket_count, tile_offset, big, queue, total;
-    size_t order, bucket_of, pivots, bucket_cursor, bucket_base, hiz, work_next;
+    size_t order, bucket_of, pivots, bucket_cursor, bucket_base, hiz, work_next, active_tiles;
     uint32_t hiz_off[dirt::kHizLevels];
     size_t zero_bytes;
     uint32_t cap_big;
@@ -79,6 +79,7 @@ Layout workspace_layout(const DirtShape &s)
     L.zero_bytes = off - L.counters;
     off = align_up(off);
     L.tile_offset = off; off = align_up(off + ntiles * sizeof(uint32_t));
+    L.active_tiles = off; off = align_up(off + ntiles * sizeof(uint32_t));
     L.big = off;         off = align_up(off + (size_t)L.cap_big * 16);
     L.queue = off;       off = align_up(off + (size_t)(L.cap_queue + 4) * sizeof(uint32_t));
     // depth-ordered passes (depth_order.cu)
@@ -195,6 +196,7 @@ int dirt_rasterise_forward(const DirtForwardArgs *a, void *stream)
     p.tile_count = reinterpret_cast<uint32_t *>(ws + L.tile_count);
     p.tile_cursor = reinterpret_cast<uint32_t *>(ws + L.tile_cursor);
     p.tile_offset = reinterpret_cast<uint32_t *>(ws + L.tile_offset);
+    p.active_tiles = reinterpret_cast<uint32_t *>(ws + L.active_tiles);
     p.big = ws + L.big;
     p.queue = reinterpret_cast<uint32_t *>(ws + L.queue);
     p.cap_big = L.cap_big; p.cap_queue = L.cap_queue; p.zero_bytes = L.zero_bytes;

@@ -92,6 +92,7 @@ __global__ void __launch_bounds__(256) k_bin_alloc(FwdParams p)
         if (c == 0) continue;
         uint32_t padded = (c + 3u) & ~3u;
         p.tile_offset[i] = atomicAdd(&p.counters[kCtrQueue], padded);
+        p.active_tiles[atomicAdd(&p.counters[kCtrActiveTiles], 1u)] = (uint32_t)i;
     }
 }
 
@@ -132,9 +133,15 @@ __global__ void __launch_bounds__(kTileThreads) k_tile_raster(FwdParams p)
     __shared__ __align__(8) uint64_t s_bar;
 
     const int tiles = p.tiles_x * p.tiles_y;
-    const size_t tile = blockIdx.x;
+    const uint32_t nactive = p.counters[kCtrActiveTiles];
+    if (threadIdx.x == 0) mbar_init(&s_bar, 1);
+    __syncthreads();
+    uint32_t parity = 0;
+    // the CTAs walk the list of tiles that have a queue (k_bin_alloc): most scenes leave most
+    // tiles without large triangles, and a CTA launch per empty tile costs more than the work
+    for (uint32_t at = blockIdx.x; at < nactive; at += gridDim.x) {
+    const size_t tile = p.active_tiles[at];
     const uint32_t count = p.tile_count[tile];
-    if (count == 0) return;
     const int b = (int)(tile / tiles), tl = (int)(tile - (size_t)b * tiles);
     const int ty = tl / p.tiles_x, tx = tl - ty * p.tiles_x;
     const int px = tx * kTile + (threadIdx.x & (kTile - 1)), py = ty * kTile + (threadIdx.x >> 4);
@@ -146,9 +153,6 @@ __global__ void __launch_bounds__(kTileThreads) k_tile_raster(FwdParams p)
     const unsigned long long off = p.tile_offset[tile];
     uint32_t avail = off >= p.cap_queue ? 0u : (uint32_t)min((unsigned long long)count, p.cap_queue - off);
 
-    if (threadIdx.x == 0) mbar_init(&s_bar, 1);
-    __syncthreads();
-    uint32_t parity = 0;
     for (uint32_t base = 0; base < avail; base += kChunk) {
         uint32_t n = min((uint32_t)kChunk, avail - base);
         // (1) queue segment -> shared memory: one bulk async copy (16-byte granules)
@@ -184,6 +188,7 @@ __global__ void __launch_bounds__(kTileThreads) k_tile_raster(FwdParams p)
         __syncthreads();
     }
     if (in_image && best < orig) *keyp = best;
+    }
 }
 
 // Barycentrics of pixel (px, py) on a face that went through the clipper (rare): finds the
@@ -341,7 +346,7 @@ cudaError_t launch_forward(const FwdParams &p, int sm_count, cudaStream_t stream
         k_bin<true><<<sm_count * 4, 256, 0, stream>>>(p);
         tm.end(kStageBinFill, stream);
         tm.begin(kStageTileRaster, stream);
-        k_tile_raster<<<(unsigned)ntiles, kTileThreads, 0, stream>>>(p);
+        k_tile_raster<<<grid_for((long long)ntiles * kTileThreads, kTileThreads, sm_count, 16), kTileThreads, 0, stream>>>(p);
         tm.end(kStageTileRaster, stream);
         *launches += 5;        // k_project is counted here, the setup launches in launch_setup
     }

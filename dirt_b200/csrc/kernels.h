@@ -7,7 +7,7 @@
 
 namespace dirt {
 
-enum { kCtrBig = 0, kCtrQueue = 1, kCtrOverdraw = 2, kCtrCount = 8 };   // kCtrOverdraw: float bits, see depth_order.cu
+enum { kCtrBig = 0, kCtrQueue = 1, kCtrOverdraw = 2, kCtrActiveTiles = 3, kCtrCount = 8 };   // kCtrOverdraw: float bits, see depth_order.cu
 
 struct FwdParams {
     int B, H, W, C, V, F;
@@ -27,6 +27,7 @@ struct FwdParams {
     uint32_t *tile_count;        // [B*tiles]
     uint32_t *tile_cursor;       // [B*tiles]
     uint32_t *tile_offset;       // [B*tiles]
+    uint32_t *active_tiles;      // [B*tiles] tiles with a non-empty queue, counters[kCtrActiveTiles] of them
     void *big;                   // [cap_big] BigTri (16 B each)
     uint32_t *queue;             // [cap_queue + 4]
     uint32_t cap_big;
