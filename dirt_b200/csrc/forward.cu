@@ -281,13 +281,30 @@ __global__ void __launch_bounds__(256, KRES_CTAS) k_resolve(FwdParams p)
             t.X0 = ra.x; t.Y0 = ra.y; t.rw0 = __int_as_float(ra.w);
             t.X1 = rb.x; t.Y1 = rb.y; t.rw1 = __int_as_float(rb.w);
             t.X2 = rc.x; t.Y2 = rc.y; t.rw2 = __int_as_float(rc.w);
-            const long long area2 = orient2d(t.X0, t.Y0, t.X1, t.Y1, t.X2, t.Y2);
-            t.sign = area2 > 0 ? 1 : -1;
-            t.rcp_area = fdiv(1.0f, __ll2float_rn(area2 > 0 ? area2 : -area2));
-            long long e0, e1, e2;
-            edge_values(t, px, py, e0, e1, e2);
+            const int ex = max(t.X0, max(t.X1, t.X2)) - min(t.X0, min(t.X1, t.X2));
+            const int ey = max(t.Y0, max(t.Y1, t.Y2)) - min(t.Y0, min(t.Y1, t.Y2));
             float l0, l1, l2, b2;
-            screen_bary(t, e0, e1, e2, l0, l1, l2);
+            if (ex < kSmallExtent && ey < kSmallExtent) {
+                // every difference is below 2^15 (the sample lies inside the triangle), so the same
+                // integers come out of 32-bit arithmetic and convert to the same floats
+                const int cx = px * kSubpix + kSubpixHalf, cy = py * kSubpix + kSubpixHalf;
+                const int area2 = (t.X1 - t.X0) * (t.Y2 - t.Y0) - (t.Y1 - t.Y0) * (t.X2 - t.X0);
+                const int sg = area2 > 0 ? 1 : -1;
+                t.rcp_area = fdiv(1.0f, __int2float_rn(area2 > 0 ? area2 : -area2));
+                const int e0 = ((t.X2 - t.X1) * (cy - t.Y1) - (t.Y2 - t.Y1) * (cx - t.X1)) * sg;
+                const int e1 = ((t.X0 - t.X2) * (cy - t.Y2) - (t.Y0 - t.Y2) * (cx - t.X2)) * sg;
+                const int e2 = ((t.X1 - t.X0) * (cy - t.Y0) - (t.Y1 - t.Y0) * (cx - t.X0)) * sg;
+                l0 = fmul(__int2float_rn(e0), t.rcp_area);
+                l1 = fmul(__int2float_rn(e1), t.rcp_area);
+                l2 = fmul(__int2float_rn(e2), t.rcp_area);
+            } else {
+                const long long area2 = orient2d(t.X0, t.Y0, t.X1, t.Y1, t.X2, t.Y2);
+                t.sign = area2 > 0 ? 1 : -1;
+                t.rcp_area = fdiv(1.0f, __ll2float_rn(area2 > 0 ? area2 : -area2));
+                long long e0, e1, e2;
+                edge_values(t, px, py, e0, e1, e2);
+                screen_bary(t, e0, e1, e2, l0, l1, l2);
+            }
             perspective_weights(t, l0, l1, l2, B0, B1, b2, wc);
         } else {
             const FwdParams pc = p;      // keeps the kernel parameter block itself out of local memory
