@@ -37,6 +37,7 @@ constexpr int kWarpsPerCta = 8;
 #endif
 constexpr int kCtasPerSm = KCTAS;                     // the kernel waits on depth loads: occupancy over registers
 constexpr int kFragRound = KFRAG;                     // spans are 1-2 pixels on 3 lines out of 4 (profiles/r1_setup_notes.md)
+constexpr long long kFewFaces = 4096;
 constexpr float kLineRcpAreaMin = 1.0f / (2.0f * 65536.0f * 1024.0f);   // 1 / |2 area| of a 1024 px triangle: fatter ones go to the tile path
 
 // ---------------------------------------------------------------------------------------
@@ -279,6 +280,9 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
     // Smaller batches shorten the tail of a launch but repeat the latency-bound setup phase more
     // often: 16 and 8 faces per claim measured slower (profiles/r1_setup_notes.md).
     unsigned long long *work = p.work_next + bucket;
+    // a handful of faces cannot fill the machine line by line (one warp would walk every span in
+    // turn): then anything but tiny triangles goes to the pixel-parallel tile path
+    const bool many_faces = (long long)p.B * p.F >= kFewFaces;
     unsigned long long claim = 0;
     if (lane == 0) claim = atomicAdd(work, 32ull);
     for (;;) {
@@ -307,7 +311,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
                         atomicAdd(p.counters + 4, 1u);
                         atomicAdd(p.counters + 5, (uint32_t)max(t.xmax - t.xmin + 1, t.ymax - t.ymin + 1));
 #endif
-                    } else if (ex < kSmallExtent && ey < kSmallExtent && (t.rcp_area > kLineRcpAreaMin || (t.xmax - t.xmin + 1) * (t.ymax - t.ymin + 1) <= 256))
+                    } else if (ex < kSmallExtent && ey < kSmallExtent && ((many_faces && t.rcp_area > kLineRcpAreaMin) || (t.xmax - t.xmin + 1) * (t.ymax - t.ymin + 1) <= 256))
                     {   // few-but-fat triangles are better off pixel-parallel in the tile path
                         nlines = max(t.xmax - t.xmin, t.ymax - t.ymin) + 1;     // the longer side of the bounding box
                         dims = write_record(recs + lane * kRecWords, t, (uint32_t)f, (uint32_t)b, p.H, p.W);
