@@ -29,6 +29,8 @@ constexpr unsigned kFull = 0xFFFFFFFFu;
 constexpr int kBT = 16;                 // threads per CTA edge
 constexpr int kBI = kBT - 2;            // interior (output) pixels per CTA edge
 constexpr int kBR = kBT + 2;            // staged region edge
+constexpr int kBP = 24;                 // row pitch of the shared arrays: a warp is an 8x4 pixel block, and
+                                        // 4 rows at a pitch of 24 words land in 4 disjoint groups of 8 banks
 constexpr int kMaxC = 16;
 
 __device__ __forceinline__ float finite_or_zero(float v) { return fabsf(v) <= FLT_MAX ? v : 0.0f; }
@@ -91,10 +93,10 @@ __global__ void __launch_bounds__(kBT * kBT, KBWD_CTAS) k_grad_assemble(BwdParam
 {
     constexpr int CS = C > 0 ? C : kMaxC;
     const int CC = C > 0 ? C : p.C;
-    __shared__ float s_px[CS][kBR * kBR];
-    __shared__ int s_fid[kBR * kBR];
-    __shared__ float s_zw[kBR * kBR];
-    __shared__ float s_in[2][3][kBT * kBT];
+    __shared__ float s_px[CS][kBR * kBP];
+    __shared__ int s_fid[kBR * kBP];
+    __shared__ float s_zw[kBR * kBP];
+    __shared__ float s_in[2][3][kBT * kBP];
 
     const int tid = threadIdx.x;
     // a warp is an 8x4 pixel block: better odds that its lanes share faces than a 32x1 strip
@@ -115,17 +117,20 @@ __global__ void __launch_bounds__(kBT * kBT, KBWD_CTAS) k_grad_assemble(BwdParam
             const bool in = gx >= 0 && gx < W && gy >= 0 && gy < H;
             const int cx = min(max(gx, 0), W - 1), cy = min(max(gy, 0), H - 1);
             const size_t o = (size_t)cy * W + cx;
-            for (int c = 0; c < CC; ++c) s_px[c][i] = __ldg(img + o * CC + c);
+            const int si = ry * kBP + rx;
+            for (int c = 0; c < CC; ++c) s_px[c][si] = __ldg(img + o * CC + c);
+            // both loads are issued before either is used (the depth of an uncovered pixel is ignored)
             const int f = in ? __ldg(p.face_id + base + o) : -1;
-            s_fid[i] = f;
-            s_zw[i] = f >= 0 ? __ldg(&gbuf_all[base + o].w) : 2.0f;
+            const float zw = __ldg(&gbuf_all[base + o].w);
+            s_fid[si] = f;
+            s_zw[si] = f >= 0 ? zw : 2.0f;
         }
         __syncthreads();
 
         // ---- phase 1: Sobel response, owners, inbox -----------------------------------------
         const bool valid = x >= 0 && x < W && r >= 0 && r < H;
         const bool interior = valid && lx >= 1 && lx <= kBI && ly >= 1 && ly <= kBI;
-        const int ri = (ly + 1) * kBR + (lx + 1);               // own position in the staged region
+        const int ri = (ly + 1) * kBP + (lx + 1);               // own position in the staged region
         const size_t o = valid ? (size_t)r * W + x : 0;
         const int fself = s_fid[ri];
         float g[CS];
@@ -135,9 +140,9 @@ __global__ void __launch_bounds__(kBT * kBT, KBWD_CTAS) k_grad_assemble(BwdParam
             for (int c = 0; c < CC; ++c) {
                 g[c] = __ldg(gp + c);
                 const float *q = &s_px[c][ri];
-                // rows go down the image: q[-kBR] is the row above
-                const float dx = ((q[-kBR + 1] - q[-kBR - 1]) + 2.0f * (q[1] - q[-1]) + (q[kBR + 1] - q[kBR - 1])) * 0.125f;
-                const float dr = ((q[kBR - 1] - q[-kBR - 1]) + 2.0f * (q[kBR] - q[-kBR]) + (q[kBR + 1] - q[-kBR + 1])) * 0.125f;
+                // rows go down the image: q[-kBP] is the row above
+                const float dx = ((q[-kBP + 1] - q[-kBP - 1]) + 2.0f * (q[1] - q[-1]) + (q[kBP + 1] - q[kBP - 1])) * 0.125f;
+                const float dr = ((q[kBP - 1] - q[-kBP - 1]) + 2.0f * (q[kBP] - q[-kBP]) + (q[kBP + 1] - q[-kBP + 1])) * 0.125f;
                 sx += g[c] * finite_or_zero(dx);
                 sr += g[c] * finite_or_zero(dr);
             }
@@ -149,15 +154,15 @@ __global__ void __launch_bounds__(kBT * kBT, KBWD_CTAS) k_grad_assemble(BwdParam
         {
             const float zs = s_zw[ri];
             const int ox = sx != 0.0f ? pick_owner(fself, zs, s_fid[ri - 1], s_zw[ri - 1], s_fid[ri + 1], s_zw[ri + 1]) : 0;
-            const int oy = sr != 0.0f ? pick_owner(fself, zs, s_fid[ri - kBR], s_zw[ri - kBR], s_fid[ri + kBR], s_zw[ri + kBR]) : 0;
-            const int li = ly * kBT + lx;
+            const int oy = sr != 0.0f ? pick_owner(fself, zs, s_fid[ri - kBP], s_zw[ri - kBP], s_fid[ri + kBP], s_zw[ri + kBP]) : 0;
+            const int li = ly * kBP + lx;
             // candidate c = this pixel + d, d in {-1, 0, +1}; this pixel is sender slot 1 - d of c
             if (lx > 0) s_in[0][2][li - 1] = ox == 1 ? sx : 0.0f;
             s_in[0][1][li] = ox == 2 ? sx : 0.0f;
             if (lx < kBT - 1) s_in[0][0][li + 1] = ox == 3 ? sx : 0.0f;
-            if (ly > 0) s_in[1][2][li - kBT] = oy == 1 ? sr : 0.0f;
+            if (ly > 0) s_in[1][2][li - kBP] = oy == 1 ? sr : 0.0f;
             s_in[1][1][li] = oy == 2 ? sr : 0.0f;
-            if (ly < kBT - 1) s_in[1][0][li + kBT] = oy == 3 ? sr : 0.0f;
+            if (ly < kBT - 1) s_in[1][0][li + kBP] = oy == 3 ? sr : 0.0f;
         }
         __syncthreads();
 
@@ -165,7 +170,7 @@ __global__ void __launch_bounds__(kBT * kBT, KBWD_CTAS) k_grad_assemble(BwdParam
         const bool act = interior && fself >= 0;
         float B0 = 0.f, B1 = 0.f, gxv = 0.f, gyv = 0.f, gwv = 0.f;
         if (act) {
-            const int li = ly * kBT + lx;
+            const int li = ly * kBP + lx;
             const float4 gb = __ldg(gbuf_all + base + o);
             B0 = gb.x; B1 = gb.y;
             const float totx = (s_in[0][0][li] + s_in[0][1][li]) + s_in[0][2][li];
