@@ -238,12 +238,11 @@ def run_ours(args, wl, rank, world, local_rank):
         px, fid, gb = ops.forward_raw(d["background"], d["vertices"], d["vertex_colors"], d["faces"], want_aux=True)
         if not shared:
             return ops.backward_raw(d["faces"], px, grad_pixels, fid, gb, V)
-        # shared mesh: colour gradients are summed over the frames by the kernel (stride 0); the
-        # clip-space vertex gradients are folded to world space with each frame's matrix, then
-        # ONE packed allreduce sums vertex + colour gradients over the ranks
-        gv, gc, gbg = ops.backward_raw(d["faces"], px, grad_pixels, fid, gb, V, shared_colors=True)
-        gworld = torch.einsum("bvj,bij->vi", gv, d["matrices"])
-        return sharding.allreduce_shared_gradients(gworld, gc)
+        # shared mesh: the backward folds each frame's clip-space vertex gradient to world space
+        # with that frame's matrix and sums position + colour gradients over the frames into one
+        # packed [V, 8] buffer, which ONE allreduce then sums over the ranks in place
+        packed, gbg = ops.backward_shared_raw(d["faces"], px, grad_pixels, fid, gb, V, d["matrices"])
+        return sharding.allreduce_packed(packed, C)
 
     def barrier():
         if world > 1:

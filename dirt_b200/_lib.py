@@ -43,6 +43,13 @@ class DirtBackwardArgs(ctypes.Structure):
                 ("grad_background", _f32p)]
 
 
+class DirtSharedBackwardArgs(ctypes.Structure):
+    _fields_ = [("shape", DirtShape),
+                ("faces", _f32p), ("faces_bstride", _i64),
+                ("pixels", _f32p), ("grad_pixels", _f32p), ("face_id", _f32p), ("gbuffer", _f32p),
+                ("clip_from_world", _f32p), ("grad_shared", _f32p), ("grad_background", _f32p)]
+
+
 class DirtSceneArgs(ctypes.Structure):
     _fields_ = [("shape", DirtShape),
                 ("background", _f32p), ("background_bstride", _i64),
@@ -58,6 +65,8 @@ EXPORTS = {
     "dirt_workspace_bytes": (ctypes.c_size_t, [ctypes.POINTER(DirtShape)]),
     "dirt_rasterise_forward": (ctypes.c_int, [ctypes.POINTER(DirtForwardArgs), ctypes.c_void_p]),
     "dirt_rasterise_backward": (ctypes.c_int, [ctypes.POINTER(DirtBackwardArgs), ctypes.c_void_p]),
+    "dirt_shared_grad_stride": (ctypes.c_int, [ctypes.c_int]),
+    "dirt_rasterise_backward_shared": (ctypes.c_int, [ctypes.POINTER(DirtSharedBackwardArgs), ctypes.c_void_p]),
     "dirt_rasterise_forward_host": (ctypes.c_int, [ctypes.POINTER(DirtForwardArgs)]),
     "dirt_rasterise_backward_host": (ctypes.c_int, [ctypes.POINTER(DirtBackwardArgs)]),
     "dirt_release_host_staging": (ctypes.c_int, []),

@@ -187,6 +187,16 @@ __global__ void __launch_bounds__(kBT * kBT, KBWD_CTAS) k_grad_assemble(BwdParam
         const int32_t *fp = p.faces + (int64_t)b * p.faces_bs + 3 * (int64_t)(act ? fself : 0);
         float4 *gv = reinterpret_cast<float4 *>(p.grad_vertices + (int64_t)b * p.grad_vertices_bs);
         float *gc = p.grad_vertex_colors + (int64_t)b * p.grad_vertex_colors_bs;
+        const bool packed = p.grad_packed != nullptr;
+        // shared mesh: clip = world @ M_b, so grad_world[j] = sum_i grad_clip[i] * M_b[j][i]; the
+        // z column never receives a gradient (GRADIENT_SPEC 4)
+        const float *M = p.matrices + 16 * (int64_t)b;
+        auto to_world = [&](float gx, float gy, float gw) {
+            return make_float4(gx * __ldg(M + 0) + gy * __ldg(M + 1) + gw * __ldg(M + 3),
+                               gx * __ldg(M + 4) + gy * __ldg(M + 5) + gw * __ldg(M + 7),
+                               gx * __ldg(M + 8) + gy * __ldg(M + 9) + gw * __ldg(M + 11),
+                               gx * __ldg(M + 12) + gy * __ldg(M + 13) + gw * __ldg(M + 15));
+        };
         if (C == 1 || C == 3) {
             constexpr int NQ = 3 + (C > 0 ? C : 1);
             float v[3 * NQ];
@@ -202,10 +212,17 @@ __global__ void __launch_bounds__(kBT * kBT, KBWD_CTAS) k_grad_assemble(BwdParam
 #pragma unroll
                 for (int k = 0; k < 3; ++k) {
                     const int vi = __ldg(fp + k);
-                    if (v[k * NQ] != 0.0f || v[k * NQ + 1] != 0.0f || v[k * NQ + 2] != 0.0f)
-                        atomicAdd(gv + vi, make_float4(v[k * NQ], v[k * NQ + 1], 0.0f, v[k * NQ + 2]));
-                    if (C == 3) red_add3(gc + (int64_t)vi * 3, v[k * NQ + 3], v[k * NQ + 4], v[k * NQ + 5]);
-                    else atomicAdd(gc + vi, v[k * NQ + 3]);
+                    const bool moved = v[k * NQ] != 0.0f || v[k * NQ + 1] != 0.0f || v[k * NQ + 2] != 0.0f;
+                    if (packed) {
+                        float *row = p.grad_packed + (int64_t)vi * p.packed_stride;
+                        if (moved) atomicAdd(reinterpret_cast<float4 *>(row), to_world(v[k * NQ], v[k * NQ + 1], v[k * NQ + 2]));
+                        if (C == 3) atomicAdd(reinterpret_cast<float4 *>(row + 4), make_float4(v[k * NQ + 3], v[k * NQ + 4], v[k * NQ + 5], 0.0f));
+                        else atomicAdd(row + 4, v[k * NQ + 3]);
+                    } else {
+                        if (moved) atomicAdd(gv + vi, make_float4(v[k * NQ], v[k * NQ + 1], 0.0f, v[k * NQ + 2]));
+                        if (C == 3) red_add3(gc + (int64_t)vi * 3, v[k * NQ + 3], v[k * NQ + 4], v[k * NQ + 5]);
+                        else atomicAdd(gc + vi, v[k * NQ + 3]);
+                    }
                 }
             }
         } else {
@@ -220,9 +237,15 @@ __global__ void __launch_bounds__(kBT * kBT, KBWD_CTAS) k_grad_assemble(BwdParam
                 for (int k = 0; k < 3; ++k) {
                     const int vi = __ldg(fp + k);
                     const float bk = k == 0 ? B0 : (k == 1 ? B1 : B2);
-                    if (leader && (v[k * 3] != 0.0f || v[k * 3 + 1] != 0.0f || v[k * 3 + 2] != 0.0f))
-                        atomicAdd(gv + vi, make_float4(v[k * 3], v[k * 3 + 1], 0.0f, v[k * 3 + 2]));
-                    for (int c = 0; c < CC; ++c) atomicAdd(gc + (int64_t)vi * CC + c, g[c] * bk);
+                    const bool moved = leader && (v[k * 3] != 0.0f || v[k * 3 + 1] != 0.0f || v[k * 3 + 2] != 0.0f);
+                    if (packed) {
+                        float *row = p.grad_packed + (int64_t)vi * p.packed_stride;
+                        if (moved) atomicAdd(reinterpret_cast<float4 *>(row), to_world(v[k * 3], v[k * 3 + 1], v[k * 3 + 2]));
+                        for (int c = 0; c < CC; ++c) atomicAdd(row + 4 + c, g[c] * bk);
+                    } else {
+                        if (moved) atomicAdd(gv + vi, make_float4(v[k * 3], v[k * 3 + 1], 0.0f, v[k * 3 + 2]));
+                        for (int c = 0; c < CC; ++c) atomicAdd(gc + (int64_t)vi * CC + c, g[c] * bk);
+                    }
                 }
             }
         }
@@ -235,8 +258,12 @@ cudaError_t launch_backward(const BwdParams &p, int sm_count, cudaStream_t strea
     cudaError_t e;
     const size_t nbv = p.grad_vertices_bs == 0 ? 1 : (size_t)p.B, nbc = p.grad_vertex_colors_bs == 0 ? 1 : (size_t)p.B;
     tm.begin(kStageGradClear, stream);
-    if ((e = cudaMemsetAsync(p.grad_vertices, 0, nbv * p.V * 4 * sizeof(float), stream)) != cudaSuccess) return e;
-    if ((e = cudaMemsetAsync(p.grad_vertex_colors, 0, nbc * p.V * p.C * sizeof(float), stream)) != cudaSuccess) return e;
+    if (p.grad_packed) {
+        if ((e = cudaMemsetAsync(p.grad_packed, 0, (size_t)p.V * p.packed_stride * sizeof(float), stream)) != cudaSuccess) return e;
+    } else {
+        if ((e = cudaMemsetAsync(p.grad_vertices, 0, nbv * p.V * 4 * sizeof(float), stream)) != cudaSuccess) return e;
+        if ((e = cudaMemsetAsync(p.grad_vertex_colors, 0, nbc * p.V * p.C * sizeof(float), stream)) != cudaSuccess) return e;
+    }
     tm.end(kStageGradClear, stream);
     if ((long long)p.B * p.H * p.W == 0) return cudaSuccess;
     // each CTA walks several batch elements: tiles are small, and a grid of ~32 CTAs per SM is

@@ -246,10 +246,53 @@ int dirt_rasterise_backward(const DirtBackwardArgs *a, void *stream)
     p.grad_vertices = a->grad_vertices;           p.grad_vertices_bs = a->grad_vertices_bstride;
     p.grad_vertex_colors = a->grad_vertex_colors; p.grad_vertex_colors_bs = a->grad_vertex_colors_bstride;
     p.grad_background = a->grad_background;
+    p.matrices = nullptr; p.grad_packed = nullptr; p.packed_stride = 0;
     uint64_t n = 0;
     cudaError_t e = dirt::launch_backward(p, sms, static_cast<cudaStream_t>(stream), &n, g_timer);
     g_launches += n;
     if (e != cudaSuccess) return cuda_fail(e, "rasterise backward launch");
+    return DIRT_STATUS_OK;
+}
+
+int dirt_shared_grad_stride(int channels) { return channels < 1 ? 0 : (4 + channels + 3) / 4 * 4; }
+
+int dirt_rasterise_backward_shared(const DirtSharedBackwardArgs *a, void *stream)
+{
+    if (!a) return fail(DIRT_STATUS_INVALID_ARGUMENT, "null arguments");
+    const DirtShape &s = a->shape;
+    int rc = check_shape(s);
+    if (rc) return rc;
+    if ((rc = check_stride(a->faces_bstride, (int64_t)s.face_count * 3, "faces"))) return rc;
+    if (s.vertex_count > 0 && !a->grad_shared) return fail(DIRT_STATUS_INVALID_ARGUMENT, "grad_shared must not be null");
+    if ((uintptr_t)a->grad_shared & 15u) return fail(DIRT_STATUS_INVALID_ARGUMENT, "grad_shared must be 16-byte aligned");
+    const int stride = dirt_shared_grad_stride(s.channels);
+    if (s.batch == 0) {
+        // nothing renders the mesh: the sum over an empty batch is zero
+        if (s.vertex_count > 0) {
+            cudaError_t e = cudaMemsetAsync(a->grad_shared, 0, (size_t)s.vertex_count * stride * sizeof(float), static_cast<cudaStream_t>(stream));
+            if (e != cudaSuccess) return cuda_fail(e, "cudaMemsetAsync");
+        }
+        return DIRT_STATUS_OK;
+    }
+    if (!a->pixels || !a->grad_pixels || !a->face_id || !a->gbuffer || !a->clip_from_world)
+        return fail(DIRT_STATUS_INVALID_ARGUMENT, "pixels, grad_pixels, face_id, gbuffer and clip_from_world must not be null");
+    if (s.face_count > 0 && !a->faces) return fail(DIRT_STATUS_INVALID_ARGUMENT, "faces must not be null");
+    if ((uintptr_t)a->gbuffer & 15u) return fail(DIRT_STATUS_INVALID_ARGUMENT, "gbuffer must be 16-byte aligned");
+    int sms = 0;
+    if ((rc = current_sm_count(&sms))) return rc;
+
+    dirt::BwdParams p;
+    p.B = s.batch; p.H = s.height; p.W = s.width; p.C = s.channels; p.V = s.vertex_count; p.F = s.face_count;
+    p.faces = a->faces; p.faces_bs = a->faces_bstride;
+    p.pixels = a->pixels; p.grad_pixels = a->grad_pixels; p.face_id = a->face_id; p.gbuffer = a->gbuffer;
+    p.grad_vertices = nullptr;      p.grad_vertices_bs = 0;
+    p.grad_vertex_colors = nullptr; p.grad_vertex_colors_bs = 0;
+    p.grad_background = a->grad_background;
+    p.matrices = a->clip_from_world; p.grad_packed = a->grad_shared; p.packed_stride = stride;
+    uint64_t n = 0;
+    cudaError_t e = dirt::launch_backward(p, sms, static_cast<cudaStream_t>(stream), &n, g_timer);
+    g_launches += n;
+    if (e != cudaSuccess) return cuda_fail(e, "rasterise shared backward launch");
     return DIRT_STATUS_OK;
 }
 

@@ -60,6 +60,11 @@ struct BwdParams {
     float *grad_vertices;        int64_t grad_vertices_bs;
     float *grad_vertex_colors;   int64_t grad_vertex_colors_bs;
     float *grad_background;      // optional
+    // shared-mesh mode (grad_packed != nullptr): world-space position + colour gradients of all
+    // batch elements accumulate into grad_packed [V, packed_stride]; grad_vertices / colours unused
+    const float *matrices;       // [B,4,4] clip = world @ M_b
+    float *grad_packed;
+    int packed_stride;
 };
 
 enum Stage {

@@ -146,6 +146,31 @@ def backward_raw(faces, pixels, grad_pixels, face_id, gbuffer, V, shared_vertice
     return gv, gc, gbg
 
 
+def backward_shared_raw(faces, pixels, grad_pixels, face_id, gbuffer, V, clip_from_world, want_grad_background=True):
+    """Shared-mesh backward: one C-ABI call that folds every element's
+    clip-space vertex gradient to world space with its matrix (clip_b = world @ M_b) and sums
+    position and colour gradients over the batch into ONE packed buffer [V, stride]: columns 0..3
+    world-space position gradient, 4..4+C-1 colour gradient.  The buffer is the all-reduce message
+    of `sharding.allreduce_packed`.  Returns (grad_shared, grad_background | None)."""
+    lib = _lib.load()
+    device = pixels.device
+    B, H, W, C = pixels.shape
+    F = faces.shape[1]
+    stride = lib.dirt_shared_grad_stride(C)
+    packed = torch.empty((V, stride), dtype=torch.float32, device=device)
+    gbg = torch.empty((B, H, W, C), dtype=torch.float32, device=device) if want_grad_background else None
+    m = clip_from_world.to(torch.float32).contiguous()
+    if tuple(m.shape) != (B, 4, 4):
+        raise _lib.InvalidArgumentError(-1, "clip_from_world must be [batch, 4, 4]")
+    args = _lib.DirtSharedBackwardArgs(
+        DirtShape(B, H, W, C, V, F), faces.data_ptr(), _bstride(faces, B),
+        pixels.data_ptr(), grad_pixels.data_ptr(), face_id.data_ptr(), gbuffer.data_ptr(),
+        m.data_ptr(), packed.data_ptr(), gbg.data_ptr() if want_grad_background else None)
+    with torch.cuda.device(device):
+        _lib.check(lib.dirt_rasterise_backward_shared(ctypes.byref(args), torch.cuda.current_stream(device).cuda_stream))
+    return packed, gbg
+
+
 class _Rasterise(torch.autograd.Function):
     """Forward = op "Rasterise"; backward = op "RasteriseGrad".  In the TF shim the same pairing
     is `@ops.RegisterGradient("Rasterise")` (INTEGRATION.md)."""

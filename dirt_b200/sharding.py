@@ -65,6 +65,27 @@ def allreduce_shared_gradients(grad_vertices, grad_vertex_colors, group=None, as
     return split()
 
 
+def allreduce_packed(packed, channels, group=None, async_op=False):
+    """All-reduce of the packed shared-mesh gradient buffer [V, stride] that
+    `rasterise_ops.backward_shared_raw` fills (in place, ONE collective, no packing copy).
+    Returns (grad_world [V,4], grad_vertex_colors [V,C]) as views of the buffer -- or, with
+    async_op=True, (work, finish)."""
+    world = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+
+    def split():
+        return packed[:, :4], packed[:, 4:4 + channels]
+
+    if world == 1:
+        return (None, split) if async_op else split()
+    work = dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=group, async_op=async_op)
+    if async_op:
+        def finish():
+            work.wait()
+            return split()
+        return work, finish
+    return split()
+
+
 def rasterise_batch_sharded(background, vertices, vertex_colors, faces, rank=None, world=None):
     """`rasterise_batch` on this rank's shard of the batch (no collective; outputs stay sharded,
     as the reference's per-device graphs do).  Returns (pixels_shard, (lo, hi))."""

@@ -96,6 +96,28 @@ typedef struct DirtBackwardArgs {
     float *grad_background;       /* out [B,H,W,C]; may be NULL                            */
 } DirtBackwardArgs;
 
+/* Shared-mesh backward: every batch element renders the SAME mesh, element b
+ * through its own matrix (clip_b = world @ M_b, row vectors: the convention of dirt/matrices.py and
+ * the inverse-rendering loop of tests/optimize_sequence.py:293-352).  The clip-space vertex
+ * gradient of each element is folded to world space (grad_world += grad_clip_b @ M_b^T) and
+ * accumulated, together with the colour gradient, straight into ONE packed buffer
+ *     grad_shared [V, stride],  stride = dirt_shared_grad_stride(C) = 4 + C rounded up to 4:
+ *     columns 0..3 world-space position gradient, 4..4+C-1 colour gradient, rest zero,
+ * which is also the message of the cross-GPU all-reduce.  Neither [B,V,4] nor [B,V,C] exists. */
+typedef struct DirtSharedBackwardArgs {
+    DirtShape shape;
+    const int32_t *faces;         int64_t faces_bstride;         /* [B,F,3] (0 = shared)   */
+    const float *pixels;          /* [B,H,W,C] forward output                              */
+    const float *grad_pixels;     /* [B,H,W,C]                                             */
+    const int32_t *face_id;       /* [B,H,W]   from forward                                */
+    const float *gbuffer;         /* [B,H,W,4] from forward                                */
+    const float *clip_from_world; /* [B,4,4] row-major M_b                                 */
+    float *grad_shared;           /* out [V, stride], 16-byte aligned, zeroed by the callee */
+    float *grad_background;       /* out [B,H,W,C]; may be NULL                            */
+} DirtSharedBackwardArgs;
+DIRT_API int dirt_shared_grad_stride(int channels);
+DIRT_API int dirt_rasterise_backward_shared(const DirtSharedBackwardArgs *args, void *stream);
+
 /* Library identity. */
 DIRT_API int dirt_abi_version(void);
 /* Thread-local message of the last failing call on this thread ("" if none). */

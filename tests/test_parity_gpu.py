@@ -162,6 +162,35 @@ def test_broadcast_shared_mesh_and_summed_gradients():
     _check_backward(sc, dev, ora, shared=True)
 
 
+@pytest.mark.parametrize("C", [1, 3, 5])
+def test_shared_mesh_backward_folds_to_world_space(C):
+    """one call sums grad_clip[b] @ M_b^T and the colour gradients of all frames
+    into the packed [V, stride] buffer.  Checked against the oracle's per-frame gradients folded
+    with numpy; bar as for gradients (1e-4 of max|grad|)."""
+    from dirt_b200 import rasterise_ops as ops
+    sc = scenes.hill(3, 96, 128, C=C, n=40, seed=2)
+    M = sc.pop("matrices")
+    sc.pop("world")
+    dev, ora = _check_forward(sc)
+    px, fid, gb, t = dev
+    opx, ofid, ogb = ora
+    g = np.random.RandomState(3).randn(*opx.shape).astype(np.float32)
+    V = sc["vertices"].shape[1]
+    packed, gbg = ops.backward_shared_raw(t["faces"], px, torch.from_numpy(g).cuda(), fid, gb, V, torch.from_numpy(M).cuda())
+    torch.cuda.synchronize()
+    faces_b = np.broadcast_to(sc["faces"], (3,) + sc["faces"].shape[1:])
+    ogv, ogc, ogbg = golden.backward(np.ascontiguousarray(faces_b), opx, g, ofid, ogb, V, threads=8)
+    exp_w = np.einsum("bvj,bij->vi", ogv.astype(np.float64), M.astype(np.float64))
+    exp_c = ogc.astype(np.float64).sum(0)
+    got = packed.cpu().numpy()
+    assert got.shape == (V, (4 + C + 3) // 4 * 4)
+    assert np.array_equal(gbg.cpu().numpy(), ogbg)
+    for name, a, b in (("grad_world", got[:, :4], exp_w), ("grad_vertex_colors", got[:, 4:4 + C], exp_c)):
+        err = np.abs(a - b).max() / max(np.abs(b).max(), 1e-12)
+        assert err <= GRAD_RTOL, "%s: max err %.3g of max|grad|" % (name, err)
+    assert not got[:, 4 + C:].any()
+
+
 def test_determinism_run_to_run():
     sc = scenes.sphere(2, 128, 128, n_lat=64, n_lon=64)
     a = _run_forward(sc)

@@ -76,3 +76,35 @@ def test_allreduce_of_shared_gradients_world2_gloo():
         np.testing.assert_allclose(b, exp_c, rtol=1e-6, atol=1e-6)
         assert np.array_equal(a, a2) and np.array_equal(b, b2)
     assert res[0][4] == (0, 4) and res[1][4] == (4, 7)
+
+
+def _worker_packed(rank, world, port, V, C, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        stride = (4 + C + 3) // 4 * 4
+        packed = torch.from_numpy(np.random.RandomState(200 + rank).randn(V, stride).astype(np.float32))
+        gw, gc = sharding.allreduce_packed(packed.clone(), C)
+        work, finish = sharding.allreduce_packed(packed.clone(), C, async_op=True)
+        gw2, gc2 = finish()
+        out[rank] = (gw.numpy().copy(), gc.numpy().copy(), gw2.numpy().copy(), gc2.numpy().copy())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_allreduce_of_the_packed_shared_gradient_buffer_world2_gloo():
+    """The buffer `backward_shared_raw` fills ([V, stride]: world-space position gradient, colour
+    gradient, padding) is reduced in place with one collective; the results are views of it."""
+    world, V, C = 2, 41, 3
+    port = _free_port()
+    with mp.Manager() as m:
+        out = m.dict()
+        mp.spawn(_worker_packed, args=(world, port, V, C, out), nprocs=world, join=True)
+        res = dict(out)
+    exp = sum(np.random.RandomState(200 + r).randn(V, 8).astype(np.float32) for r in range(world))
+    for r in range(world):
+        gw, gc, gw2, gc2 = res[r]
+        assert gw.shape == (V, 4) and gc.shape == (V, C)
+        np.testing.assert_allclose(gw, exp[:, :4], rtol=1e-6, atol=1e-6)
+        np.testing.assert_allclose(gc, exp[:, 4:7], rtol=1e-6, atol=1e-6)
+        assert np.array_equal(gw, gw2) and np.array_equal(gc, gc2)
