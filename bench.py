@@ -318,7 +318,9 @@ def run_ours(args, wl, rank, world, local_rank):
     # and reads back its loss and gradients.  Steps are software-pipelined over two buffer sets
     # and three streams (upload i+1 | compute i | download i-1), the way a training loop feeds a
     # GPU; the target image of the loss stays resident.
-    in_keys = ("background", "vertices", "vertex_colors", "faces")
+    # shared mesh (c5): the caller feeds the mesh once in world space plus one matrix per frame
+    in_keys = ("background", "world", "matrices", "vertex_colors", "faces") if shared else \
+        ("background", "vertices", "vertex_colors", "faces")
     s_in, s_out, s_main = torch.cuda.Stream(dev), torch.cuda.Stream(dev), torch.cuda.current_stream(dev)
     dev_in = [{k: torch.empty_like(d[k]) for k in in_keys} for _ in range(2)]
     out_gv = [torch.empty((1 if shared else B, V, 4), dtype=torch.float32).pin_memory() for _ in range(2)]
@@ -341,13 +343,18 @@ def run_ours(args, wl, rank, world, local_rank):
         slot = i % 2
         s_main.wait_event(ready[slot])
         bg = dev_in[slot]["background"].detach().requires_grad_(True)
-        v = dev_in[slot]["vertices"].detach().requires_grad_(True)
-        c = dev_in[slot]["vertex_colors"].detach().requires_grad_(True)
-        px = dirt_b200.rasterise_batch(bg, v, c, dev_in[slot]["faces"])
+        if shared:
+            v = dev_in[slot]["world"].detach().requires_grad_(True)
+            c = dev_in[slot]["vertex_colors"][0].detach().requires_grad_(True)
+            px = dirt_b200.rasterise_batch_shared(bg, v, dev_in[slot]["matrices"], c, dev_in[slot]["faces"][0])
+        else:
+            v = dev_in[slot]["vertices"].detach().requires_grad_(True)
+            c = dev_in[slot]["vertex_colors"].detach().requires_grad_(True)
+            px = dirt_b200.rasterise_batch(bg, v, c, dev_in[slot]["faces"])
         loss = 0.5 * ((px - d["target"]) ** 2).sum()
         loss.backward()
         if shared:
-            gvo, gco = sharding.allreduce_shared_gradients(torch.einsum("bvj,bij->vi", v.grad, d["matrices"]), c.grad)
+            gvo, gco = sharding.allreduce_shared_gradients(v.grad.unsqueeze(0), c.grad.unsqueeze(0))
             gvo, gco = gvo.unsqueeze(0), gco.unsqueeze(0)
         else:
             gvo, gco = v.grad, c.grad
@@ -388,7 +395,8 @@ def run_ours(args, wl, rank, world, local_rank):
     d2h = out_gv[0].numel() * 4 + out_gc[0].numel() * 4 + 4
     e2e = {"value": world * B * H * W / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": e2e_steps, "last_loss": losses[-1],
-           "path": "dirt_b200.rasterise_batch + autograd backward; each step uploads its inputs from pinned host "
+           "path": ("dirt_b200.rasterise_batch_shared" if shared else "dirt_b200.rasterise_batch") +
+                   " + autograd backward; each step uploads its inputs from pinned host "
                    "memory and downloads loss + gradients; double-buffered over copy/compute/copy streams"}
 
     cpu_base = None

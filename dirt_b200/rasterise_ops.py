@@ -242,6 +242,63 @@ def rasterise_batch(background, vertices, vertex_colors, faces, height=None, wid
     return _Rasterise.apply(bg, v, c, f)
 
 
+class _RasteriseShared(torch.autograd.Function):
+    """One mesh seen by B cameras: forward projects and rasterises, backward is the fused
+    shared-mesh backward (gradients w.r.t. the world-space vertices and the colours, already
+    summed over the frames)."""
+
+    @staticmethod
+    def forward(ctx, background, world_vertices, clip_from_world, vertex_colors, faces):
+        if ctx.needs_input_grad[2]:
+            raise NotImplementedError("rasterise_batch_shared has no gradient w.r.t. clip_from_world: project the "
+                                      "vertices yourself and call rasterise_batch for that")
+        vertices = torch.matmul(world_vertices.unsqueeze(0), clip_from_world).contiguous()      # [B,V,4]
+        need_grad = any(ctx.needs_input_grad)
+        pixels, face_id, gbuffer = forward_raw(background, vertices, vertex_colors.unsqueeze(0), faces.unsqueeze(0),
+                                               want_aux=need_grad)
+        if need_grad:
+            ctx.save_for_backward(faces, pixels, face_id, gbuffer, clip_from_world)
+            ctx.meta = (world_vertices.shape[0], background.shape[0])
+        return pixels
+
+    @staticmethod
+    def backward(ctx, grad_pixels):
+        faces, pixels, face_id, gbuffer, clip_from_world = ctx.saved_tensors
+        V, bg_b = ctx.meta
+        C = pixels.shape[-1]
+        packed, gbg = backward_shared_raw(faces.unsqueeze(0), pixels, grad_pixels.contiguous().to(torch.float32), face_id,
+                                          gbuffer, V, clip_from_world, want_grad_background=ctx.needs_input_grad[0])
+        if gbg is not None and bg_b == 1 and pixels.shape[0] > 1:
+            gbg = gbg.sum(dim=0, keepdim=True)
+        return gbg, packed[:, :4], None, packed[:, 4:4 + C], None
+
+
+def rasterise_batch_shared(background, world_vertices, clip_from_world, vertex_colors, faces):
+    """The shared-mesh form of `rasterise_batch` (the inverse-rendering loop of
+    tests/optimize_sequence.py:293-352): ONE mesh `world_vertices` [V,4], `vertex_colors` [V,C],
+    `faces` [F,3], rendered by B cameras `clip_from_world` [B,4,4] (row vectors: clip = world @ M_b)
+    over `background` [B|1,H,W,C].  Returns pixels [B,H,W,C]; the backward delivers the gradients
+    w.r.t. world_vertices and vertex_colors summed over the frames without materialising the
+    per-frame [B,V,4] / [B,V,C] gradients.  Across GPUs, all-reduce `.grad` of the two leaves (or use
+    `rasterise_ops.backward_shared_raw` + `sharding.allreduce_packed` for a single collective)."""
+    dev = _device_of(background, world_vertices, clip_from_world, vertex_colors, faces)
+    bg = _as_tensor(background, torch.float32, dev, "background").contiguous()
+    wv = _as_tensor(world_vertices, torch.float32, dev, "world_vertices").contiguous()
+    m = _as_tensor(clip_from_world, torch.float32, dev, "clip_from_world").contiguous()
+    col = _as_tensor(vertex_colors, torch.float32, dev, "vertex_colors").contiguous()
+    f = _as_tensor(faces, torch.int32, dev, "faces").contiguous()
+    if bg.dim() != 4 or wv.dim() != 2 or wv.shape[1] != 4 or m.dim() != 3 or tuple(m.shape[1:]) != (4, 4) \
+            or col.dim() != 2 or col.shape[0] != wv.shape[0] or f.dim() != 2 or f.shape[1] != 3:
+        raise InvalidArgumentError(-1, "rasterise_batch_shared expects background [B|1,H,W,C], world_vertices [V,4], "
+                                       "clip_from_world [B,4,4], vertex_colors [V,C], faces [F,3]")
+    if col.shape[1] != bg.shape[3]:
+        raise InvalidArgumentError(-1, "vertex_colors and background must have the same number of channels")
+    B = m.shape[0]
+    if bg.shape[0] not in (1, B):
+        raise InvalidArgumentError(-1, "background batch must be 1 or the number of cameras")
+    return _RasteriseShared.apply(bg, wv, m, col, f)
+
+
 def rasterise_grad(background, vertices, vertex_colors, faces, camera_pos=None, height=None, width=None,
                    channels=None, name=None, grad_pixels=None):
     """Explicit backward (op name "RasteriseGrad", csrc/rasterise_grad_egl.cpp:33-53) with the

@@ -191,6 +191,32 @@ def test_shared_mesh_backward_folds_to_world_space(C):
     assert not got[:, 4 + C:].any()
 
 
+def test_public_shared_mesh_api_matches_the_per_frame_autograd_path():
+    """dirt_b200.rasterise_batch_shared (fused backward) against rasterise_batch fed with
+    world @ M_b through torch autograd (per-frame gradients, then matmul backward)."""
+    import dirt_b200
+    sc = scenes.hill(3, 80, 96, C=3, n=36, seed=4)
+    dev = {k: torch.from_numpy(np.ascontiguousarray(v)).cuda() for k, v in sc.items()}
+    target = torch.rand(3, 80, 96, 3, device="cuda")
+
+    def run(fused):
+        w = dev["world"].clone().requires_grad_(True)
+        c = dev["vertex_colors"][0].clone().requires_grad_(True)
+        bg = dev["background"].clone().requires_grad_(True)
+        if fused:
+            px = dirt_b200.rasterise_batch_shared(bg, w, dev["matrices"], c, dev["faces"][0])
+        else:
+            px = dirt_b200.rasterise_batch(bg, torch.matmul(w.unsqueeze(0), dev["matrices"]), c.unsqueeze(0), dev["faces"])
+        (0.5 * ((px - target) ** 2).sum()).backward()
+        return px.detach(), w.grad, c.grad, bg.grad
+
+    pa, wa, ca, ba = run(True)
+    pb, wb, cb, bb = run(False)
+    assert torch.equal(pa, pb) and torch.equal(ba, bb)
+    for a, b in ((wa, wb), (ca, cb)):
+        assert float((a - b).abs().max()) <= GRAD_RTOL * float(b.abs().max())
+
+
 def test_determinism_run_to_run():
     sc = scenes.sphere(2, 128, 128, n_lat=64, n_lon=64)
     a = _run_forward(sc)
