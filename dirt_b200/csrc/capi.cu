@@ -296,6 +296,39 @@ int dirt_rasterise_backward_shared(const DirtSharedBackwardArgs *a, void *stream
     return DIRT_STATUS_OK;
 }
 
+int dirt_vertex_normals(const float *vertices, int batch, int vertex_count, int vertex_dim, const int32_t *faces, int face_count,
+                        float *sums, float *normals, void *stream)
+{
+    if (batch < 0 || vertex_count < 0 || face_count < 0 || (vertex_dim != 3 && vertex_dim != 4))
+        return fail(DIRT_STATUS_INVALID_ARGUMENT, "vertex_normals: vertices must be [batch, V, 3|4], counts non-negative");
+    if ((long long)batch * vertex_count == 0) return DIRT_STATUS_OK;
+    if (!vertices || !sums || !normals || (face_count > 0 && !faces)) return fail(DIRT_STATUS_INVALID_ARGUMENT, "vertex_normals: null pointer");
+    int sms = 0, rc;
+    if ((rc = current_sm_count(&sms))) return rc;
+    cudaError_t e = dirt::launch_vertex_normals(vertices, batch, vertex_count, vertex_dim, faces, face_count, sums, normals,
+                                                static_cast<cudaStream_t>(stream));
+    g_launches += face_count > 0 ? 2 : 1;
+    if (e != cudaSuccess) return cuda_fail(e, "vertex_normals launch");
+    return DIRT_STATUS_OK;
+}
+
+int dirt_vertex_normals_grad(const float *vertices, int batch, int vertex_count, int vertex_dim, const int32_t *faces, int face_count,
+                             const float *sums, const float *grad_normals, float *grad_sums, float *grad_vertices, void *stream)
+{
+    if (batch < 0 || vertex_count < 0 || face_count < 0 || (vertex_dim != 3 && vertex_dim != 4))
+        return fail(DIRT_STATUS_INVALID_ARGUMENT, "vertex_normals_grad: vertices must be [batch, V, 3|4], counts non-negative");
+    if ((long long)batch * vertex_count == 0) return DIRT_STATUS_OK;
+    if (!vertices || !grad_normals || !grad_vertices || (sums && !grad_sums) || (face_count > 0 && !faces))
+        return fail(DIRT_STATUS_INVALID_ARGUMENT, "vertex_normals_grad: null pointer");
+    int sms = 0, rc;
+    if ((rc = current_sm_count(&sms))) return rc;
+    cudaError_t e = dirt::launch_vertex_normals_grad(vertices, batch, vertex_count, vertex_dim, faces, face_count, sums, grad_normals,
+                                                     grad_sums, grad_vertices, static_cast<cudaStream_t>(stream));
+    g_launches += face_count > 0 ? 2 : 1;
+    if (e != cudaSuccess) return cuda_fail(e, "vertex_normals_grad launch");
+    return DIRT_STATUS_OK;
+}
+
 int dirt_dilate_silhouette(const float *x, float *out, int batch, int height, int width, int channels, void *stream)
 {
     if (batch < 0 || height <= 0 || width <= 0 || channels <= 0) return fail(DIRT_STATUS_INVALID_ARGUMENT, "dilate: bad shape");

@@ -95,6 +95,10 @@ void launch_hiz_build(const FwdParams &p, const BucketPlan &plan, int sm_count, 
 cudaError_t launch_dilate(const float *x, float *out, int B, int H, int W, int C, int sm_count, cudaStream_t stream);
 cudaError_t launch_dilate_grad(const float *x, const float *grad_out, float *grad_x, int B, int H, int W, int C,
                                int sm_count, cudaStream_t stream);
+cudaError_t launch_vertex_normals(const float *vertices, int B, int V, int D, const int32_t *faces, int F,
+                                  float *sums, float *normals, cudaStream_t stream);
+cudaError_t launch_vertex_normals_grad(const float *vertices, int B, int V, int D, const int32_t *faces, int F, const float *sums,
+                                       const float *grad_normals, float *grad_sums, float *grad_vertices, cudaStream_t stream);
 cudaError_t launch_backward(const BwdParams &p, int sm_count, cudaStream_t stream, uint64_t *launches, StageTimer &tm);
 
 }  // namespace dirt

@@ -1,0 +1,166 @@
+"""Geometry and lighting helpers with the names, argument order and arithmetic of the reference's
+dirt/lighting.py, on torch tensors.
+
+`vertex_normals` is the expensive one -- the reference builds a sparse tensor with 9*F*N entries
+and reduces it (dirt/lighting.py:74-88) -- and runs as hand-written CUDA kernels behind the C ABI
+(`dirt_vertex_normals`, `dirt_vertex_normals_grad`; dirt_b200/csrc/geometry.cu) with autograd wired.
+The shading functions are per-point arithmetic: they are written with torch operations (one to
+five element-wise kernels each, differentiable by torch), formula by formula as the reference has
+them, including its `+ 1e-12` terms.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import InvalidArgumentError
+
+
+def _prepare_vertices_and_faces(vertices, faces):
+    # dirt/lighting.py:12-21
+    vertices = torch.as_tensor(vertices)
+    faces = torch.as_tensor(faces, device=vertices.device)
+    if faces.dtype != torch.int32:
+        if faces.dtype != torch.int64:
+            raise InvalidArgumentError(-1, "faces must be int32 or int64")
+        faces = faces.to(torch.int32)
+    if faces.dim() != 2 or faces.shape[1] != 3:
+        raise InvalidArgumentError(-1, "faces must be [face count, 3]")
+    if vertices.dim() < 2 or vertices.shape[-1] not in (3, 4):
+        raise InvalidArgumentError(-1, "vertices must be [*, vertex count, 3] or [*, vertex count, 4]")
+    return vertices, faces
+
+
+class _VertexNormals(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, vertices, faces):
+        lib = _lib.load()
+        if not vertices.is_cuda:
+            raise RuntimeError("dirt_b200.lighting.vertex_normals needs CUDA tensors; there is no CPU fallback")
+        lead, (V, D) = vertices.shape[:-2], vertices.shape[-2:]
+        v = vertices.to(torch.float32).reshape(-1, V, D).contiguous()
+        f = faces.contiguous()
+        B = v.shape[0]
+        sums = torch.empty((B, V, 3), dtype=torch.float32, device=v.device)
+        normals = torch.empty((B, V, 3), dtype=torch.float32, device=v.device)
+        with torch.cuda.device(v.device):
+            _lib.check(lib.dirt_vertex_normals(v.data_ptr(), B, V, D, f.data_ptr(), f.shape[0], sums.data_ptr(),
+                                               normals.data_ptr(), torch.cuda.current_stream(v.device).cuda_stream))
+        ctx.save_for_backward(v, f, sums)
+        ctx.shape = tuple(vertices.shape)
+        return normals.reshape(*lead, V, 3)
+
+    @staticmethod
+    def backward(ctx, grad_normals):
+        lib = _lib.load()
+        v, f, sums = ctx.saved_tensors
+        B, V, D = v.shape
+        g = grad_normals.to(torch.float32).reshape(B, V, 3).contiguous()
+        grad_sums = torch.empty_like(sums)
+        grad_vertices = torch.empty_like(v)
+        with torch.cuda.device(v.device):
+            _lib.check(lib.dirt_vertex_normals_grad(v.data_ptr(), B, V, D, f.data_ptr(), f.shape[0], sums.data_ptr(),
+                                                    g.data_ptr(), grad_sums.data_ptr(), grad_vertices.data_ptr(),
+                                                    torch.cuda.current_stream(v.device).cuda_stream))
+        return grad_vertices.reshape(ctx.shape), None
+
+
+def vertex_normals(vertices, faces, name=None):
+    """Vertex normals of a batch of meshes with common topology (dirt/lighting.py:34-93).
+    vertices [*, V, 3|4] (w ignored), faces [F, 3]; returns [*, V, 3]: for each vertex the
+    normalised sum of the unit normals of the faces that use it."""
+    del name
+    vertices, faces = _prepare_vertices_and_faces(vertices, faces)
+    return _VertexNormals.apply(vertices, faces)
+
+
+def vertex_normals_pre_split(vertices, faces, name=None, static=False):
+    """dirt/lighting.py:101-133: vertex normals of a mesh whose vertices are each used by exactly
+    one face (e.g. the output of `split_vertices_by_face`).  NOTE the reference does NOT
+    re-normalise here: a vertex gets its face's unit normal, and an unused vertex gets zeros --
+    which is what the general kernel's `sums` output holds, so this returns it."""
+    del name, static
+    vertices, faces = _prepare_vertices_and_faces(vertices, faces)
+    return _FaceNormalSums.apply(vertices, faces)
+
+
+class _FaceNormalSums(torch.autograd.Function):
+    """The un-normalised per-vertex sum of unit face normals (first kernel of `vertex_normals`)."""
+
+    @staticmethod
+    def forward(ctx, vertices, faces):
+        lib = _lib.load()
+        if not vertices.is_cuda:
+            raise RuntimeError("dirt_b200.lighting.vertex_normals_pre_split needs CUDA tensors; there is no CPU fallback")
+        lead, (V, D) = vertices.shape[:-2], vertices.shape[-2:]
+        v = vertices.to(torch.float32).reshape(-1, V, D).contiguous()
+        f = faces.contiguous()
+        B = v.shape[0]
+        sums = torch.empty((B, V, 3), dtype=torch.float32, device=v.device)
+        scratch = torch.empty((B, V, 3), dtype=torch.float32, device=v.device)
+        with torch.cuda.device(v.device):
+            _lib.check(lib.dirt_vertex_normals(v.data_ptr(), B, V, D, f.data_ptr(), f.shape[0], sums.data_ptr(),
+                                               scratch.data_ptr(), torch.cuda.current_stream(v.device).cuda_stream))
+        ctx.save_for_backward(v, f)
+        ctx.shape = tuple(vertices.shape)
+        return sums.reshape(*lead, V, 3)
+
+    @staticmethod
+    def backward(ctx, grad_sums):
+        lib = _lib.load()
+        v, f = ctx.saved_tensors
+        B, V, D = v.shape
+        g = grad_sums.to(torch.float32).reshape(B, V, 3).contiguous()
+        grad_vertices = torch.empty_like(v)
+        with torch.cuda.device(v.device):
+            # sums = NULL: skip the final normalisation stage (include/dirt_b200.h)
+            _lib.check(lib.dirt_vertex_normals_grad(v.data_ptr(), B, V, D, f.data_ptr(), f.shape[0], None, g.data_ptr(), None,
+                                                    grad_vertices.data_ptr(), torch.cuda.current_stream(v.device).cuda_stream))
+        return grad_vertices.reshape(ctx.shape), None
+
+
+def split_vertices_by_face(vertices, faces, name=None):
+    """dirt/lighting.py:136-179: an equivalent mesh in which every vertex is used by exactly one
+    face.  Returns (new_vertices [*, 3F, D], new_faces [F, 3])."""
+    del name
+    vertices, faces = _prepare_vertices_and_faces(vertices, faces)
+    new_vertices = vertices.index_select(-2, faces.reshape(-1).long())
+    new_faces = torch.arange(faces.shape[0] * 3, dtype=torch.int32, device=faces.device).reshape(-1, 3)
+    return new_vertices, new_faces
+
+
+def _cosine_term(cosines, double_sided):
+    return cosines.abs() if double_sided else cosines.clamp_min(0.)
+
+
+def diffuse_directional(vertex_normals, vertex_colors, light_direction, light_color, double_sided=True, name=None):
+    """Lambertian reflectance under one directional light (dirt/lighting.py:182-225).
+    vertex_normals [*, V, 3], vertex_colors [*, V, C], light_direction [*, 3], light_color [*, C]."""
+    del name
+    n, c, d, lc = (torch.as_tensor(x) for x in (vertex_normals, vertex_colors, light_direction, light_color))
+    cosines = torch.matmul(n, -d.unsqueeze(-1))                       # [*, V, 1]
+    return lc.unsqueeze(-2) * c * _cosine_term(cosines, double_sided)
+
+
+def specular_directional(vertex_positions, vertex_normals, vertex_reflectivities, light_direction, light_color,
+                         camera_position, shininess, double_sided=True, name=None):
+    """Phong reflectance under one directional light (dirt/lighting.py:228-288), including the
+    reference's operator precedence: the 1e-12 is added AFTER the division by the norm."""
+    del name
+    p, n, r, d, lc, cam, sh = (torch.as_tensor(x) for x in (vertex_positions, vertex_normals, vertex_reflectivities,
+                                                            light_direction, light_color, camera_position, shininess))
+    to_light = -d
+    reflected = -to_light.unsqueeze(-2) + 2. * torch.matmul(n, to_light.unsqueeze(-1)) * n
+    to_camera = cam.unsqueeze(-2) - p
+    cosines = ((to_camera / to_camera.norm(dim=-1, keepdim=True) + 1.e-12) * reflected).sum(dim=-1, keepdim=True)
+    return lc.unsqueeze(-2) * r * torch.pow(_cosine_term(cosines, double_sided), sh[..., None, None])
+
+
+def diffuse_point(vertex_positions, vertex_normals, vertex_colors, light_position, light_color, double_sided=True, name=None):
+    """Lambertian reflectance under one point light (dirt/lighting.py:291-343)."""
+    del name
+    p, n, c, lp, lc = (torch.as_tensor(x) for x in (vertex_positions, vertex_normals, vertex_colors, light_position, light_color))
+    relative = p - lp.unsqueeze(-2)
+    incident = relative / (relative.norm(dim=-1, keepdim=True) + 1.e-12)
+    cosines = (n * incident).sum(dim=-1)
+    return lc.unsqueeze(-2) * c * _cosine_term(cosines, double_sided).unsqueeze(-1)

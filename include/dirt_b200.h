@@ -118,6 +118,22 @@ typedef struct DirtSharedBackwardArgs {
 DIRT_API int dirt_shared_grad_stride(int channels);
 DIRT_API int dirt_rasterise_backward_shared(const DirtSharedBackwardArgs *args, void *stream);
 
+/* Vertex normals of `batch` meshes with common topology: replaces
+ * vertex_normals / vertex_normals_pre_split, dirt/lighting.py:34-93, :101-133 -- the normalised
+ * sum, per vertex, of the unit normals (v1 - v0) x (v2 - v0) of the faces that use it, with the
+ * reference's + 1e-12 in both normalisations.  vertices [batch, V, D], D = 3 or 4 (w ignored);
+ * faces [F,3] shared by the batch; sums [batch,V,3] (un-normalised, kept for the backward) and
+ * normals [batch,V,3] are outputs.  Faces with an index outside [0,V) are skipped. */
+DIRT_API int dirt_vertex_normals(const float *vertices, int batch, int vertex_count, int vertex_dim, const int32_t *faces,
+                                 int face_count, float *sums, float *normals, void *stream);
+/* Its backward: grad_normals [batch,V,3] -> grad_vertices [batch,V,D] (zero-initialised by the
+ * callee; the w column stays zero).  grad_sums [batch,V,3] is scratch.  With sums == NULL the
+ * final normalisation is left out: grad_normals is taken as the gradient w.r.t. the `sums`
+ * output (the un-renormalised normals of vertex_normals_pre_split). */
+DIRT_API int dirt_vertex_normals_grad(const float *vertices, int batch, int vertex_count, int vertex_dim, const int32_t *faces,
+                                      int face_count, const float *sums, const float *grad_normals, float *grad_sums,
+                                      float *grad_vertices, void *stream);
+
 /* Library identity. */
 DIRT_API int dirt_abi_version(void);
 /* Thread-local message of the last failing call on this thread ("" if none). */

@@ -1,0 +1,175 @@
+"""geometry / lighting helpers (dirt/lighting.py, dirt/matrices.py).
+CPU part: the numpy oracle against hand-derived cases, and the torch composites of
+dirt_b200.lighting / dirt_b200.matrices against the oracle (they run on CPU tensors too).
+GPU part: the vertex-normal CUDA kernels, forward and backward, against the oracle and against
+torch autograd in float64."""
+import numpy as np
+import pytest
+import torch
+
+import scenes
+from oracle import lighting as ol
+from dirt_b200 import lighting, matrices
+
+
+def _cube():
+    v, f = scenes.cube_mesh()
+    return np.asarray(v, np.float64), np.asarray(f, np.int32)
+
+
+# ---- oracle pinned by hand cases ------------------------------------------------------------
+
+def test_oracle_face_and_vertex_normals_of_one_triangle_and_a_cube():
+    tri = np.array([[0., 0., 0.], [1., 0., 0.], [0., 1., 0.]])
+    f = np.array([[0, 1, 2]], np.int32)
+    assert np.allclose(ol.face_normals(tri, f), [[0., 0., 1.]])
+    assert np.allclose(ol.vertex_normals(tri, f), [[0., 0., 1.]] * 3)
+    assert np.allclose(ol.face_normals(tri, f[:, ::-1]), [[0., 0., -1.]])        # winding flips the normal
+    # two triangles at a right angle sharing the edge v0-v1: normals +z and +y
+    v = np.array([[0., 0., 0.], [1., 0., 0.], [0., 1., 0.], [0., 0., 1.]])
+    f2 = np.array([[0, 1, 2], [0, 3, 1]], np.int32)
+    assert np.allclose(ol.face_normals(v, f2), [[0., 0., 1.], [0., 1., 0.]])
+    r = np.sqrt(0.5)
+    assert np.allclose(ol.vertex_normals(v, f2), [[0., r, r], [0., r, r], [0., 0., 1.], [0., 1., 0.]])
+    assert np.allclose(ol.vertex_normal_sums(v, f2), [[0., 1., 1.], [0., 1., 1.], [0., 0., 1.], [0., 1., 0.]])
+    # the pre-split cube of samples/simple.py: every vertex carries its own face's axis-aligned normal
+    cv, cf = _cube()
+    n = ol.vertex_normals(cv, cf)
+    assert np.allclose(np.abs(n).sum(-1), 1.0) and np.allclose(np.abs(n).max(-1), 1.0)
+    assert np.allclose(n.reshape(12, 3, 3), ol.face_normals(cv, cf)[:, None, :])
+
+
+def test_oracle_matrices_known_values():
+    R = ol.rodrigues([0., 0., np.pi / 2])
+    # K is written [in, out] in dirt/matrices.py:44-48, so a ROW vector turns clockwise about +z
+    assert np.allclose(np.array([1., 0., 0., 1.]) @ R, [0., -1., 0., 1.], atol=1e-9)
+    # (the scene-fixture helper tests/scenes.py:rodrigues turns the other way; it only poses test meshes)
+    assert np.allclose(R[:3, :3], scenes.rodrigues([0., 0., np.pi / 2]).T, atol=1e-9)
+    T = ol.translation([1., 2., 3.])
+    assert np.allclose(np.array([0., 0., 0., 1.]) @ T, [1., 2., 3., 1.])
+    P = ol.perspective_projection(0.1, 10., 0.05, 0.75)
+    near_pt = np.array([0.05, 0.0375, -0.1, 1.]) @ P                                  # top-right corner of the near plane
+    assert np.allclose(near_pt[:3] / near_pt[3], [1., 1., -1.])
+    far_pt = np.array([0., 0., -10., 1.]) @ P
+    assert np.allclose(far_pt[2] / far_pt[3], 1.)
+    assert np.allclose(ol.compose(T, R), T @ R) and np.allclose(ol.compose(), np.eye(4))
+    assert np.allclose(ol.pad_3x3_to_4x4(2 * np.eye(3)), np.diag([2., 2., 2., 1.]))
+
+
+# ---- torch composites against the oracle (CPU tensors) ----------------------------------------
+
+def test_matrices_match_the_oracle():
+    rng = np.random.RandomState(0)
+    vecs = rng.randn(5, 3)
+    np.testing.assert_allclose(matrices.rodrigues(torch.tensor(vecs)).numpy(), ol.rodrigues(vecs), atol=1e-12)
+    np.testing.assert_allclose(matrices.rodrigues(torch.zeros(3, dtype=torch.float64)).numpy(), ol.rodrigues(np.zeros(3)), atol=1e-12)
+    np.testing.assert_allclose(matrices.translation(torch.tensor(vecs)).numpy(), ol.translation(vecs))
+    np.testing.assert_allclose(matrices.perspective_projection(0.1, 20., 0.05, 0.75).numpy(),
+                               ol.perspective_projection(0.1, 20., 0.05, 0.75), rtol=1e-6)
+    m3 = rng.randn(2, 3, 3)
+    np.testing.assert_allclose(matrices.pad_3x3_to_4x4(torch.tensor(m3)).numpy(), ol.pad_3x3_to_4x4(m3))
+    a, b, c = (torch.tensor(rng.randn(4, 4)) for _ in range(3))
+    np.testing.assert_allclose(matrices.compose(a, b, c).numpy(), ol.compose(a.numpy(), b.numpy(), c.numpy()))
+    assert torch.equal(matrices.compose(), torch.eye(4)) and matrices.compose(a) is a
+    # rodrigues is differentiable at exactly zero (the reason for the reference's + 1e-12)
+    z = torch.zeros(3, dtype=torch.float64, requires_grad=True)
+    matrices.rodrigues(z).sum().backward()
+    assert torch.isfinite(z.grad).all()
+
+
+@pytest.mark.parametrize("double_sided", [True, False])
+def test_shading_functions_match_the_oracle(double_sided):
+    rng = np.random.RandomState(1)
+    B, V, C = 2, 50, 3
+    n = rng.randn(B, V, 3)
+    n /= np.linalg.norm(n, axis=-1, keepdims=True)
+    p, col = rng.randn(B, V, 3), rng.uniform(0, 1, (B, V, C))
+    d = rng.randn(B, 3)
+    d /= np.linalg.norm(d, axis=-1, keepdims=True)
+    lc, cam, lp, sh = rng.uniform(0, 1, (B, C)), rng.randn(B, 3) * 3, rng.randn(B, 3) * 3, rng.uniform(1, 8, B)
+    t = lambda *xs: [torch.tensor(x) for x in xs]  # noqa: E731
+    np.testing.assert_allclose(lighting.diffuse_directional(*t(n, col, d, lc), double_sided=double_sided).numpy(),
+                               ol.diffuse_directional(n, col, d, lc, double_sided), rtol=1e-12, atol=1e-14)
+    np.testing.assert_allclose(lighting.diffuse_point(*t(p, n, col, lp, lc), double_sided=double_sided).numpy(),
+                               ol.diffuse_point(p, n, col, lp, lc, double_sided), rtol=1e-12, atol=1e-14)
+    np.testing.assert_allclose(lighting.specular_directional(*t(p, n, col, d, lc, cam, sh), double_sided=double_sided).numpy(),
+                               ol.specular_directional(p, n, col, d, lc, cam, sh, double_sided), rtol=1e-10, atol=1e-14)
+
+
+def test_split_vertices_by_face_matches_the_oracle():
+    v, f = _cube()
+    vb = np.stack([v, v * 2.0])
+    nv, nf = lighting.split_vertices_by_face(torch.tensor(vb), torch.tensor(f))
+    ov, of = ol.split_vertices_by_face(vb, f)
+    assert np.array_equal(nv.numpy(), ov) and np.array_equal(nf.numpy(), of) and nf.dtype == torch.int32
+    with pytest.raises(ValueError):
+        lighting.split_vertices_by_face(torch.tensor(vb), torch.tensor(f[:, :2]))
+
+
+# ---- the CUDA kernels ---------------------------------------------------------------------------
+
+def _torch_reference(v, f, renormalise):
+    p = v[..., :3]
+    idx = f.long()
+    m = torch.cross(p[:, idx[:, 1]] - p[:, idx[:, 0]], p[:, idx[:, 2]] - p[:, idx[:, 0]], dim=-1)
+    n = m / (m.norm(dim=-1, keepdim=True) + 1.e-12)
+    s = torch.zeros_like(p)
+    for k in range(3):
+        s = s.index_add(1, idx[:, k], n)
+    return s / (s.norm(dim=-1, keepdim=True) + 1.e-12) if renormalise else s
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("D", [3, 4])
+def test_vertex_normals_forward_and_backward_on_the_gpu(D):
+    mesh_v, mesh_f = scenes.uv_sphere_mesh(24, 32)
+    rng = np.random.RandomState(2)
+    v = np.stack([mesh_v * s + 0.05 * rng.randn(*mesh_v.shape) for s in (1.0, 1.7, 0.4)]).astype(np.float32)
+    if D == 4:
+        v = np.concatenate([v, np.ones(v.shape[:2] + (1,), np.float32)], -1)
+    f = mesh_f.astype(np.int32)
+    vt = torch.tensor(v, device="cuda", requires_grad=True)
+    ft = torch.tensor(f, device="cuda")
+    out = lighting.vertex_normals(vt, ft)
+    np.testing.assert_allclose(out.detach().cpu().numpy(), ol.vertex_normals(v, f), atol=2e-6)
+    g = torch.tensor(rng.randn(*out.shape).astype(np.float32), device="cuda")
+    out.backward(g)
+    v64 = torch.tensor(v, dtype=torch.float64, device="cuda", requires_grad=True)
+    _torch_reference(v64, ft, True).backward(g.double())
+    exp = v64.grad.cpu().numpy()
+    got = vt.grad.cpu().numpy()
+    assert got.shape == v.shape
+    assert np.abs(got[..., :3] - exp[..., :3]).max() <= 1e-4 * np.abs(exp).max()
+    if D == 4:
+        assert not got[..., 3].any()
+    # leading dims other than one batch axis, and int64 faces
+    out2 = lighting.vertex_normals(torch.tensor(v[0], device="cuda"), ft.long())
+    assert torch.allclose(out2, out[0].detach(), atol=1e-6)      # float reductions: summation order varies
+
+
+@pytest.mark.gpu
+def test_vertex_normals_pre_split_keeps_the_face_normal():
+    v, f = _cube()
+    sv, sf = ol.split_vertices_by_face(v[None].astype(np.float32), f)
+    vt = torch.tensor(sv, device="cuda", requires_grad=True)
+    ft = torch.tensor(sf, device="cuda")
+    out = lighting.vertex_normals_pre_split(vt, ft)
+    np.testing.assert_allclose(out.detach().cpu().numpy(), ol.vertex_normal_sums(sv, sf), atol=1e-6)
+    np.testing.assert_allclose(out.detach().cpu().numpy()[0].reshape(-1, 3, 3)[:, 0], ol.face_normals(v, f), atol=1e-6)
+    g = torch.randn_like(out)
+    out.backward(g)
+    v64 = torch.tensor(sv, dtype=torch.float64, device="cuda", requires_grad=True)
+    _torch_reference(v64, ft, False).backward(g.double())
+    assert np.abs(vt.grad.cpu().numpy() - v64.grad.cpu().numpy()).max() <= 1e-4 * np.abs(v64.grad.cpu().numpy()).max()
+
+
+@pytest.mark.gpu
+def test_vertex_normals_edge_cases():
+    ft = torch.zeros((0, 3), dtype=torch.int32, device="cuda")
+    out = lighting.vertex_normals(torch.rand(2, 5, 3, device="cuda"), ft)                 # no faces: all zero
+    assert out.shape == (2, 5, 3) and not out.any()
+    bad = torch.tensor([[0, 1, 7], [0, 1, 2]], dtype=torch.int32, device="cuda")           # out-of-range face is skipped
+    v = torch.tensor([[0., 0., 0.], [1., 0., 0.], [0., 1., 0.]], device="cuda")
+    assert torch.allclose(lighting.vertex_normals(v, bad), torch.tensor([[0., 0., 1.]] * 3, device="cuda"))
+    with pytest.raises(RuntimeError):
+        lighting.vertex_normals(torch.rand(5, 3), torch.zeros((1, 3), dtype=torch.int32))    # CPU tensors: no fallback
