@@ -5,6 +5,8 @@ The public names mirror the reference package (`import dirt`): dirt/__init__.py:
 dirt/rasterise_ops.py.
 """
 from .rasterise_ops import rasterise, rasterise_batch, rasterise_batch_shared, rasterise_grad  # noqa: F401
-from .scene_ops import oceanic_horizon, oceanic_horizon_batch  # noqa: F401
+from .scene_ops import (hill, hill_batch, oceanic, oceanic_batch, oceanic_horizon, oceanic_horizon_batch,  # noqa: F401
+                        oceanic_no_cloud, oceanic_no_cloud_batch, oceanic_opt_flow, oceanic_opt_flow_batch,
+                        oceanic_simple_proxy, oceanic_simple_proxy_batch, oceanic_still_cloud, oceanic_still_cloud_batch)
 from .deferred import dilate_silhouette, rasterise_gbuffer  # noqa: F401
 from ._lib import DirtError, InvalidArgumentError  # noqa: F401

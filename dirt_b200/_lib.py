@@ -71,6 +71,8 @@ EXPORTS = {
     "dirt_rasterise_backward_host": (ctypes.c_int, [ctypes.POINTER(DirtBackwardArgs)]),
     "dirt_release_host_staging": (ctypes.c_int, []),
     "dirt_scene_oceanic_horizon": (ctypes.c_int, [ctypes.POINTER(DirtSceneArgs), ctypes.c_void_p]),
+    "dirt_scene_camera_floats": (ctypes.c_int, [ctypes.c_int]),
+    "dirt_scene_shade": (ctypes.c_int, [ctypes.c_int, ctypes.POINTER(DirtSceneArgs), ctypes.c_int, ctypes.c_int, ctypes.c_void_p]),
     "dirt_vertex_normals": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 3 + [ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 3),
     "dirt_vertex_normals_grad": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 3 + [ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 5),
     "dirt_dilate_silhouette": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p] + [ctypes.c_int] * 4 + [ctypes.c_void_p]),

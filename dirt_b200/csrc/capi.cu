@@ -138,6 +138,8 @@ int current_sm_count(int *out)
 
 }  // namespace
 
+namespace dirt { void note_launches(uint64_t n) { g_launches += n; } }
+
 extern "C" {
 
 int dirt_abi_version(void) { return DIRT_B200_ABI_VERSION; }

@@ -100,5 +100,7 @@ cudaError_t launch_vertex_normals(const float *vertices, int B, int V, int D, co
 cudaError_t launch_vertex_normals_grad(const float *vertices, int B, int V, int D, const int32_t *faces, int F, const float *sums,
                                        const float *grad_normals, float *grad_sums, float *grad_vertices, cudaStream_t stream);
 cudaError_t launch_backward(const BwdParams &p, int sm_count, cudaStream_t stream, uint64_t *launches, StageTimer &tm);
+// capi.cu: adds to the counter behind dirt_kernel_launch_count (scene stages launch outside capi.cu)
+void note_launches(uint64_t n);
 
 }  // namespace dirt

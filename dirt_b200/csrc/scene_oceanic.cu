@@ -10,6 +10,7 @@
 // (csrc/rasterise_egl.cpp:323) has no counterpart.  Dead shader code (godrays, the zero-weighted
 // small-wave octaves) is listed in DESIGN.md and not evaluated.
 #include "forward_common.cuh"
+#include "kernels.h"
 
 namespace dirt {
 
@@ -114,6 +115,7 @@ cudaError_t launch_oceanic_horizon(const SceneParams &p, cudaStream_t stream)
     if ((long long)p.B * p.H * p.W == 0) return cudaSuccess;
     const dim3 g((unsigned)((p.H * p.W + 255) / 256), (unsigned)(p.B < 65535 ? p.B : 65535));
     k_oceanic_horizon<<<g, 256, 0, stream>>>(p);
+    note_launches(1);
     return cudaGetLastError();
 }
 

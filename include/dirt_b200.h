@@ -180,6 +180,35 @@ typedef struct DirtSceneArgs {
 } DirtSceneArgs;
 DIRT_API int dirt_scene_oceanic_horizon(const DirtSceneArgs *args, void *stream);
 
+/* The fork's other procedural scene ops (dirt/rasterise_ops.py:91-205): same inputs and outputs as
+ * `Rasterise`, a different fragment program per op.  One entry point, selected by `scene`:
+ *   OCEANIC              op "RasteriseGrad"      csrc/rasterise_grad_egl.cpp:33, :399  shaders.cpp:556-865
+ *   OCEANIC_STILL_CLOUD  op "OceanicStillCloud"  csrc/oceanic_still_cloud.cpp:33, :385 shaders.cpp:866-1175
+ *   OCEANIC_NO_CLOUD     op "OceanicNoCloud"     csrc/oceanic_no_cloud.cpp:33, :385    shaders.cpp:1402-1665
+ *   OCEANIC_SIMPLE_PROXY op "OceanicSimpleProxy" csrc/oceanic_simple_proxy.cpp:33, :385 shaders.cpp:1921-2185
+ *   OCEANIC_OPT_FLOW     op "OceanicOptFlow"     csrc/oceanic_opt_flow.cpp:33, :385    shaders.cpp:1178-1398
+ *   HILL                 op "Hill"               csrc/hill.cpp:33, :378                shaders.cpp:123-552
+ * Call after dirt_rasterise_forward (face_id / gbuffer requested) on the same stream; covered
+ * pixels of `pixels` [B,H,W,shape.channels] receive fragColor.xyz, the rest keep what they hold.
+ * `background` is [B,H,W,background_channels] with background_channels in {1,3,4} (the upload
+ * kernel's cases, csrc/rasterise_egl.cu:29-48): the sample jitter of the ocean ops, the terrain
+ * height + normal texture of HILL (bilinear, clamp to edge, each frame its own texture).
+ * camera_pos is a DEVICE pointer to camera_pos_count floats; the count each scene reads is
+ * dirt_scene_camera_floats(scene) (8, 8, 9, 8, 8, 16, 12 -- the cudaMemcpy sizes at :323 of each
+ * op file); fewer is DIRT_STATUS_INVALID_ARGUMENT.  OPT_FLOW writes the previous-frame pixel
+ * coordinates into channels 0 and 1. */
+enum {
+    DIRT_SCENE_OCEANIC_HORIZON = 0,
+    DIRT_SCENE_OCEANIC = 1,
+    DIRT_SCENE_OCEANIC_STILL_CLOUD = 2,
+    DIRT_SCENE_OCEANIC_NO_CLOUD = 3,
+    DIRT_SCENE_OCEANIC_SIMPLE_PROXY = 4,
+    DIRT_SCENE_OCEANIC_OPT_FLOW = 5,
+    DIRT_SCENE_HILL = 6
+};
+DIRT_API int dirt_scene_camera_floats(int scene);
+DIRT_API int dirt_scene_shade(int scene, const DirtSceneArgs *args, int background_channels, int camera_pos_count, void *stream);
+
 /* Host-buffer convenience calls: every pointer in `args` is HOST memory (pinned or pageable);
  * the library stages inputs to the current device, runs the kernels and copies the outputs
  * back, then synchronises.  workspace / workspace_bytes are ignored (library-owned, grow-only,

@@ -18,11 +18,15 @@ _lib = None
 
 _SO_SCENE = os.path.join(_HERE, "_build", "libscene_oceanic.so")
 _scene = None
+_SO_SHADERS = os.path.join(_HERE, "_build", "libscene_shaders.so")
+_shaders = None
+SCENES = {"oceanic_horizon": 0, "oceanic": 1, "oceanic_still_cloud": 2, "oceanic_no_cloud": 3, "oceanic_simple_proxy": 4,
+          "oceanic_opt_flow": 5, "hill": 6}
 
 
 def build(force=False):
     stale = force
-    for so, src in ((_SO, "golden_raster.c"), (_SO_SCENE, "scene_oceanic.c")):
+    for so, src in ((_SO, "golden_raster.c"), (_SO_SCENE, "scene_oceanic.c"), (_SO_SHADERS, "scene_shaders.cpp")):
         src = os.path.join(_HERE, src)
         stale = stale or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src)
     if stale:
@@ -139,4 +143,39 @@ def oceanic_horizon(background, vertices, faces, camera_pos, threads=1):
                                        pixels.ctypes.data)
     if rc != 0:
         raise RuntimeError("golden_oceanic_horizon failed: %d" % rc)
+    return pixels
+
+
+def scene(name, background, vertices, faces, camera_pos, channels=None, threads=1):
+    """Any of the fork's scene ops (SCENES) on the CPU: coverage and the interpolated texCoordV from
+    the golden rasteriser, then the shader restated in oracle/scene_shaders.cpp (scene_oceanic.c
+    for oceanic_horizon).  background [B,H,W,Cb]; for hill it is the terrain texture and
+    `channels` (default 3) sizes the output, whose uncovered pixels are 0."""
+    global _shaders
+    sid = SCENES[name]
+    if sid == 0:
+        return oceanic_horizon(background, vertices, faces, camera_pos, threads=threads)
+    build()
+    if _shaders is None:
+        _shaders = ctypes.CDLL(_SO_SHADERS)
+        vp = ctypes.c_void_p
+        _shaders.golden_scene_shade.argtypes = [ctypes.c_int] * 6 + [vp] * 4 + [ctypes.c_int, vp]
+        _shaders.golden_scene_shade.restype = ctypes.c_int
+    bg = _prep(background, np.float32, 4, "background")
+    v = _prep(vertices, np.float32, 3, "vertices")
+    B = max(bg.shape[0], v.shape[0])
+    _, H, W, Cb = bg.shape
+    bgB = np.ascontiguousarray(np.broadcast_to(bg, (B, H, W, Cb)))
+    tc, fid, _ = forward(np.zeros((B, H, W, 2), np.float32), v, v[..., :2], faces, threads=threads)
+    cam = np.ascontiguousarray(camera_pos, np.float32).reshape(-1)
+    if sid == 6:
+        C = 3 if channels is None else int(channels)
+        pixels = np.zeros((B, H, W, C), np.float32)
+    else:
+        C = Cb
+        pixels = bgB.copy()
+    rc = _shaders.golden_scene_shade(sid, B, H, W, C, Cb, tc.ctypes.data, fid.ctypes.data, bgB.ctypes.data, cam.ctypes.data,
+                                     int(cam.size), pixels.ctypes.data)
+    if rc != 0:
+        raise ValueError("golden_scene_shade rejected its arguments (scene %s, %d camera values)" % (name, cam.size))
     return pixels

@@ -38,12 +38,26 @@ def oracle_case(sc, seed):
     return out
 
 
+def scene_cases():
+    """One small render of every scene op by the oracle (oracle/scene_oceanic.c, scene_shaders.cpp):
+    inputs are rebuilt from tests/test_scene_shaders.py, only the images are stored."""
+    import test_scene_shaders as T
+    H, W = 36, 64
+    out = {}
+    bg, v, c, f = T.quad(1, H, W, 3, seed=5, noise=0.4)
+    for name in ["oceanic_horizon"] + T.OCEAN_SCENES:
+        out[name] = golden.scene(name, bg, v, f, T.CAM_A)
+    out["hill"] = golden.scene("hill", T.terrain_texture(H, W)[None], v, f, T.HILL_CAM)
+    return out
+
+
 def main():
     for name, sc in (("kat1", scenes.kat1_square()), ("kat2", scenes.kat2_square())):
         np.savez_compressed(os.path.join(HERE, name + ".npz"), **sc)
     np.savez_compressed(os.path.join(HERE, "cylinder.npz"), **oracle_case(scenes.cylinder(), 0))
     np.savez_compressed(os.path.join(HERE, "cube.npz"), **oracle_case(scenes.cube(B=2, H=64, W=64), 1))
     np.savez_compressed(os.path.join(HERE, "clip.npz"), **oracle_case(scenes.near_crossing(B=1, H=48, W=64), 2))
+    np.savez_compressed(os.path.join(HERE, "scenes.npz"), **scene_cases())
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):
             print(f, os.path.getsize(os.path.join(HERE, f)), "bytes")

@@ -144,3 +144,86 @@ public:
     }
 };
 REGISTER_KERNEL_BUILDER(Name("RasteriseGrad").Device(DEVICE_GPU), RasteriseGradOpB200);
+
+// ---- the fork's procedural scene ops --------------------------------------------------------
+// Same inputs / attrs / output as "Rasterise" (csrc/hill.cpp:33-53, csrc/oceanic_*.cpp:33-53); the
+// fragment program is selected by the op name.  Each runs the rasteriser for coverage, then
+// dirt_scene_shade on the same stream.  camera_pos stays on the device (no cudaMemcpy as at :323).
+template <int SCENE> class SceneOpB200 : public OpKernel {
+public:
+    explicit SceneOpB200(OpKernelConstruction *c) : OpKernel(c)
+    {
+        OP_REQUIRES_OK(c, c->GetAttr("height", &height_));
+        OP_REQUIRES_OK(c, c->GetAttr("width", &width_));
+        OP_REQUIRES_OK(c, c->GetAttr("channels", &channels_));
+    }
+    void Compute(OpKernelContext *ctx) override
+    {
+        const Tensor &bg = ctx->input(0), &v = ctx->input(1), &col = ctx->input(2), &f = ctx->input(3), &cam = ctx->input(4);
+        const bool hill = SCENE == DIRT_SCENE_HILL;   // csrc/hill.cpp:310 drops the channel check: the background is the terrain texture
+        OP_REQUIRES(ctx, bg.dims() == 4 && bg.dim_size(1) == height_ && bg.dim_size(2) == width_ && (hill || bg.dim_size(3) == channels_),
+                    errors::InvalidArgument("Rasterise expects background_tensor to be 4D, and bgcolor.shape == [None, height, width, channels]"));
+        OP_REQUIRES(ctx, v.dims() == 3 && v.dim_size(2) == 4, errors::InvalidArgument("Rasterise expects vertices to be 3D, and vertices.shape[2] == 4"));
+        OP_REQUIRES(ctx, f.dims() == 3 && f.dim_size(2) == 3, errors::InvalidArgument("Rasterise expects faces to be 3D, and faces.shape[2] == 3"));
+        DirtForwardArgs a = {};
+        a.shape = shape_of(bg, v, f, channels_);
+        const int64 B = a.shape.batch;
+        auto stride = [B](const Tensor &t) -> int64_t { return t.dim_size(0) == 1 && B > 1 ? 0 : t.NumElements() / std::max<int64>(t.dim_size(0), 1); };
+        Tensor *pixels, face_id, gbuffer, ws, blank;
+        OP_REQUIRES_OK(ctx, ctx->allocate_output(0, {B, height_, width_, channels_}, &pixels));
+        OP_REQUIRES_OK(ctx, ctx->allocate_temp(DT_INT32, {B, height_, width_}, &face_id));
+        OP_REQUIRES_OK(ctx, ctx->allocate_temp(DT_FLOAT, {B, height_, width_, 4}, &gbuffer));
+        if (hill) {   // uncovered pixels of the hill target are 0: rasterise over a blank background
+            OP_REQUIRES_OK(ctx, ctx->allocate_temp(DT_FLOAT, {1, height_, width_, channels_}, &blank));
+            cudaMemsetAsync(blank.flat<float>().data(), 0, blank.NumElements() * sizeof(float), static_cast<cudaStream_t>(cuda_stream_of(ctx)));
+            a.background = blank.flat<float>().data();  a.background_bstride = B > 1 ? 0 : blank.NumElements();
+        } else {
+            a.background = bg.flat<float>().data();     a.background_bstride = stride(bg);
+        }
+        a.vertices = v.flat<float>().data();           a.vertices_bstride = stride(v);
+        a.vertex_colors = col.flat<float>().data();    a.vertex_colors_bstride = stride(col);
+        a.faces = f.flat<int32>().data();              a.faces_bstride = stride(f);
+        a.workspace_bytes = dirt_workspace_bytes(&a.shape);
+        OP_REQUIRES_OK(ctx, ctx->allocate_temp(DT_UINT8, {static_cast<int64>(a.workspace_bytes)}, &ws));
+        a.pixels = pixels->flat<float>().data();
+        a.face_id = face_id.flat<int32>().data();
+        a.gbuffer = gbuffer.flat<float>().data();
+        a.workspace = ws.flat<uint8>().data();
+        OP_REQUIRES_OK(ctx, status_from(dirt_rasterise_forward(&a, cuda_stream_of(ctx))));
+        DirtSceneArgs s = {};
+        s.shape = a.shape;
+        s.background = bg.flat<float>().data();        s.background_bstride = stride(bg);
+        s.vertices = a.vertices;                       s.vertices_bstride = a.vertices_bstride;
+        s.faces = a.faces;                             s.faces_bstride = a.faces_bstride;
+        s.face_id = a.face_id; s.gbuffer = a.gbuffer; s.camera_pos = cam.flat<float>().data(); s.pixels = a.pixels;
+        OP_REQUIRES_OK(ctx, status_from(dirt_scene_shade(SCENE, &s, static_cast<int>(bg.dim_size(3)),
+                                                         static_cast<int>(cam.NumElements()), cuda_stream_of(ctx))));
+    }
+private:
+    int height_, width_, channels_;
+};
+
+#define DIRT_REGISTER_SCENE_OP(NAME, SCENE)                                                              \
+    REGISTER_OP(NAME)                                                                                    \
+        .Attr("height: int").Attr("width: int").Attr("channels: int = 3")                                \
+        .Input("background: float32").Input("vertices: float32").Input("vertex_colors: float32")         \
+        .Input("faces: int32").Input("camera_pos: float32")                                              \
+        .Output("pixels: float32")                                                                       \
+        .SetShapeFn([](shape_inference::InferenceContext *c) {                                           \
+            int h, w, ch;                                                                                \
+            TF_RETURN_IF_ERROR(c->GetAttr("height", &h));                                                \
+            TF_RETURN_IF_ERROR(c->GetAttr("width", &w));                                                 \
+            TF_RETURN_IF_ERROR(c->GetAttr("channels", &ch));                                             \
+            c->set_output(0, c->MakeShape({c->Dim(c->input(1), 0), h, w, ch}));                          \
+            return Status::OK();                                                                         \
+        });                                                                                              \
+    REGISTER_KERNEL_BUILDER(Name(NAME).Device(DEVICE_GPU), SceneOpB200<SCENE>)
+
+DIRT_REGISTER_SCENE_OP("Hill", DIRT_SCENE_HILL);                                   // csrc/hill.cpp:33, :503
+DIRT_REGISTER_SCENE_OP("OceanicNoCloud", DIRT_SCENE_OCEANIC_NO_CLOUD);             // csrc/oceanic_no_cloud.cpp:33, :519
+DIRT_REGISTER_SCENE_OP("OceanicSimpleProxy", DIRT_SCENE_OCEANIC_SIMPLE_PROXY);     // csrc/oceanic_simple_proxy.cpp:33, :519
+DIRT_REGISTER_SCENE_OP("OceanicStillCloud", DIRT_SCENE_OCEANIC_STILL_CLOUD);       // csrc/oceanic_still_cloud.cpp:33, :523
+DIRT_REGISTER_SCENE_OP("OceanicOptFlow", DIRT_SCENE_OCEANIC_OPT_FLOW);             // csrc/oceanic_opt_flow.cpp:33, :544
+// The fork's own "Rasterise" / "RasteriseGrad" pictures, for callers that want them back under new names:
+DIRT_REGISTER_SCENE_OP("OceanicHorizon", DIRT_SCENE_OCEANIC_HORIZON);              // csrc/rasterise_egl.cpp:385
+DIRT_REGISTER_SCENE_OP("Oceanic", DIRT_SCENE_OCEANIC);                             // csrc/rasterise_grad_egl.cpp:399
