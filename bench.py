@@ -204,6 +204,42 @@ def run_reference(args, wl, rank, world):
         "gpu_launches": 0}))
 
 
+_ORIG_AFFINITY = None
+
+
+def bind_to_gpu_numa(index):
+    """Pins this process to the CPUs of the NUMA node its GPU hangs off, before any pinned host
+    buffer is allocated (first touch puts the pages on that node), the way a production launcher
+    binds one rank per GPU.  Returns a short description for the JSON line, or why it was skipped."""
+    try:
+        import torch
+        import pynvml
+        pynvml.nvmlInit()
+        uuid = str(torch.cuda.get_device_properties(index).uuid)
+        h = pynvml.nvmlDeviceGetHandleByUUID(("GPU-" + uuid) if not uuid.startswith("GPU-") else uuid)
+        bus = pynvml.nvmlDeviceGetPciInfo(h).busId
+        bus = bus.decode() if isinstance(bus, bytes) else bus
+        bus = bus.lower()
+        if len(bus.split(":")[0]) == 8:            # nvml prints an 8-digit domain, sysfs a 4-digit one
+            bus = bus[4:]
+        base = "/sys/bus/pci/devices/" + bus
+        node = open(base + "/numa_node").read().strip()
+        cpulist = open(base + "/local_cpulist").read().strip()
+        cpus = set()
+        for part in cpulist.split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        global _ORIG_AFFINITY
+        _ORIG_AFFINITY = os.sched_getaffinity(0)
+        cpus &= _ORIG_AFFINITY
+        if not cpus:
+            return "skipped: no local CPUs in this process's affinity mask"
+        os.sched_setaffinity(0, cpus)
+        return "rank bound to NUMA node %s (%d CPUs) of GPU %s" % (node, len(cpus), bus)
+    except Exception as e:                          # no sysfs / nvml in this container: run unbound
+        return "skipped: %s" % (str(e)[:80] or type(e).__name__)
+
+
 def run_ours(args, wl, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -214,6 +250,7 @@ def run_ours(args, wl, rank, world, local_rank):
         raise SystemExit("bench.py needs a CUDA device (no CPU fallback); use --impl reference for the CPU arm")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa = bind_to_gpu_numa(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     lib = _lib.load()
@@ -401,6 +438,8 @@ def run_ours(args, wl, rank, world, local_rank):
 
     cpu_base = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        if _ORIG_AFFINITY:
+            os.sched_setaffinity(0, _ORIG_AFFINITY)      # the CPU baseline may use every host core again
         cpu_base = cpu_baseline_run(wl, 12.0)
     if world > 1:
         dist.barrier()
@@ -415,7 +454,8 @@ def run_ours(args, wl, rank, world, local_rank):
                    "vertices": V, "faces": F,
                    "sharding": ("frames across ranks; one packed all_reduce of [V,4+C] shared-mesh gradients per step" if shared
                                 else "batch elements across ranks, no data-path collective"),
-                   "l2": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2; no explicit flush" % ((fwd_bytes + bwd_bytes) / 1e6)},
+                   "l2": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2; no explicit flush" % ((fwd_bytes + bwd_bytes) / 1e6),
+                   "host": numa},
         "roofline": roofline, "stages_ms": stages, "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": int(launches),
         "clocks": clock_info}))
 

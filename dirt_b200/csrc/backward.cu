@@ -7,8 +7,11 @@
 // [B,V,C] and write grad_background [B,H,W,C].  The gradient definition is
 // docs/GRADIENT_SPEC.md ("filter-based derivatives", README.md:146-147).
 //
-// One CTA of 16x16 threads per 14x14-pixel output tile; the outer ring of threads is a halo.
-//   phase 0  the 18x18 neighbourhood (pixels, face id, window depth) is staged in shared memory
+// One CTA of 256 threads per 16x12-pixel output tile.  Warps 0..5 own the interior (six 8x4 pixel
+// blocks, every lane an output pixel); warps 6..7 own the 60 pixels of the one-pixel ring around it,
+// which only take part in phase 1 -- so the expensive phase 2 (shuffles, atomics) runs on six full
+// warps instead of eight partly idle ones.
+//   phase 0  the 20x16 neighbourhood (pixels, face id, window depth) is staged in shared memory
 //   phase 1  every thread: Sobel response of `pixels` weighted by grad_pixels, then the OWNER of
 //            the x- and of the row-direction change (itself or the occluding neighbour) and a
 //            plain store of the response into the owner's inbox slot -- a pixel has exactly
@@ -26,11 +29,14 @@
 namespace dirt {
 
 constexpr unsigned kFull = 0xFFFFFFFFu;
-constexpr int kBT = 16;                 // threads per CTA edge
-constexpr int kBI = kBT - 2;            // interior (output) pixels per CTA edge
-constexpr int kBR = kBT + 2;            // staged region edge
+constexpr int kThreads = 256;
+constexpr int kTX = 16, kTY = 12;       // interior (output) pixels per CTA
+constexpr int kRX = kTX + 2, kRY = kTY + 2;   // pixels that compute a response (interior + ring)
+constexpr int kSX = kTX + 4, kSY = kTY + 4;   // staged region
+constexpr int kInteriorWarps = (kTX / 8) * (kTY / 4);
 constexpr int kBP = 24;                 // row pitch of the shared arrays: a warp is an 8x4 pixel block, and
                                         // 4 rows at a pitch of 24 words land in 4 disjoint groups of 8 banks
+static_assert(kInteriorWarps * 32 + 2 * kRX + 2 * kTY <= kThreads && kSX <= kBP, "tile does not fit the CTA");
 constexpr int kMaxC = 16;
 
 __device__ __forceinline__ float finite_or_zero(float v) { return fabsf(v) <= FLT_MAX ? v : 0.0f; }
@@ -89,31 +95,45 @@ template <int C>
 #ifndef KBWD_CTAS
 #define KBWD_CTAS 5
 #endif
-__global__ void __launch_bounds__(kBT * kBT, KBWD_CTAS) k_grad_assemble(BwdParams p)
+__global__ void __launch_bounds__(kThreads, KBWD_CTAS) k_grad_assemble(BwdParams p)
 {
     constexpr int CS = C > 0 ? C : kMaxC;
     const int CC = C > 0 ? C : p.C;
-    __shared__ float s_px[CS][kBR * kBP];
-    __shared__ int s_fid[kBR * kBP];
-    __shared__ float s_zw[kBR * kBP];
-    __shared__ float s_in[2][3][kBT * kBP];
+    __shared__ float s_px[CS][kSY * kBP];
+    __shared__ int s_fid[kSY * kBP];
+    __shared__ float s_zw[kSY * kBP];
+    __shared__ float s_in[2][3][kRY * kBP];
 
     const int tid = threadIdx.x;
     // a warp is an 8x4 pixel block: better odds that its lanes share faces than a 32x1 strip
     const int warp = tid >> 5, lane = tid & 31;
-    const int lx = (warp & 1) * 8 + (lane & 7), ly = (warp >> 1) * 4 + (lane >> 3);
+    // (lx, ly) in the kRX x kRY region of responding pixels; interior = [1, kTX] x [1, kTY]
+    int lx, ly;
+    bool has = true;
+    if (warp < kInteriorWarps) {
+        lx = 1 + (warp % (kTX / 8)) * 8 + (lane & 7);
+        ly = 1 + (warp / (kTX / 8)) * 4 + (lane >> 3);
+    } else {
+        const int q = tid - kInteriorWarps * 32;      // ring: top row, bottom row, left column, right column
+        if (q < kRX) { lx = q; ly = 0; }
+        else if (q < 2 * kRX) { lx = q - kRX; ly = kRY - 1; }
+        else if (q < 2 * kRX + kTY) { lx = 0; ly = 1 + (q - 2 * kRX); }
+        else { lx = kRX - 1; ly = 1 + (q - 2 * kRX - kTY); }
+        has = q < 2 * kRX + 2 * kTY;
+        if (!has) { lx = 0; ly = 0; }
+    }
     const int W = p.W, H = p.H;
-    const int x = (int)blockIdx.x * kBI - 1 + lx, r = (int)blockIdx.y * kBI - 1 + ly;
+    const int x = (int)blockIdx.x * kTX - 1 + lx, r = (int)blockIdx.y * kTY - 1 + ly;
     const float halfW = 0.5f * (float)W, halfH = 0.5f * (float)H;
     const float4 *gbuf_all = reinterpret_cast<const float4 *>(p.gbuffer);
 
     for (int b = blockIdx.z; b < p.B; b += gridDim.z) {
         const size_t base = (size_t)b * H * W;
         const float *img = p.pixels + base * CC;
-        // ---- phase 0: stage the 18x18 neighbourhood (replicated at the image border) --------
-        for (int i = tid; i < kBR * kBR; i += kBT * kBT) {
-            const int ry = i / kBR, rx = i - ry * kBR;
-            const int gx = (int)blockIdx.x * kBI - 2 + rx, gy = (int)blockIdx.y * kBI - 2 + ry;
+        // ---- phase 0: stage the 20x16 neighbourhood (replicated at the image border) --------
+        for (int i = tid; i < kSX * kSY; i += kThreads) {
+            const int ry = i / kSX, rx = i - ry * kSX;
+            const int gx = (int)blockIdx.x * kTX - 2 + rx, gy = (int)blockIdx.y * kTY - 2 + ry;
             const bool in = gx >= 0 && gx < W && gy >= 0 && gy < H;
             const int cx = min(max(gx, 0), W - 1), cy = min(max(gy, 0), H - 1);
             const size_t o = (size_t)cy * W + cx;
@@ -128,8 +148,8 @@ __global__ void __launch_bounds__(kBT * kBT, KBWD_CTAS) k_grad_assemble(BwdParam
         __syncthreads();
 
         // ---- phase 1: Sobel response, owners, inbox -----------------------------------------
-        const bool valid = x >= 0 && x < W && r >= 0 && r < H;
-        const bool interior = valid && lx >= 1 && lx <= kBI && ly >= 1 && ly <= kBI;
+        const bool valid = has && x >= 0 && x < W && r >= 0 && r < H;
+        const bool interior = valid && warp < kInteriorWarps;
         const int ri = (ly + 1) * kBP + (lx + 1);               // own position in the staged region
         const size_t o = valid ? (size_t)r * W + x : 0;
         const int fself = s_fid[ri];
@@ -151,7 +171,7 @@ __global__ void __launch_bounds__(kBT * kBT, KBWD_CTAS) k_grad_assemble(BwdParam
                 for (int c = 0; c < CC; ++c) gbg[c] = fself < 0 ? g[c] : 0.0f;       // exact
             }
         }
-        {
+        if (has) {
             const float zs = s_zw[ri];
             const int ox = sx != 0.0f ? pick_owner(fself, zs, s_fid[ri - 1], s_zw[ri - 1], s_fid[ri + 1], s_zw[ri + 1]) : 0;
             const int oy = sr != 0.0f ? pick_owner(fself, zs, s_fid[ri - kBP], s_zw[ri - kBP], s_fid[ri + kBP], s_zw[ri + kBP]) : 0;
@@ -159,92 +179,94 @@ __global__ void __launch_bounds__(kBT * kBT, KBWD_CTAS) k_grad_assemble(BwdParam
             // candidate c = this pixel + d, d in {-1, 0, +1}; this pixel is sender slot 1 - d of c
             if (lx > 0) s_in[0][2][li - 1] = ox == 1 ? sx : 0.0f;
             s_in[0][1][li] = ox == 2 ? sx : 0.0f;
-            if (lx < kBT - 1) s_in[0][0][li + 1] = ox == 3 ? sx : 0.0f;
+            if (lx < kRX - 1) s_in[0][0][li + 1] = ox == 3 ? sx : 0.0f;
             if (ly > 0) s_in[1][2][li - kBP] = oy == 1 ? sr : 0.0f;
             s_in[1][1][li] = oy == 2 ? sr : 0.0f;
-            if (ly < kBT - 1) s_in[1][0][li + kBP] = oy == 3 ? sr : 0.0f;
+            if (ly < kRY - 1) s_in[1][0][li + kBP] = oy == 3 ? sr : 0.0f;
         }
         __syncthreads();
 
         // ---- phase 2: one scatter per covered interior pixel, summed per face across the warp --
-        const bool act = interior && fself >= 0;
-        float B0 = 0.f, B1 = 0.f, gxv = 0.f, gyv = 0.f, gwv = 0.f;
-        if (act) {
-            const int li = ly * kBP + lx;
-            const float4 gb = __ldg(gbuf_all + base + o);
-            B0 = gb.x; B1 = gb.y;
-            const float totx = (s_in[0][0][li] + s_in[0][1][li]) + s_in[0][2][li];
-            const float toty = (s_in[1][0][li] + s_in[1][1][li]) + s_in[1][2][li];
-            // GRADIENT_SPEC 4: a clip-space shift of the surface point by dx moves it by
-            // dx * W / (2 w) pixels; +y_clip moves it UP, towards smaller rows
-            const float xn = ((float)x + 0.5f) / halfW - 1.0f;
-            const float yn = ((float)(H - 1 - r) + 0.5f) / halfH - 1.0f;
-            const float ax = totx * halfW / gb.z, ay = toty * halfH / gb.z;
-            gxv = -ax; gyv = ay; gwv = ax * xn - ay * yn;
-        }
-        const unsigned peers = __match_any_sync(kFull, act ? fself : -1 - lane);
-        const float B2 = (1.0f - B0) - B1;
-        const int32_t *fp = p.faces + (int64_t)b * p.faces_bs + 3 * (int64_t)(act ? fself : 0);
-        float4 *gv = reinterpret_cast<float4 *>(p.grad_vertices + (int64_t)b * p.grad_vertices_bs);
-        float *gc = p.grad_vertex_colors + (int64_t)b * p.grad_vertex_colors_bs;
-        const bool packed = p.grad_packed != nullptr;
-        // shared mesh: clip = world @ M_b, so grad_world[j] = sum_i grad_clip[i] * M_b[j][i]; the
-        // z column never receives a gradient (GRADIENT_SPEC 4)
-        const float *M = p.matrices + 16 * (int64_t)b;
-        auto to_world = [&](float gx, float gy, float gw) {
-            return make_float4(gx * __ldg(M + 0) + gy * __ldg(M + 1) + gw * __ldg(M + 3),
-                               gx * __ldg(M + 4) + gy * __ldg(M + 5) + gw * __ldg(M + 7),
-                               gx * __ldg(M + 8) + gy * __ldg(M + 9) + gw * __ldg(M + 11),
-                               gx * __ldg(M + 12) + gy * __ldg(M + 13) + gw * __ldg(M + 15));
-        };
-        if (C == 1 || C == 3) {
-            constexpr int NQ = 3 + (C > 0 ? C : 1);
-            float v[3 * NQ];
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                const float bk = k == 0 ? B0 : (k == 1 ? B1 : B2);
-                v[k * NQ] = gxv * bk; v[k * NQ + 1] = gyv * bk; v[k * NQ + 2] = gwv * bk;
-#pragma unroll
-                for (int c = 0; c < NQ - 3; ++c) v[k * NQ + 3 + c] = act ? g[c] * bk : 0.0f;
+        if (warp < kInteriorWarps) {      // warp-uniform: the ring warps have nothing to scatter
+            const bool act = interior && fself >= 0;
+            float B0 = 0.f, B1 = 0.f, gxv = 0.f, gyv = 0.f, gwv = 0.f;
+            if (act) {
+                const int li = ly * kBP + lx;
+                const float4 gb = __ldg(gbuf_all + base + o);
+                B0 = gb.x; B1 = gb.y;
+                const float totx = (s_in[0][0][li] + s_in[0][1][li]) + s_in[0][2][li];
+                const float toty = (s_in[1][0][li] + s_in[1][1][li]) + s_in[1][2][li];
+                // GRADIENT_SPEC 4: a clip-space shift of the surface point by dx moves it by
+                // dx * W / (2 w) pixels; +y_clip moves it UP, towards smaller rows
+                const float xn = ((float)x + 0.5f) / halfW - 1.0f;
+                const float yn = ((float)(H - 1 - r) + 0.5f) / halfH - 1.0f;
+                const float ax = totx * halfW / gb.z, ay = toty * halfH / gb.z;
+                gxv = -ax; gyv = ay; gwv = ax * xn - ay * yn;
             }
-            const bool leader = peer_reduce(peers, v);
-            if (leader && act) {
-#pragma unroll
+            const unsigned peers = __match_any_sync(kFull, act ? fself : -1 - lane);
+            const float B2 = (1.0f - B0) - B1;
+            const int32_t *fp = p.faces + (int64_t)b * p.faces_bs + 3 * (int64_t)(act ? fself : 0);
+            float4 *gv = reinterpret_cast<float4 *>(p.grad_vertices + (int64_t)b * p.grad_vertices_bs);
+            float *gc = p.grad_vertex_colors + (int64_t)b * p.grad_vertex_colors_bs;
+            const bool packed = p.grad_packed != nullptr;
+            // shared mesh: clip = world @ M_b, so grad_world[j] = sum_i grad_clip[i] * M_b[j][i]; the
+            // z column never receives a gradient (GRADIENT_SPEC 4)
+            const float *M = p.matrices + 16 * (int64_t)b;
+            auto to_world = [&](float gx, float gy, float gw) {
+                return make_float4(gx * __ldg(M + 0) + gy * __ldg(M + 1) + gw * __ldg(M + 3),
+                                   gx * __ldg(M + 4) + gy * __ldg(M + 5) + gw * __ldg(M + 7),
+                                   gx * __ldg(M + 8) + gy * __ldg(M + 9) + gw * __ldg(M + 11),
+                                   gx * __ldg(M + 12) + gy * __ldg(M + 13) + gw * __ldg(M + 15));
+            };
+            if (C == 1 || C == 3) {
+                constexpr int NQ = 3 + (C > 0 ? C : 1);
+                float v[3 * NQ];
+    #pragma unroll
                 for (int k = 0; k < 3; ++k) {
-                    const int vi = __ldg(fp + k);
-                    const bool moved = v[k * NQ] != 0.0f || v[k * NQ + 1] != 0.0f || v[k * NQ + 2] != 0.0f;
-                    if (packed) {
-                        float *row = p.grad_packed + (int64_t)vi * p.packed_stride;
-                        if (moved) atomicAdd(reinterpret_cast<float4 *>(row), to_world(v[k * NQ], v[k * NQ + 1], v[k * NQ + 2]));
-                        if (C == 3) atomicAdd(reinterpret_cast<float4 *>(row + 4), make_float4(v[k * NQ + 3], v[k * NQ + 4], v[k * NQ + 5], 0.0f));
-                        else atomicAdd(row + 4, v[k * NQ + 3]);
-                    } else {
-                        if (moved) atomicAdd(gv + vi, make_float4(v[k * NQ], v[k * NQ + 1], 0.0f, v[k * NQ + 2]));
-                        if (C == 3) red_add3(gc + (int64_t)vi * 3, v[k * NQ + 3], v[k * NQ + 4], v[k * NQ + 5]);
-                        else atomicAdd(gc + vi, v[k * NQ + 3]);
+                    const float bk = k == 0 ? B0 : (k == 1 ? B1 : B2);
+                    v[k * NQ] = gxv * bk; v[k * NQ + 1] = gyv * bk; v[k * NQ + 2] = gwv * bk;
+    #pragma unroll
+                    for (int c = 0; c < NQ - 3; ++c) v[k * NQ + 3 + c] = act ? g[c] * bk : 0.0f;
+                }
+                const bool leader = peer_reduce(peers, v);
+                if (leader && act) {
+    #pragma unroll
+                    for (int k = 0; k < 3; ++k) {
+                        const int vi = __ldg(fp + k);
+                        const bool moved = v[k * NQ] != 0.0f || v[k * NQ + 1] != 0.0f || v[k * NQ + 2] != 0.0f;
+                        if (packed) {
+                            float *row = p.grad_packed + (int64_t)vi * p.packed_stride;
+                            if (moved) atomicAdd(reinterpret_cast<float4 *>(row), to_world(v[k * NQ], v[k * NQ + 1], v[k * NQ + 2]));
+                            if (C == 3) atomicAdd(reinterpret_cast<float4 *>(row + 4), make_float4(v[k * NQ + 3], v[k * NQ + 4], v[k * NQ + 5], 0.0f));
+                            else atomicAdd(row + 4, v[k * NQ + 3]);
+                        } else {
+                            if (moved) atomicAdd(gv + vi, make_float4(v[k * NQ], v[k * NQ + 1], 0.0f, v[k * NQ + 2]));
+                            if (C == 3) red_add3(gc + (int64_t)vi * 3, v[k * NQ + 3], v[k * NQ + 4], v[k * NQ + 5]);
+                            else atomicAdd(gc + vi, v[k * NQ + 3]);
+                        }
                     }
                 }
-            }
-        } else {
-            float v[9];
-#pragma unroll
-            for (int k = 0; k < 3; ++k) {
-                const float bk = k == 0 ? B0 : (k == 1 ? B1 : B2);
-                v[k * 3] = gxv * bk; v[k * 3 + 1] = gyv * bk; v[k * 3 + 2] = gwv * bk;
-            }
-            const bool leader = peer_reduce(peers, v);
-            if (act) {
+            } else {
+                float v[9];
+    #pragma unroll
                 for (int k = 0; k < 3; ++k) {
-                    const int vi = __ldg(fp + k);
                     const float bk = k == 0 ? B0 : (k == 1 ? B1 : B2);
-                    const bool moved = leader && (v[k * 3] != 0.0f || v[k * 3 + 1] != 0.0f || v[k * 3 + 2] != 0.0f);
-                    if (packed) {
-                        float *row = p.grad_packed + (int64_t)vi * p.packed_stride;
-                        if (moved) atomicAdd(reinterpret_cast<float4 *>(row), to_world(v[k * 3], v[k * 3 + 1], v[k * 3 + 2]));
-                        for (int c = 0; c < CC; ++c) atomicAdd(row + 4 + c, g[c] * bk);
-                    } else {
-                        if (moved) atomicAdd(gv + vi, make_float4(v[k * 3], v[k * 3 + 1], 0.0f, v[k * 3 + 2]));
-                        for (int c = 0; c < CC; ++c) atomicAdd(gc + (int64_t)vi * CC + c, g[c] * bk);
+                    v[k * 3] = gxv * bk; v[k * 3 + 1] = gyv * bk; v[k * 3 + 2] = gwv * bk;
+                }
+                const bool leader = peer_reduce(peers, v);
+                if (act) {
+                    for (int k = 0; k < 3; ++k) {
+                        const int vi = __ldg(fp + k);
+                        const float bk = k == 0 ? B0 : (k == 1 ? B1 : B2);
+                        const bool moved = leader && (v[k * 3] != 0.0f || v[k * 3 + 1] != 0.0f || v[k * 3 + 2] != 0.0f);
+                        if (packed) {
+                            float *row = p.grad_packed + (int64_t)vi * p.packed_stride;
+                            if (moved) atomicAdd(reinterpret_cast<float4 *>(row), to_world(v[k * 3], v[k * 3 + 1], v[k * 3 + 2]));
+                            for (int c = 0; c < CC; ++c) atomicAdd(row + 4 + c, g[c] * bk);
+                        } else {
+                            if (moved) atomicAdd(gv + vi, make_float4(v[k * 3], v[k * 3 + 1], 0.0f, v[k * 3 + 2]));
+                            for (int c = 0; c < CC; ++c) atomicAdd(gc + (int64_t)vi * CC + c, g[c] * bk);
+                        }
                     }
                 }
             }
@@ -267,18 +289,18 @@ cudaError_t launch_backward(const BwdParams &p, int sm_count, cudaStream_t strea
     tm.end(kStageGradClear, stream);
     if ((long long)p.B * p.H * p.W == 0) return cudaSuccess;
     // each CTA walks several batch elements: tiles are small, and a grid of ~32 CTAs per SM is
-    // enough to balance without paying a block launch per 196 pixels
-    const long long tiles = (long long)((p.W + kBI - 1) / kBI) * ((p.H + kBI - 1) / kBI);
+    // enough to balance without paying a block launch per 192 pixels
+    const long long tiles = (long long)((p.W + kTX - 1) / kTX) * ((p.H + kTY - 1) / kTY);
     long long gz = ((long long)sm_count * 32 + tiles - 1) / tiles;
     if (gz > p.B) gz = p.B;
     if (gz > 65535) gz = 65535;
     if (gz < 1) gz = 1;
-    const dim3 grid((p.W + kBI - 1) / kBI, (p.H + kBI - 1) / kBI, (unsigned)gz);
+    const dim3 grid((p.W + kTX - 1) / kTX, (p.H + kTY - 1) / kTY, (unsigned)gz);
     tm.begin(kStageGradAssemble, stream);
     switch (p.C) {
-        case 1: k_grad_assemble<1><<<grid, kBT * kBT, 0, stream>>>(p); break;
-        case 3: k_grad_assemble<3><<<grid, kBT * kBT, 0, stream>>>(p); break;
-        default: k_grad_assemble<0><<<grid, kBT * kBT, 0, stream>>>(p); break;
+        case 1: k_grad_assemble<1><<<grid, kThreads, 0, stream>>>(p); break;
+        case 3: k_grad_assemble<3><<<grid, kThreads, 0, stream>>>(p); break;
+        default: k_grad_assemble<0><<<grid, kThreads, 0, stream>>>(p); break;
     }
     tm.end(kStageGradAssemble, stream);
     *launches += 1;

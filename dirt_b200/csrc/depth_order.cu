@@ -30,15 +30,21 @@ constexpr int kSamples = 256;
 
 // Nearest corner depth of a face; 0 (first bucket, never culled) for faces on the general path.
 // `frags` (optional) receives an estimate of the fragments the face generates.
-__device__ __forceinline__ float face_near_depth(const FwdParams &p, int b, int f, float *frags = nullptr)
+__device__ __forceinline__ float face_near_depth(const FwdParams &p, int b, int f, float *frags = nullptr, int *facing = nullptr)
 {
     if (frags) *frags = 0.0f;
+    if (facing) *facing = 0;
     const int32_t *fp = p.faces + (int64_t)b * p.faces_bs + 3 * (int64_t)f;
     const int i0 = __ldg(fp), i1 = __ldg(fp + 1), i2 = __ldg(fp + 2);
     if ((unsigned)i0 >= (unsigned)p.V || (unsigned)i1 >= (unsigned)p.V || (unsigned)i2 >= (unsigned)p.V) return 0.0f;
     const int4 *pp = proj_ptr(p, b);
     const int4 a = __ldg(pp + i0), c = __ldg(pp + i1), d = __ldg(pp + i2);
     if (a.x == kProjSlow || c.x == kProjSlow || d.x == kProjSlow) return 0.0f;
+    if (facing) {
+        // winding in the window: sign of twice the area of the snapped corners
+        const long long a2 = (long long)(c.x - a.x) * (d.y - a.y) - (long long)(c.y - a.y) * (d.x - a.x);
+        *facing = a2 > 0 ? 1 : (a2 < 0 ? -1 : 0);
+    }
     if (frags) {
         TriSetup t;
         bool slow;
@@ -51,23 +57,9 @@ __device__ __forceinline__ float face_near_depth(const FwdParams &p, int b, int 
     return fminf(__int_as_float(a.z), fminf(__int_as_float(c.z), __int_as_float(d.z)));
 }
 
-__global__ void __launch_bounds__(kSamples) k_depth_pivots(FwdParams p, BucketPlan plan)
+// ascending bitonic sort of s_z[kSamples] by the kSamples threads of the CTA
+__device__ __forceinline__ void sort_samples(float *s_z, int t)
 {
-    __shared__ float s_z[kSamples];
-    __shared__ float s_frags;
-    const int b = blockIdx.x, t = threadIdx.x;
-    const int f = (int)(((long long)t * p.F) / kSamples);
-    if (t == 0) s_frags = 0.0f;
-    __syncthreads();
-    float frags;
-    s_z[t] = face_near_depth(p, b, f, &frags);
-    for (int o = 16; o >= 1; o >>= 1) frags += __shfl_xor_sync(kFull, frags, o);
-    if ((t & 31) == 0) atomicAdd(&s_frags, frags);
-    __syncthreads();
-    // fragments per pixel of this element, extrapolated from the sample; summed over the batch
-    if (t == 0)
-        atomicAdd(reinterpret_cast<float *>(p.counters + kCtrOverdraw), s_frags * ((float)p.F / kSamples) / ((float)p.H * (float)p.W));
-    // bitonic sort, ascending
     for (int k = 2; k <= kSamples; k <<= 1)
         for (int j = k >> 1; j > 0; j >>= 1) {
             const int q = t ^ j;
@@ -78,8 +70,49 @@ __global__ void __launch_bounds__(kSamples) k_depth_pivots(FwdParams p, BucketPl
             }
             __syncthreads();
         }
+}
+
+__global__ void __launch_bounds__(kSamples) k_depth_pivots(FwdParams p, BucketPlan plan)
+{
+    __shared__ float s_z[kSamples];
+    __shared__ float s_frags;
+    __shared__ int s_vote, s_front;
+    const int b = blockIdx.x, t = threadIdx.x;
+    const int f = (int)(((long long)t * p.F) / kSamples);
+    if (t == 0) { s_frags = 0.0f; s_vote = 0; s_front = 0; }
+    __syncthreads();
+    float frags;
+    int facing;
+    const float z = face_near_depth(p, b, f, &frags, &facing);
+    s_z[t] = z;
+    for (int o = 16; o >= 1; o >>= 1) frags += __shfl_xor_sync(kFull, frags, o);
+    if ((t & 31) == 0) atomicAdd(&s_frags, frags);
+    __syncthreads();
+    // fragments per pixel of this element, extrapolated from the sample; summed over the batch
+    if (t == 0)
+        atomicAdd(reinterpret_cast<float *>(p.counters + kCtrOverdraw), s_frags * ((float)p.F / kSamples) / ((float)p.H * (float)p.W));
+    sort_samples(s_z, t);
+    int nfront = kSamples;
+    if (plan.facing) {
+        // Which winding faces the viewer?  The one most of the NEARER half of the sample has: on a
+        // closed surface the far half hides behind the near half, and the near half's other winding
+        // is the inside of bumps.  Faces of the other winding go to the last bucket, behind the
+        // pyramid built from everything before it (a guess only orders the work; results are the same).
+        const float median = s_z[kSamples / 2];
+        __syncthreads();
+        if (z < median && facing) atomicAdd(&s_vote, facing);
+        __syncthreads();
+        const int front = s_vote >= 0 ? 1 : -1;
+        const bool is_front = facing == front || z == 0.0f;      // clipped / invalid faces stay in the first bucket
+        s_z[t] = is_front ? z : 3.0f;                            // window depths are <= 1
+        if (is_front) atomicAdd(&s_front, 1);
+        __syncthreads();
+        nfront = s_front;
+        sort_samples(s_z, t);
+        if (t == 0) p.pivots[b * kMaxBuckets + kMaxBuckets - 1] = (float)front;
+    }
     if (t < plan.n - 1) {
-        int at = (int)(plan.upto[t] * kSamples);
+        int at = (int)(plan.upto[t] * nfront);
         at = at < 0 ? 0 : (at > kSamples - 1 ? kSamples - 1 : at);
         p.pivots[b * kMaxBuckets + t] = s_z[at];
     }
@@ -96,7 +129,7 @@ constexpr int kChunkFaces = 2048;          // faces of ONE element per CTA in cl
 
 // blockIdx.y = element, blockIdx.x = chunk of kChunkFaces faces.  Counts go through shared
 // memory: kMaxBuckets global reductions per CTA instead of one per warp and bucket.
-__global__ void __launch_bounds__(256) k_depth_classify(FwdParams p, int nb, float min_overdraw)
+__global__ void __launch_bounds__(256) k_depth_classify(FwdParams p, int nb, float min_overdraw, int use_facing)
 {
     if (!plan_is_ordered(p, min_overdraw)) return;
     __shared__ uint32_t s_cnt[kMaxBuckets];
@@ -105,8 +138,11 @@ __global__ void __launch_bounds__(256) k_depth_classify(FwdParams p, int nb, flo
     if (t < kMaxBuckets) { s_cnt[t] = 0; s_pv[t] = t < nb - 1 ? p.pivots[b * kMaxBuckets + t] : 0.0f; }
     __syncthreads();
     const int f0 = blockIdx.x * kChunkFaces, f1 = min(f0 + kChunkFaces, p.F);
+    const int front = use_facing ? (int)p.pivots[b * kMaxBuckets + kMaxBuckets - 1] : 0;
     for (int f = f0 + t; f < f1; f += 256) {
-        const int k = bucket_for(s_pv, nb, face_near_depth(p, b, f));
+        int facing;
+        const float z = face_near_depth(p, b, f, nullptr, &facing);
+        const int k = (front == 0 || facing == front || z == 0.0f) ? bucket_for(s_pv, nb, z) : nb - 1;
         p.bucket_of[(size_t)b * p.F + f] = (uint8_t)k;
         atomicAdd(&s_cnt[k], 1u);
     }
@@ -235,9 +271,11 @@ BucketPlan bucket_plan()
         q.min_overdraw = 4.0f;
         if (const char *e = std::getenv("DIRT_B200_MIN_OVERDRAW")) q.min_overdraw = std::strtof(e, nullptr);
         q.n = 2; q.upto[0] = 0.35f; q.upto[1] = 1.0f;       // measured best on the 100k-face workloads (profiles/r1_setup_notes.md)
+        q.facing = false;
+        if (const char *e = std::getenv("DIRT_B200_FACING")) q.facing = e[0] == '1';
         if (const char *e = std::getenv("DIRT_B200_BUCKETS")) {
-            if (e[0] == '0' && e[1] == 0) { q.n = 0; return q; }
-            BucketPlan r; r.n = 0; r.min_overdraw = q.min_overdraw;
+            if (e[0] == '0' && e[1] == 0) { q.n = 0; q.facing = false; return q; }
+            BucketPlan r; r.n = 0; r.min_overdraw = q.min_overdraw; r.facing = q.facing;
             float last = 0.0f;
             while (*e && r.n < kMaxBuckets) {
                 char *end = nullptr;
@@ -259,7 +297,7 @@ void launch_depth_order(const FwdParams &p, const BucketPlan &plan, int sm_count
     (void)sm_count;
     const dim3 chunks((unsigned)((p.F + kChunkFaces - 1) / kChunkFaces), (unsigned)p.B);
     k_depth_pivots<<<p.B, kSamples, 0, stream>>>(p, plan);
-    k_depth_classify<<<chunks, 256, 0, stream>>>(p, plan.n, plan.min_overdraw);
+    k_depth_classify<<<chunks, 256, 0, stream>>>(p, plan.n, plan.min_overdraw, plan.facing ? 1 : 0);
     k_depth_offsets<<<1, 1024, 0, stream>>>(p, plan.n, plan.min_overdraw);
     k_depth_scatter<<<chunks, 256, 0, stream>>>(p, plan.n, plan.min_overdraw);
 }

@@ -88,6 +88,7 @@ cudaError_t launch_forward(const FwdParams &p, int sm_count, cudaStream_t stream
 struct BucketPlan {
     int n; float upto[kMaxBuckets];      // cumulative face fractions, upto[n-1] = 1
     float min_overdraw;                  // estimated fragments per pixel below which ordering does not pay
+    bool facing;                         // faces of the winding that looks away from the viewer go to the last bucket
 };
 BucketPlan bucket_plan();
 void launch_depth_order(const FwdParams &p, const BucketPlan &plan, int sm_count, cudaStream_t stream);
