@@ -270,22 +270,33 @@ BucketPlan bucket_plan()
         BucketPlan q;
         q.min_overdraw = 4.0f;
         if (const char *e = std::getenv("DIRT_B200_MIN_OVERDRAW")) q.min_overdraw = std::strtof(e, nullptr);
-        q.n = 2; q.upto[0] = 0.35f; q.upto[1] = 1.0f;       // measured best on the 100k-face workloads (profiles/r1_setup_notes.md)
+        // measured best on the 100k-face workloads (profiles/r1_setup_notes.md)
+        q.n = 2; q.upto[0] = 0.35f; q.upto[1] = 1.0f;
+        q.nlaunch = 2; q.launch_first[0] = 0; q.launch_first[1] = 1; q.launch_first[2] = 2;
         q.facing = false;
         if (const char *e = std::getenv("DIRT_B200_FACING")) q.facing = e[0] == '1';
         if (const char *e = std::getenv("DIRT_B200_BUCKETS")) {
-            if (e[0] == '0' && e[1] == 0) { q.n = 0; q.facing = false; return q; }
+            if (e[0] == '0' && e[1] == 0) { q.n = 0; q.nlaunch = 0; q.facing = false; return q; }
+            // "a,b;c,1": ';' ends a launch, ',' only a bucket inside it; without any ';' every bucket is a launch
+            bool grouped = false;
+            for (const char *c = e; *c; ++c) grouped = grouped || *c == ';';
             BucketPlan r; r.n = 0; r.min_overdraw = q.min_overdraw; r.facing = q.facing;
+            r.nlaunch = 0; r.launch_first[0] = 0;
             float last = 0.0f;
             while (*e && r.n < kMaxBuckets) {
                 char *end = nullptr;
                 const float v = std::strtof(e, &end);
                 if (end == e) break;
                 if (v > last && v <= 1.0f) { r.upto[r.n++] = v; last = v; }
-                e = (*end == ',') ? end + 1 : end;
-                if (*end != ',' ) break;
+                if ((*end == ';' || !grouped) && r.n > r.launch_first[r.nlaunch]) r.launch_first[++r.nlaunch] = r.n;
+                e = (*end == ',' || *end == ';') ? end + 1 : end;
+                if (*end != ',' && *end != ';') break;
             }
-            if (r.n > 0) { r.upto[r.n - 1] = 1.0f; q = r; }
+            if (r.n > 0) {
+                r.upto[r.n - 1] = 1.0f;
+                if (r.launch_first[r.nlaunch] != r.n) r.launch_first[++r.nlaunch] = r.n;
+                q = r;
+            }
         }
         return q;
     }();

@@ -87,6 +87,8 @@ cudaError_t launch_forward(const FwdParams &p, int sm_count, cudaStream_t stream
 // depth_order.cu
 struct BucketPlan {
     int n; float upto[kMaxBuckets];      // cumulative face fractions, upto[n-1] = 1
+    int nlaunch;                         // buckets are sampled in `nlaunch` launches (pyramid rebuilt between them);
+    int launch_first[kMaxBuckets + 1];   // launch j covers buckets launch_first[j] .. launch_first[j+1]-1, nearest first
     float min_overdraw;                  // estimated fragments per pixel below which ordering does not pay
     bool facing;                         // faces of the winding that looks away from the viewer go to the last bucket
 };

@@ -253,10 +253,11 @@ __device__ __forceinline__ bool hidden_by_hiz(const FwdParams &p, int b, const T
     return m < dmin;          // equal depth: the face index decides
 }
 
-// ORDERED: the faces of depth bucket `bucket` (depth_order.cu), tested against the hierarchical
-// depth buffer when `use_hiz`; otherwise all faces in index order.
+// ORDERED: the faces of depth buckets k0 .. k1 (depth_order.cu), nearest bucket first because work
+// is claimed in the order of `order`; tested against the hierarchical depth buffer when `use_hiz`
+// (every launch but the first).  Otherwise all faces in index order.
 template <bool ORDERED>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdParams p, int bucket, float min_overdraw)
+__global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdParams p, int k0, int k1, int launch_index, float min_overdraw)
 {
     __shared__ __align__(16) uint32_t s_recs[kWarpsPerCta][32 * kRecWords];
     __shared__ uint8_t s_owner[kWarpsPerCta][32];
@@ -266,20 +267,22 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
     // ORDERED launches check the verdict of k_depth_pivots: without enough overdraw the launch of
     // bucket 0 samples every face in index order and the other buckets' launches do nothing.
     const bool ordered = ORDERED && plan_is_ordered(p, min_overdraw);
-    if (ORDERED && !ordered && bucket > 0) return;
-    const bool use_hiz = ordered && bucket > 0;
-    const bool preload = !ordered || bucket > 0 || KPRE0 != 0;     // nearest bucket: nearly every fragment wins,
-                                                                    // reading the depth first only adds latency
+    if (ORDERED && !ordered && launch_index > 0) return;
+    const bool use_hiz = ordered && launch_index > 0;
     long long first_entry = 0, total = (long long)p.B * p.F;
+    // entries of the very nearest bucket: nearly every fragment wins there, reading the depth
+    // first only adds latency; later buckets (of this or a later launch) look before they reduce
+    long long no_preload_below = 0;
     if (ordered) {
-        first_entry = p.bucket_base[bucket];
-        total = (long long)p.bucket_base[bucket + 1] - first_entry;
+        first_entry = p.bucket_base[k0];
+        total = (long long)p.bucket_base[k1 + 1] - first_entry;
+        if (k0 == 0 && KPRE0 == 0) no_preload_below = (long long)p.bucket_base[1];
     }
     // Batches of 32 faces are claimed dynamically (their line counts differ by orders of
     // magnitude); the claim for the next batch is issued before the current one is sampled.
     // Smaller batches shorten the tail of a launch but repeat the latency-bound setup phase more
     // often: 16 and 8 faces per claim measured slower (profiles/r1_setup_notes.md).
-    unsigned long long *work = p.work_next + bucket;
+    unsigned long long *work = p.work_next + launch_index;
     // a handful of faces cannot fill the machine line by line (one warp would walk every span in
     // turn): then anything but tiny triangles goes to the pixel-parallel tile path
     const bool many_faces = (long long)p.B * p.F >= kFewFaces;
@@ -289,6 +292,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
         const long long i0 = (long long)__shfl_sync(kFullMask, claim, 0);
         if (i0 >= total) break;
         const long long i = i0 + lane;
+        const bool preload = i0 >= no_preload_below;
         if (lane == 0) claim = atomicAdd(work, 32ull);
         // ---- setup: one face per lane -------------------------------------------------------
         int nlines = 0;                  // > 0: this lane's face is line-sampled by the warp
@@ -386,27 +390,28 @@ void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_
         tm.begin(kStageDepthOrder, stream);
         launch_depth_order(p, plan, sm_count, stream);
         tm.end(kStageDepthOrder, stream);
-        for (int k = 0; k < plan.n; ++k) {
-            if (k > 0) {
+        for (int j = 0; j < plan.nlaunch; ++j) {
+            if (j > 0) {
                 tm.begin(kStageHizBuild, stream);
                 launch_hiz_build(p, plan, sm_count, stream);
                 tm.end(kStageHizBuild, stream);
             }
             tm.begin(kStageSetup, stream);
-            k_setup<true><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, k, plan.min_overdraw);
+            k_setup<true><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, plan.launch_first[j], plan.launch_first[j + 1] - 1, j, plan.min_overdraw);
             tm.end(kStageSetup, stream);
 #ifdef DIRT_STATS
             uint32_t c[8], bb[kMaxBuckets + 1];
             cudaStreamSynchronize(stream);
             cudaMemcpy(c, p.counters, sizeof(c), cudaMemcpyDeviceToHost);
             cudaMemcpy(bb, p.bucket_base, sizeof(bb), cudaMemcpyDeviceToHost);
-            printf("bucket %d: faces %u | cumulative: culled tris %u (lines %u), sampled tris %u (lines %u)\n", k, bb[k + 1] - bb[k], c[4], c[5], c[6], c[7]);
+            printf("launch %d: faces %u | cumulative: culled tris %u (lines %u), sampled tris %u (lines %u)\n", j,
+                   bb[plan.launch_first[j + 1]] - bb[plan.launch_first[j]], c[4], c[5], c[6], c[7]);
 #endif
         }
-        *launches += 4 + 2 * plan.n - 1;
+        *launches += 4 + 2 * plan.nlaunch - 1;
     } else {
         tm.begin(kStageSetup, stream);
-        k_setup<false><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, 0, 0.0f);
+        k_setup<false><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, 0, 0, 0, 0.0f);
         tm.end(kStageSetup, stream);
         *launches += 1;
     }
