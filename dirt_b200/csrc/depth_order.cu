@@ -13,7 +13,9 @@
 //
 //   k_depth_pivots    256 evenly spaced sample faces per element, sorted by nearest corner depth
 //                     -> the bucket boundaries of the element (sample quantiles)
-//   k_depth_classify  bucket of every face; faces per (bucket, element)
+//   k_depth_split2    two buckets (the default): classify + count + scatter in one pass, bucket 0 filled
+//                     from the front of `order`, bucket 1 from its back
+//   k_depth_classify  (three buckets and more) bucket of every face; faces per (bucket, element)
 //   k_depth_offsets   exclusive scan, bucket-major: bucket k of all elements is one contiguous
 //                     range of `order`, so one launch samples bucket k of the whole batch
 //   k_depth_scatter   flat face numbers into their ranges (order inside a range is arbitrary)
@@ -207,6 +209,62 @@ __global__ void __launch_bounds__(256) k_depth_scatter(FwdParams p, int nb, floa
     }
 }
 
+// Two buckets (the default plan): classify, count and scatter in ONE pass.  Bucket 0 grows up from
+// the start of `order`, bucket 1 down from its end -- every face lands in exactly one of them, so
+// the two ranges meet and [0, n0) / [n0, B*F) are the bucket-major ranges the setup launches expect.
+// A CTA reserves its two ranges with one atomic each (ranks inside the CTA from shared counters);
+// the last CTA to finish publishes the boundaries.  bucket_count[0..2] serve as the two cursors and
+// the ticket (zeroed with the other counters before every forward pass).
+__global__ void __launch_bounds__(256) k_depth_split2(FwdParams p, float min_overdraw, int use_facing)
+{
+    if (!plan_is_ordered(p, min_overdraw)) return;
+    __shared__ uint32_t s_cnt[2], s_base[2];
+    const int b = blockIdx.y, t = threadIdx.x;
+    if (t < 2) s_cnt[t] = 0;
+    __syncthreads();
+    const float pivot = p.pivots[b * kMaxBuckets];
+    const int front = use_facing ? (int)p.pivots[b * kMaxBuckets + kMaxBuckets - 1] : 0;
+    const int f0 = blockIdx.x * kChunkFaces, f1 = min(f0 + kChunkFaces, p.F);
+    uint32_t rank[kChunkFaces / 256];
+    uint32_t kbits = 0;
+#pragma unroll
+    for (int j = 0; j < kChunkFaces / 256; ++j) {
+        const int f = f0 + t + j * 256;
+        if (f < f1) {
+            int facing = 0;
+            const float z = face_near_depth(p, b, f, nullptr, use_facing ? &facing : nullptr);
+            const int k = (front == 0 || facing == front || z == 0.0f) ? (z >= pivot ? 1 : 0) : 1;
+            kbits |= (uint32_t)k << j;
+            rank[j] = atomicAdd(&s_cnt[k], 1u);
+        }
+    }
+    __syncthreads();
+    if (t < 2 && s_cnt[t]) s_base[t] = atomicAdd(p.bucket_count + t, s_cnt[t]);
+    __syncthreads();
+    const uint32_t total = (uint32_t)((size_t)p.B * p.F);
+#pragma unroll
+    for (int j = 0; j < kChunkFaces / 256; ++j) {
+        const int f = f0 + t + j * 256;
+        if (f < f1) {
+            const int k = (kbits >> j) & 1;
+            const uint32_t at = s_base[k] + rank[j];
+            p.order[k == 0 ? at : total - 1u - at] = (uint32_t)((size_t)b * p.F + f);
+        }
+    }
+    // publish the boundaries once every CTA has reserved its ranges
+    __syncthreads();
+    if (t == 0) {
+        __threadfence();
+        const uint32_t done = atomicAdd(p.bucket_count + 2, 1u);
+        if (done == gridDim.x * gridDim.y - 1) {
+            __threadfence();
+            p.bucket_base[0] = 0u;
+            p.bucket_base[1] = atomicAdd(p.bucket_count + 0, 0u);
+            p.bucket_base[2] = total;
+        }
+    }
+}
+
 // Depth pyramid of one 64 x 64 pixel block per CTA: warp w reduces pixel rows 8w .. 8w+7 to
 // eight 8x8 tiles, then levels 1..3 are reduced from shared memory.
 __global__ void __launch_bounds__(256) k_hiz_build(FwdParams p, float min_overdraw)
@@ -308,6 +366,10 @@ void launch_depth_order(const FwdParams &p, const BucketPlan &plan, int sm_count
     (void)sm_count;
     const dim3 chunks((unsigned)((p.F + kChunkFaces - 1) / kChunkFaces), (unsigned)p.B);
     k_depth_pivots<<<p.B, kSamples, 0, stream>>>(p, plan);
+    if (plan.n == 2) {
+        k_depth_split2<<<chunks, 256, 0, stream>>>(p, plan.min_overdraw, plan.facing ? 1 : 0);
+        return;
+    }
     k_depth_classify<<<chunks, 256, 0, stream>>>(p, plan.n, plan.min_overdraw, plan.facing ? 1 : 0);
     k_depth_offsets<<<1, 1024, 0, stream>>>(p, plan.n, plan.min_overdraw);
     k_depth_scatter<<<chunks, 256, 0, stream>>>(p, plan.n, plan.min_overdraw);

@@ -408,7 +408,7 @@ void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_
                    bb[plan.launch_first[j + 1]] - bb[plan.launch_first[j]], c[4], c[5], c[6], c[7]);
 #endif
         }
-        *launches += 4 + 2 * plan.nlaunch - 1;
+        *launches += (plan.n == 2 ? 2 : 4) + 2 * plan.nlaunch - 1;     // ordering kernels + setup launches + pyramid builds
     } else {
         tm.begin(kStageSetup, stream);
         k_setup<false><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, 0, 0, 0, 0.0f);

@@ -297,21 +297,25 @@ print("plan ok")
 """
 
 
-@pytest.mark.parametrize("plan,min_overdraw", [("0", "0"), ("1", "0"), ("0.5,1", "0"), ("0.05,0.1,0.2,0.3,0.4,0.6,0.8,1", "0"),
-                                               ("0.35,1", "1.5"), ("0.35,1", "1e9")])
-def test_depth_bucket_plans_do_not_change_the_result(plan, min_overdraw):
+@pytest.mark.parametrize("plan,min_overdraw,facing", [("0", "0", "0"), ("1", "0", "0"), ("0.5,1", "0", "0"),
+                                                      ("0.05,0.1,0.2,0.3,0.4,0.6,0.8,1", "0", "0"),
+                                                      ("0.35,1", "1.5", "0"), ("0.35,1", "1e9", "0"),
+                                                      ("0.1,0.2,0.35;0.5,0.7,1", "0", "0"), ("0.2,0.4;1", "0", "1"), ("0.5,1", "0", "1")])
+def test_depth_bucket_plans_do_not_change_the_result(plan, min_overdraw, facing):
     """Meshes of >= 4096 faces are sampled front to back in depth buckets, with triangles hidden
     behind the depth pyramid dropped (dirt_b200/csrc/depth_order.cu).  The cull is conservative by
     construction, so every plan -- unordered ("0"), one ordered pass, two and eight buckets --
     must reproduce the oracle bit for bit (face ids, window depth), depth ties included.
     DIRT_B200_MIN_OVERDRAW = 0 forces the ordered kernels whatever overdraw the scene is
     estimated to have; 1.5 lets the estimate choose per scene, 1e9 always falls back to the
-    in-kernel unordered pass.  The plan is read once per process, hence the subprocess."""
+    in-kernel unordered pass.  "a,b;c,1" puts several buckets into one launch (';' ends a launch);
+    DIRT_B200_FACING=1 sends the faces of the winding that looks away to the last bucket.
+    The plan is read once per process, hence the subprocess."""
     import os
     import subprocess
     import sys
     tests = os.path.dirname(os.path.abspath(__file__))
-    env = dict(os.environ, DIRT_B200_BUCKETS=plan, DIRT_B200_MIN_OVERDRAW=min_overdraw)
+    env = dict(os.environ, DIRT_B200_BUCKETS=plan, DIRT_B200_MIN_OVERDRAW=min_overdraw, DIRT_B200_FACING=facing)
     r = subprocess.run([sys.executable, "-c", _PLAN_CHECK.format(root=os.path.dirname(tests), tests=tests)],
                        env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0 and "plan ok" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
