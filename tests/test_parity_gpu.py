@@ -225,6 +225,40 @@ def test_determinism_run_to_run():
         assert torch.equal(x, y)
 
 
+def test_forward_and_backward_replay_from_a_cuda_graph():
+    """Every C-ABI call is asynchronous on the caller's stream and never synchronises with the
+    host (the reference blocks on a GL thread and a cudaMemcpy, csrc/gl_dispatcher.h:58-67,
+    csrc/rasterise_egl.cpp:323), so a whole fwd+bwd step can be captured in a CUDA graph and
+    replayed on new inputs -- the way to run launch-bound small frames (configs c1, c2)."""
+    from dirt_b200 import rasterise_ops as ops
+    for sc in (scenes.cube(B=1, H=96, W=96), scenes.sphere(2, 128, 128, n_lat=64, n_lon=64)):
+        t = _cuda(sc)
+        V = sc["vertices"].shape[1]
+        g = torch.randn(sc["background"].shape, device="cuda")
+        static_v = t["vertices"].clone()
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):                         # warm-up grows the workspace outside the capture
+            px, fid, gb = ops.forward_raw(t["background"], static_v, t["vertex_colors"], t["faces"])
+            ops.backward_raw(t["faces"], px, g, fid, gb, V)
+        torch.cuda.current_stream().wait_stream(side)
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            px, fid, gb = ops.forward_raw(t["background"], static_v, t["vertex_colors"], t["faces"])
+            gv, gc, gbg = ops.backward_raw(t["faces"], px, g, fid, gb, V)
+        for k in range(3):
+            moved = t["vertices"].clone()
+            moved[..., 0] += 0.05 * k * moved[..., 3]         # shift the mesh in clip space
+            static_v.copy_(moved)
+            graph.replay()
+            torch.cuda.synchronize()
+            epx, efid, egb = ops.forward_raw(t["background"], moved, t["vertex_colors"], t["faces"])
+            egv, egc, egbg = ops.backward_raw(t["faces"], epx, g, efid, egb, V)
+            assert torch.equal(fid, efid) and torch.equal(px, epx) and torch.equal(gbg, egbg)
+            for a, b in ((gv, egv), (gc, egc)):
+                assert float((a - b).abs().max()) <= GRAD_RTOL * max(float(b.abs().max()), 1e-12)
+
+
 def test_public_api_autograd_matches_raw_calls():
     import dirt_b200
     sc = scenes.cube(B=2, H=64, W=64)

@@ -62,8 +62,24 @@ def main():
             step(); torch.cuda.synchronize(); lib.dirt_profile_collect()
         lib.dirt_profile_enable(0)
         st = {k: m / 5 for k, (m, c) in _lib.stage_times().items()}      # per step
-        print("%-9s B=%d %dx%d F=%d  step %.3f ms  %.0f Mpix/s | %s" % (
+        graph_ms = None
+        if os.environ.get("STAGES_GRAPH", "1") != "0" and ms < 0.5:
+            # launch-bound sizes: the same step captured once in a CUDA graph and replayed
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                step()
+            for _ in range(3):
+                graph.replay()
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(50):
+                graph.replay()
+            e1.record()
+            torch.cuda.synchronize()
+            graph_ms = e0.elapsed_time(e1) / 50
+        print("%-9s B=%d %dx%d F=%d  step %.3f ms  %.0f Mpix/s%s | %s" % (
             name, B, H, W, sc["faces"].shape[1], ms, B * H * W / ms / 1e3,
+            "  (CUDA graph replay %.3f ms)" % graph_ms if graph_ms else "",
             " ".join("%s=%.3f" % (k, v) for k, v in st.items())), flush=True)
 
 
