@@ -177,6 +177,18 @@ def ncu_traffic(kernel, workload):
         return None
 
 
+def ncu_pipes(kernel, workload):
+    """Issue-slot, LSU-data-pipe and DRAM utilisation of `kernel`'s launches in the same committed
+    capture: the secondary ceilings SURVEY.md 8(d) asks to be reported beside the HBM roofline."""
+    if workload != "headline":
+        return None
+    try:
+        with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
+            return json.load(f).get("_pipes", {}).get(kernel)
+    except Exception:
+        return None
+
+
 def run_reference(args, wl, rank, world):
     """--impl reference: the CPU implementation of the path on the host cores.  The reference has
     no CPU code for this path and cannot be compiled here (needs TensorFlow + EGL/OpenGL), so this
@@ -348,7 +360,10 @@ def run_ours(args, wl, rank, world, local_rank):
                 "kernel_ms": stages[dominant] / nl,
                 "step_algorithmic_bytes": fwd_bytes + bwd_bytes,
                 "step_achieved_GBps": (fwd_bytes + bwd_bytes) / (ms_step * 1e-3) / 1e9,
-                "step_frac": (fwd_bytes + bwd_bytes) / (ms_step * 1e-3) / 1e9 / peak}
+                "step_frac": (fwd_bytes + bwd_bytes) / (ms_step * 1e-3) / 1e9 / peak,
+                "binding_pipes_ncu": ncu_pipes("k_" + dominant, args.workload),
+                "note": "k_setup is bound by instruction issue, k_grad_assemble / k_resolve by the LSU data pipe "
+                        "(profiles/r1_bench_ncu.md); HBM is the stated roofline, not what limits them"}
 
     # ---- e2e: public API, pinned host inputs, H2D + D2H inside the timed region -------------
     # Every step uploads ITS inputs (background, vertices, colours, faces) from pinned host memory

@@ -71,6 +71,19 @@ def main():
                         wr = float(r[i].replace(",", "")) * UNIT_BYTES.get(units[i], 1)
             key = "k_" + name.split("<")[0].replace("k_", "")
             traffic[key] = traffic.get(key, 0.0) + rd + wr          # capture one step: launches of a kernel add up
+            # what actually binds the kernel: issue slots, the LSU data pipe, DRAM (per launch, in capture order)
+            pipes = traffic.setdefault("_pipes", {}).setdefault(key, [])
+            entry = {}
+            for label, m in (("issue_active_pct", "smsp__issue_active.avg.pct_of_peak_sustained_active"),
+                             ("lsu_data_pipe_pct", "l1tex__data_pipe_lsu_wavefronts.avg.pct_of_peak_sustained_elapsed"),
+                             ("dram_pct", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed"),
+                             ("duration_us", "gpu__time_duration.sum")):
+                if m in hdr:
+                    try:
+                        entry[label] = round(float(r[hdr.index(m)].replace(",", "")), 1)
+                    except ValueError:
+                        pass
+            pipes.append(entry)
             lines.append("")
     open(a.out, "w").write("\n".join(lines) + "\n")
     if a.traffic:
