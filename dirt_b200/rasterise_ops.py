@@ -24,8 +24,15 @@ from ._lib import DirtBackwardArgs, DirtForwardArgs, DirtShape, InvalidArgumentE
 _workspaces = {}
 
 
-def _as_tensor(x, dtype, device, name):
+def _is_host_mapped(t):
+    """A pinned host tensor: under unified addressing the kernels can read it in place over PCIe."""
+    return isinstance(t, torch.Tensor) and not t.is_cuda and t.dtype == torch.float32 and t.is_pinned()
+
+
+def _as_tensor(x, dtype, device, name, keep_pinned=False):
     # tf.convert_to_tensor(x, dtype=...) of dirt/rasterise_ops.py:40-43
+    if keep_pinned and _is_host_mapped(x) and dtype == torch.float32:
+        return x
     if isinstance(x, torch.Tensor):
         t = x
         if t.device != device:
@@ -91,9 +98,12 @@ def _validate(background, vertices, vertex_colors, faces, height, width, channel
 
 def forward_raw(background, vertices, vertex_colors, faces, want_aux=True):
     """One C-ABI forward call on batched, contiguous CUDA tensors.
-    Returns (pixels [B,H,W,C], face_id [B,H,W] | None, gbuffer [B,H,W,4] | None)."""
+    Returns (pixels [B,H,W,C], face_id [B,H,W] | None, gbuffer [B,H,W,4] | None).
+    `background` may also be a PINNED HOST tensor: the resolve kernel reads the background only
+    where no face covers the pixel, so reading it in place over PCIe moves just those bytes
+    instead of the whole image (the reference uploads all of it, csrc/rasterise_egl.cu:16-50)."""
     lib = _lib.load()
-    device = background.device
+    device = vertices.device              # `background` may be pinned host memory, read in place
     B = max(background.shape[0], vertices.shape[0], vertex_colors.shape[0], faces.shape[0])
     _, H, W, C = background.shape
     V, F = vertices.shape[1], faces.shape[1]
@@ -178,6 +188,7 @@ class _Rasterise(torch.autograd.Function):
     @staticmethod
     def forward(ctx, background, vertices, vertex_colors, faces):
         need_grad = any(ctx.needs_input_grad[:3])
+        ctx.bg_on_host = not background.is_cuda
         pixels, face_id, gbuffer = forward_raw(background, vertices, vertex_colors, faces, want_aux=need_grad)
         if need_grad:
             ctx.save_for_backward(faces, pixels, face_id, gbuffer)
@@ -195,6 +206,8 @@ class _Rasterise(torch.autograd.Function):
                                    want_grad_background=ctx.needs_input_grad[0])
         if gbg is not None and bg_b == 1 and B > 1:
             gbg = gbg.sum(dim=0, keepdim=True)
+        if gbg is not None and ctx.bg_on_host:
+            gbg = gbg.cpu()                   # autograd wants the gradient where the leaf lives
         return (gbg if ctx.needs_input_grad[0] else None,
                 gv if ctx.needs_input_grad[1] else None,
                 gc if ctx.needs_input_grad[2] else None,
@@ -203,7 +216,7 @@ class _Rasterise(torch.autograd.Function):
 
 def _prepare(background, vertices, vertex_colors, faces, batched, height, width, channels):
     device = _device_of(background, vertices, vertex_colors, faces)
-    background = _as_tensor(background, torch.float32, device, "background")
+    background = _as_tensor(background, torch.float32, device, "background", keep_pinned=True)
     vertices = _as_tensor(vertices, torch.float32, device, "vertices")
     vertex_colors = _as_tensor(vertex_colors, torch.float32, device, "vertex_colors")
     faces = _as_tensor(faces, torch.int32, device, "faces")
@@ -254,6 +267,7 @@ class _RasteriseShared(torch.autograd.Function):
                                       "vertices yourself and call rasterise_batch for that")
         vertices = torch.matmul(world_vertices.unsqueeze(0), clip_from_world).contiguous()      # [B,V,4]
         need_grad = any(ctx.needs_input_grad)
+        ctx.bg_on_host = not background.is_cuda
         pixels, face_id, gbuffer = forward_raw(background, vertices, vertex_colors.unsqueeze(0), faces.unsqueeze(0),
                                                want_aux=need_grad)
         if need_grad:
@@ -270,6 +284,8 @@ class _RasteriseShared(torch.autograd.Function):
                                           gbuffer, V, clip_from_world, want_grad_background=ctx.needs_input_grad[0])
         if gbg is not None and bg_b == 1 and pixels.shape[0] > 1:
             gbg = gbg.sum(dim=0, keepdim=True)
+        if gbg is not None and ctx.bg_on_host:
+            gbg = gbg.cpu()
         return gbg, packed[:, :4], None, packed[:, 4:4 + C], None
 
 
@@ -282,7 +298,7 @@ def rasterise_batch_shared(background, world_vertices, clip_from_world, vertex_c
     per-frame [B,V,4] / [B,V,C] gradients.  Across GPUs, all-reduce `.grad` of the two leaves (or use
     `rasterise_ops.backward_shared_raw` + `sharding.allreduce_packed` for a single collective)."""
     dev = _device_of(background, world_vertices, clip_from_world, vertex_colors, faces)
-    bg = _as_tensor(background, torch.float32, dev, "background").contiguous()
+    bg = _as_tensor(background, torch.float32, dev, "background", keep_pinned=True).contiguous()
     wv = _as_tensor(world_vertices, torch.float32, dev, "world_vertices").contiguous()
     m = _as_tensor(clip_from_world, torch.float32, dev, "clip_from_world").contiguous()
     col = _as_tensor(vertex_colors, torch.float32, dev, "vertex_colors").contiguous()

@@ -62,7 +62,11 @@ typedef struct DirtShape {
 /* Forward arguments.  Replaces the inputs/outputs of RasteriseOpGpu::Compute
  * (csrc/rasterise_egl.cpp:284-514).  `camera_pos` (input 4 of the fork's op, :41) only
  * parameterises the fork's procedural fragment shaders (:399-433) and is not an input of the
- * mesh path; adapters accept and drop it. */
+ * mesh path; adapters accept and drop it.
+ * `background` is read only at pixels no face covers, so it may also point to PINNED HOST memory
+ * mapped into the device address space (cudaHostAlloc / cudaHostRegister under unified
+ * addressing): the kernel then fetches just those pixels over PCIe, where the reference uploads
+ * the whole image first (upload_background, csrc/rasterise_egl.cu:16-50). */
 typedef struct DirtForwardArgs {
     DirtShape shape;
     const float *background;      int64_t background_bstride;    /* [B,H,W,C]              */

@@ -259,6 +259,30 @@ def test_forward_and_backward_replay_from_a_cuda_graph():
                 assert float((a - b).abs().max()) <= GRAD_RTOL * max(float(b.abs().max()), 1e-12)
 
 
+def test_background_read_in_place_from_pinned_host_memory():
+    """The resolve kernel touches the background only where no face covers the pixel, so the
+    caller may leave it in pinned host memory: same pixels bit for bit, the gradient w.r.t. the
+    background comes back on the host."""
+    import dirt_b200
+    from dirt_b200 import rasterise_ops as ops
+    sc = scenes.sphere(3, 96, 128, n_lat=32, n_lon=32)
+    t = _cuda(sc)
+    bg_host = torch.from_numpy(sc["background"]).pin_memory()
+    ref, fid, _ = ops.forward_raw(t["background"], t["vertices"], t["vertex_colors"], t["faces"])
+    px, fid2, _ = ops.forward_raw(bg_host, t["vertices"], t["vertex_colors"], t["faces"])
+    assert torch.equal(fid, fid2) and torch.equal(px, ref)
+    assert 0.05 < float((fid < 0).float().mean()) < 0.95          # both kinds of pixel are exercised
+    bg_leaf = bg_host.clone().pin_memory().requires_grad_(True)
+    v = t["vertices"].clone().requires_grad_(True)
+    out = dirt_b200.rasterise_batch(bg_leaf, v, t["vertex_colors"], t["faces"])
+    assert out.is_cuda and torch.equal(out.detach(), ref)
+    (out * 2.0).sum().backward()
+    assert not bg_leaf.grad.is_cuda and v.grad.is_cuda
+    assert torch.equal(bg_leaf.grad, (2.0 * (fid < 0)[..., None].float().expand_as(ref)).cpu())
+    one = dirt_b200.rasterise(bg_host[0], sc["vertices"][0], sc["vertex_colors"][0], sc["faces"][0])
+    assert torch.equal(one, ref[0])
+
+
 def test_public_api_autograd_matches_raw_calls():
     import dirt_b200
     sc = scenes.cube(B=2, H=64, W=64)
