@@ -176,3 +176,46 @@ def test_backward_finite_difference_translation():
     an = (gv[0, :, 0] * sc["vertices"][0, :, 3]).sum()
     assert np.sign(fd) == np.sign(an)
     assert abs(an - fd) <= 0.35 * abs(fd), (an, fd)
+
+
+def test_attributes_match_the_closed_form_of_perspective_correct_interpolation():
+    """Pins the VALUES (not just coverage) to the OpenGL definition the reference's `smooth`
+    varyings follow (csrc/shaders.cpp:16-31): with screen-space barycentrics l_i of the pixel
+    centre, attribute = sum(l_i a_i / w_i) / sum(l_i / w_i), clip w = 1 / sum(l_i / w_i), window
+    depth = (sum(l_i z_i / w_i) + 1) / 2 -- evaluated here in float64 from the raw clip coordinates,
+    independently of the oracle's arithmetic."""
+    H, W, C = 40, 56, 3
+    v = np.array([[[-0.9, -0.8, 0.2, 1.0], [0.7, -0.5, 0.9, 2.5], [0.1, 2.4, -0.6, 3.0]]], np.float32)   # different w per corner
+    col = np.array([[[1.0, 0.0, 0.25], [0.0, 1.0, 0.5], [0.3, 0.2, 1.0]]], np.float32)
+    f = np.array([[[0, 1, 2]]], np.int32)
+    bg = np.full((1, H, W, C), -7.0, np.float32)
+    px, fid, gb = golden.forward(bg, v, col, f)
+    cov = fid[0] >= 0
+    assert 200 < cov.sum() < H * W - 200
+    vd = v[0].astype(np.float64)
+    ndc = vd[:, :3] / vd[:, 3:4]
+    sx = (ndc[:, 0] + 1) * W / 2
+    sy = (ndc[:, 1] + 1) * H / 2
+    ys, xs = np.nonzero(cov)
+    cx, cy = xs + 0.5, (H - 1 - ys) + 0.5                               # window coordinates, y up
+    def edge(ax, ay, bx, by, qx, qy):
+        return (bx - ax) * (qy - ay) - (by - ay) * (qx - ax)
+    area = edge(sx[0], sy[0], sx[1], sy[1], sx[2], sy[2])
+    l0 = edge(sx[1], sy[1], sx[2], sy[2], cx, cy) / area
+    l1 = edge(sx[2], sy[2], sx[0], sy[0], cx, cy) / area
+    l2 = 1 - l0 - l1
+    # points within a hair of an edge may fall on the other side after snapping to 1/256 px
+    inside = (np.minimum(np.minimum(l0, l1), l2) > 2e-3)
+    assert inside.mean() > 0.9
+    iw = l0 / vd[0, 3] + l1 / vd[1, 3] + l2 / vd[2, 3]
+    b0, b1, b2 = l0 / vd[0, 3] / iw, l1 / vd[1, 3] / iw, l2 / vd[2, 3] / iw
+    want = b0[:, None] * col[0, 0] + b1[:, None] * col[0, 1] + b2[:, None] * col[0, 2]
+    got = px[0][cov]
+    # vertices are snapped to 1/256 px before interpolation (docs/RASTER_SPEC.md), which moves a weight by ~1e-5 here
+    assert np.abs(got - want)[inside].max() < 5e-5
+    g = gb[0][cov]
+    assert np.abs(g[:, 0] - b0)[inside].max() < 5e-5 and np.abs(g[:, 1] - b1)[inside].max() < 5e-5
+    assert np.abs(g[:, 2] * iw - 1)[inside].max() < 5e-5                 # clip-space w
+    zw = (l0 * ndc[0, 2] + l1 * ndc[1, 2] + l2 * ndc[2, 2] + 1) / 2
+    assert np.abs(g[:, 3] - zw)[inside].max() < 5e-5                     # window depth is linear on the screen
+    assert (px[0][~cov] == -7.0).all()
