@@ -10,8 +10,8 @@
 //            triangle" leaves most lanes idle on long thin triangles
 //            (profiles/r1_setup_notes.md): the unit of work is a scan LINE of a triangle --
 //            a row or a column, whichever makes the lines' spans short (slivers are scanned
-//            across their narrow side).  A warp prefix sum over the lines per triangle and a
-//            5-step shuffle search hand 32 lines at a time to the 32 lanes.  Each lane
+//            across their narrow side).  A warp prefix sum over the lines per triangle, one
+//            OR-reduction of start bits and two population counts hand 32 lines at a time to the 32 lanes.  Each lane
 //            computes its line's EXACT covered span (each edge crossing is a ceiling division
 //            evaluated in float in a form that is provably exact for these operand ranges, so
 //            coverage stays an integer decision) and walks it: plane depth, depth|face key, a plain load
