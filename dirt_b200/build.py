@@ -57,7 +57,7 @@ def build(force=False, verbose=False, defines=(), out=None):
         if p.returncode != 0:
             raise RuntimeError("nvcc failed: " + " ".join(cmd))
     target = LIB if out is None else os.path.join(HERE, out)
-    cmd = [nvcc, "-shared", "-cudart", "static", "-o", target] + objs
+    cmd = [nvcc, "-shared", "-cudart", "static", "-gencode", "arch=compute_100a,code=sm_100a", "-o", target] + objs
     subprocess.check_call(cmd)
     return target
 
