@@ -112,3 +112,130 @@ def test_guard_zones_inputs_and_workspace_independence(case):
     B, H, W, C = sc["background"].shape
     _, ofid, _ = golden.forward(sc["background"], sc["vertices"], sc["vertex_colors"], sc["faces"], threads=8)
     assert np.array_equal(a["face_id"].view(np.int32).reshape(B, H, W), ofid)
+
+
+def _f32(t):
+    import torch
+    return t.view(torch.float32)
+
+
+def test_guard_zones_dilate_and_vertex_normals():
+    import torch
+    from dirt_b200 import _lib
+    lib = _lib.load()
+    stream = torch.cuda.current_stream().cuda_stream
+    rs = np.random.RandomState(3)
+    # silhouette dilation, odd frame
+    B, H, W, C = 2, 19, 45, 3
+    x = rs.randn(B, H, W, C).astype(np.float32)
+    x[rs.rand(B, H, W) < 0.5] = -np.inf
+    arena = Arena(6 * x.nbytes + 16 * (GUARD + 256))
+    dx, go = arena.put(x), arena.put(rs.randn(B, H, W, C).astype(np.float32))
+    out, gx = arena.carve(x.nbytes), arena.carve(x.nbytes)
+    _lib.check(lib.dirt_dilate_silhouette(dx.data_ptr(), out.data_ptr(), B, H, W, C, stream))
+    _lib.check(lib.dirt_dilate_silhouette_grad(dx.data_ptr(), go.data_ptr(), gx.data_ptr(), B, H, W, C, stream))
+    torch.cuda.synchronize()
+    assert arena.guards_intact(), "dilate wrote outside its buffers"
+    assert np.array_equal(dx.cpu().numpy(), x.view(np.uint8).reshape(-1))
+    assert torch.isfinite(_f32(gx)).all()
+
+    # vertex normals, D = 3 and 4, with out-of-range faces
+    for D in (3, 4):
+        Bn, V, F = 3, 101, 333
+        v = rs.randn(Bn, V, D).astype(np.float32)
+        f = rs.randint(0, V, size=(F, 3)).astype(np.int32)
+        f[5] = (-1, 2, 3)
+        f[9] = (1, V, 3)
+        arena = Arena(v.nbytes * 2 + f.nbytes + 5 * Bn * V * 12 + 16 * (GUARD + 256))
+        dv, df = arena.put(v), arena.put(f)
+        sums, normals, gs = arena.carve(Bn * V * 12), arena.carve(Bn * V * 12), arena.carve(Bn * V * 12)
+        gn = arena.put(rs.randn(Bn, V, 3).astype(np.float32))
+        gvt = arena.carve(v.nbytes)
+        _lib.check(lib.dirt_vertex_normals(dv.data_ptr(), Bn, V, D, df.data_ptr(), F, sums.data_ptr(), normals.data_ptr(), stream))
+        _lib.check(lib.dirt_vertex_normals_grad(dv.data_ptr(), Bn, V, D, df.data_ptr(), F, sums.data_ptr(), gn.data_ptr(),
+                                                gs.data_ptr(), gvt.data_ptr(), stream))
+        torch.cuda.synchronize()
+        assert arena.guards_intact(), "vertex normals wrote outside their buffers (D=%d)" % D
+        assert np.array_equal(dv.cpu().numpy(), v.view(np.uint8).reshape(-1)) and np.array_equal(df.cpu().numpy(), f.view(np.uint8).reshape(-1))
+        assert torch.isfinite(_f32(normals)).all() and torch.isfinite(_f32(gvt)).all()
+
+
+@pytest.mark.parametrize("scene,Cb,C", [(0, 3, 3), (3, 3, 3), (5, 1, 3), (6, 4, 3), (6, 1, 1), (4, 3, 4)])
+def test_guard_zones_scene_shade(scene, Cb, C):
+    """The scene stage after a forward over a full-screen quad: camera_pos holds exactly the floats
+    the scene reads, the texture / jitter has its own channel count."""
+    import torch
+    from dirt_b200 import _lib
+    from dirt_b200._lib import DirtShape, DirtForwardArgs, DirtSceneArgs
+    lib = _lib.load()
+    stream = torch.cuda.current_stream().cuda_stream
+    rs = np.random.RandomState(scene)
+    B, H, W, V, F = 2, 27, 41, 4, 2
+    n_cam = lib.dirt_scene_camera_floats(scene)
+    quad = np.tile(np.array([[-1, -1, 0, 1], [-1, 1, 0, 1], [1, 1, 0, 1], [1, -1, 0, 1]], np.float32), (B, 1, 1))
+    faces = np.tile(np.array([[0, 1, 2], [0, 2, 3]], np.int32), (B, 1, 1))
+    tex = rs.rand(B, H, W, Cb).astype(np.float32)
+    cam = np.zeros(n_cam, np.float32)
+    cam[1] = 150.0 if scene != 6 else 0.0
+    if scene == 6:
+        cam[11] = 3.0
+    shape = DirtShape(B, H, W, C, V, F)
+    ws_bytes = lib.dirt_workspace_bytes(ctypes.byref(shape))
+    npx = B * H * W
+    arena = Arena(tex.nbytes + npx * (C * 8 + 4 + 16 + 4 * C) + quad.nbytes + faces.nbytes + ws_bytes + B * V * C * 4 + 4096 + 20 * (GUARD + 256))
+    d_tex, d_quad, d_faces, d_cam = arena.put(tex), arena.put(quad), arena.put(faces), arena.put(cam)
+    d_col = arena.put(np.ones((B, V, C), np.float32))
+    d_blank = arena.put(np.zeros((B, H, W, C), np.float32))
+    px, fid, gb, ws = arena.carve(npx * C * 4), arena.carve(npx * 4), arena.carve(npx * 16), arena.carve(ws_bytes)
+    fwd = DirtForwardArgs(shape, d_blank.data_ptr(), H * W * C, d_quad.data_ptr(), V * 4, d_col.data_ptr(), V * C,
+                          d_faces.data_ptr(), F * 3, px.data_ptr(), fid.data_ptr(), gb.data_ptr(), ws.data_ptr(), ws_bytes)
+    _lib.check(lib.dirt_rasterise_forward(ctypes.byref(fwd), stream))
+    sa = DirtSceneArgs(shape, d_tex.data_ptr(), H * W * Cb, d_quad.data_ptr(), V * 4, d_faces.data_ptr(), F * 3,
+                       fid.data_ptr(), gb.data_ptr(), d_cam.data_ptr(), px.data_ptr())
+    _lib.check(lib.dirt_scene_shade(scene, ctypes.byref(sa), Cb, n_cam, stream))
+    torch.cuda.synchronize()
+    assert arena.guards_intact(), "scene %d wrote outside its buffers" % scene
+    assert np.array_equal(d_tex.cpu().numpy(), tex.view(np.uint8).reshape(-1))
+    assert np.array_equal(d_cam.cpu().numpy(), cam.view(np.uint8).reshape(-1))
+    assert (_f32(fid).view(torch.int32) >= 0).all()
+    # one float fewer than the scene reads is refused
+    assert lib.dirt_scene_shade(scene, ctypes.byref(sa), Cb, n_cam - 1, stream) != 0
+
+
+def test_guard_zones_shared_mesh_backward():
+    import torch
+    from dirt_b200 import _lib
+    from dirt_b200._lib import DirtShape, DirtForwardArgs, DirtSharedBackwardArgs
+    lib = _lib.load()
+    stream = torch.cuda.current_stream().cuda_stream
+    sc = scenes.hill(3, 61, 83, 3, n=23, seed=1)
+    B, H, W, C = 3, 61, 83, 3
+    V, F = sc["vertices"].shape[1], sc["faces"].shape[1]
+    shape = DirtShape(B, H, W, C, V, F)
+    ws_bytes = lib.dirt_workspace_bytes(ctypes.byref(shape))
+    stride = lib.dirt_shared_grad_stride(C)
+    npx = B * H * W
+    g = np.random.RandomState(0).randn(B, H, W, C).astype(np.float32)
+    M = np.random.RandomState(1).randn(B, 4, 4).astype(np.float32)
+    bg = np.ascontiguousarray(np.broadcast_to(sc["background"], (B, H, W, C)))
+    total = (bg.nbytes + sc["vertices"].nbytes + sc["vertex_colors"].nbytes + sc["faces"].nbytes + g.nbytes + M.nbytes
+             + npx * (C * 8 + 20) + V * stride * 4 + ws_bytes + 20 * (GUARD + 256))
+    arena = Arena(total)
+    d_bg, d_v, d_c, d_f = arena.put(bg), arena.put(sc["vertices"]), arena.put(sc["vertex_colors"]), arena.put(sc["faces"])
+    d_g, d_M = arena.put(g), arena.put(M)
+    px, fid, gb, ws = arena.carve(npx * C * 4), arena.carve(npx * 4), arena.carve(npx * 16), arena.carve(ws_bytes)
+    packed, gbg = arena.carve(V * stride * 4), arena.carve(npx * C * 4)
+    packed.fill_(0x7F)                      # "zeroed by the callee"
+    cb = 0 if sc["vertex_colors"].shape[0] == 1 else V * C
+    fb = 0 if sc["faces"].shape[0] == 1 else F * 3
+    fwd = DirtForwardArgs(shape, d_bg.data_ptr(), H * W * C, d_v.data_ptr(), V * 4, d_c.data_ptr(), cb, d_f.data_ptr(), fb,
+                          px.data_ptr(), fid.data_ptr(), gb.data_ptr(), ws.data_ptr(), ws_bytes)
+    _lib.check(lib.dirt_rasterise_forward(ctypes.byref(fwd), stream))
+    bwd = DirtSharedBackwardArgs(shape, d_f.data_ptr(), fb, px.data_ptr(), d_g.data_ptr(), fid.data_ptr(), gb.data_ptr(),
+                                 d_M.data_ptr(), packed.data_ptr(), gbg.data_ptr())
+    _lib.check(lib.dirt_rasterise_backward_shared(ctypes.byref(bwd), stream))
+    torch.cuda.synchronize()
+    assert arena.guards_intact(), "the shared-mesh backward wrote outside its buffers"
+    p = _f32(packed).view(V, stride)
+    assert torch.isfinite(p).all() and p.abs().max() > 0 and (p[:, 4 + C:] == 0).all()
+    assert (_f32(fid).view(torch.int32) >= 0).float().mean() > 0.2
