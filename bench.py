@@ -210,7 +210,8 @@ def run_reference(args, wl, rank, world):
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * total / max(args.steps, 1), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload + ": " + wl["desc"], "note": "host-CPU run of the oracle port; bounded sample per step"},
+        "config": {"workload": args.workload + ": " + wl["desc"], "note": "host-CPU run of the oracle port; a step is several runs of a bounded sample (cpu_baseline.sample): "
+                                        "ms_per_step is the wall time of all of a step's runs, value comes from the median run"},
         "cpu_baseline": base,
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
