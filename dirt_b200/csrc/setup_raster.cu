@@ -35,6 +35,9 @@ constexpr int kWarpsPerCta = 8;
 #ifndef KPRE0
 #define KPRE0 0
 #endif
+#ifndef KLDCG
+#define KLDCG 0      // 1: the depth pre-load bypasses L1 (sees the reductions of this launch)
+#endif
 constexpr int kCtasPerSm = KCTAS;                     // the kernel waits on depth loads: occupancy over registers
 constexpr int kFragRound = KFRAG;                     // spans are 1-2 pixels on 3 lines out of 4 (profiles/r1_setup_notes.md)
 constexpr long long kFewFaces = 4096;
@@ -131,7 +134,11 @@ __device__ __forceinline__ void red_min_key(unsigned long long *kp, unsigned lon
 __device__ __forceinline__ uint32_t load_depth_word(const unsigned long long *kp)
 {
     uint32_t v;
+#if KLDCG
+    asm volatile("ld.global.cg.u32 %0, [%1];" : "=r"(v) : "l"(reinterpret_cast<const uint32_t *>(kp) + 1));
+#else
     asm volatile("ld.global.ca.u32 %0, [%1];" : "=r"(v) : "l"(reinterpret_cast<const uint32_t *>(kp) + 1));
+#endif
     return v;
 }
 
