@@ -1,5 +1,5 @@
-"""Per-stage device times (ms) of fwd+bwd for several workloads; development aid.
-    python tools/stages.py [headline c4 c3 c2 ...]"""
+"""Per-stage device times (ms) of fwd+bwd for several workloads (c1: forward only); development aid.
+    python tools/stages.py [headline c4 c3 c2 c1 ...]"""
 import os
 import sys
 
@@ -23,6 +23,10 @@ def scene(name):
         return scenes.cube(B=16, H=512, W=512)
     if name == "c2":
         return scenes.cube(B=1, H=256, W=256)
+    if name == "c1":                      # README.md:46-70, forward only
+        sc = scenes.kat1_square()
+        sc.pop("expected")
+        return sc
     if name == "soup":
         return scenes.random_triangles(16, 512, 512, 3, 2000, seed=1, size=0.3)
     if name == "quad":
@@ -35,7 +39,7 @@ def scene(name):
 
 def main():
     lib = _lib.load()
-    for name in (sys.argv[1:] or ["headline", "c4", "c3", "c2"]):
+    for name in (sys.argv[1:] or ["headline", "c4", "c3", "c2", "c1"]):
         sc = scene(name)
         d = {k: torch.from_numpy(np.ascontiguousarray(v)).cuda() for k, v in sc.items()}
         B, H, W, C = sc["background"].shape
@@ -43,6 +47,8 @@ def main():
         g = torch.randn(B, H, W, C, device="cuda")
 
         def step():
+            if name == "c1":
+                return ops.forward_raw(d["background"], d["vertices"], d["vertex_colors"], d["faces"], want_aux=False)
             px, fid, gb = ops.forward_raw(d["background"], d["vertices"], d["vertex_colors"], d["faces"])
             return ops.backward_raw(d["faces"], px, g, fid, gb, V)
 
