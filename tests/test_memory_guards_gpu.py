@@ -34,7 +34,7 @@ class Arena:
     def put(self, array):
         import torch
         t = self.carve(array.nbytes)
-        t.copy_(torch.from_numpy(np.ascontiguousarray(array)).view(-1).view(torch.uint8))
+        t.copy_(torch.from_numpy(np.array(array, copy=True, order="C")).view(-1).view(torch.uint8))
         return t
 
     def guards_intact(self):
