@@ -239,3 +239,48 @@ def test_guard_zones_shared_mesh_backward():
     p = _f32(packed).view(V, stride)
     assert torch.isfinite(p).all() and p.abs().max() > 0 and (p[:, 4 + C:] == 0).all()
     assert (_f32(fid).view(torch.int32) >= 0).float().mean() > 0.2
+
+
+def test_guard_zones_host_entry_points():
+    """dirt_rasterise_forward_host / _backward_host: HOST buffers carved from one numpy arena."""
+    from dirt_b200 import _lib
+    from dirt_b200._lib import DirtShape, DirtForwardArgs, DirtBackwardArgs
+    lib = _lib.load()
+    sc = scenes.random_triangles(3, 35, 51, 3, 157, seed=21, size=0.6)
+    B, H, W, C = sc["background"].shape
+    V, F = sc["vertices"].shape[1], sc["faces"].shape[1]
+    g = np.random.RandomState(0).randn(B, H, W, C).astype(np.float32)
+    npx = B * H * W
+    sizes = {"pixels": npx * C * 4, "face_id": npx * 4, "gbuffer": npx * 16, "gv": B * V * 16, "gc": B * V * C * 4, "gbg": npx * C * 4}
+    ins = {k: np.array(sc[k], copy=True, order="C") for k in ("background", "vertices", "vertex_colors", "faces")}
+    ins["g"] = g
+    arena = np.full(sum(sizes.values()) + sum(a.nbytes for a in ins.values()) + 16 * (GUARD + 256), SENTINEL, np.uint8)
+    base = arena.ctypes.data
+    off = (-base) % 256 + GUARD
+    spans, ptr = [], {}
+    for k, n in list((k, a.nbytes) for k, a in ins.items()) + list(sizes.items()):
+        spans.append((off, n))
+        ptr[k] = base + off
+        if k in ins:
+            arena[off:off + n] = ins[k].view(np.uint8).reshape(-1)
+        off = (off + n + GUARD + 255) // 256 * 256
+    assert off <= arena.size
+    shape = DirtShape(B, H, W, C, V, F)
+    fa = DirtForwardArgs(shape, ptr["background"], H * W * C, ptr["vertices"], V * 4, ptr["vertex_colors"], V * C, ptr["faces"], F * 3,
+                         ptr["pixels"], ptr["face_id"], ptr["gbuffer"], None, 0)
+    _lib.check(lib.dirt_rasterise_forward_host(ctypes.byref(fa)))
+    ba = DirtBackwardArgs(shape, ptr["faces"], F * 3, ptr["pixels"], ptr["g"], ptr["face_id"], ptr["gbuffer"],
+                          ptr["gv"], V * 4, ptr["gc"], V * C, ptr["gbg"])
+    _lib.check(lib.dirt_rasterise_backward_host(ctypes.byref(ba)))
+    _lib.check(lib.dirt_release_host_staging())
+    mask = np.ones(arena.size, bool)
+    for o, n in spans:
+        mask[o:o + n] = False
+    assert (arena[mask] == SENTINEL).all(), "a host entry point wrote outside its buffers"
+    for k, a in ins.items():
+        o = ptr[k] - base
+        assert np.array_equal(arena[o:o + a.nbytes], a.view(np.uint8).reshape(-1)), k + " was modified"
+    o = ptr["face_id"] - base
+    from oracle import golden
+    _, ofid, _ = golden.forward(sc["background"], sc["vertices"], sc["vertex_colors"], sc["faces"])
+    assert np.array_equal(arena[o:o + npx * 4].view(np.int32).reshape(B, H, W), ofid)
