@@ -192,10 +192,14 @@ __global__ void __launch_bounds__(kTileThreads) k_tile_raster(FwdParams p)
 }
 
 // Barycentrics of pixel (px, py) on a face that went through the clipper (rare): finds the
-// fan triangle that owns the pixel (exactly one does) and folds the fan weights back onto the
-// face's own corners.
+// fan triangle whose fragment won the pixel and folds the fan weights back onto the face's own
+// corners.  Normally exactly one fan triangle covers the pixel; when clipped corners land beyond
+// the guard band their window positions are clamped, the fan can fold over itself, and several
+// do -- then the winner is the one the depth test kept: the first (in fan order) whose 24-bit
+// depth equals the depth in the key, which is what the sequential rule "nearest fragment, first
+// on a tie" leaves.
 static __device__ __noinline__ void resolve_clipped(const FwdParams &p, int b, int i0, int i1, int i2, int px, int py,
-                                                    float &B0, float &B1, float &wc)
+                                                    uint32_t depth, float &B0, float &B1, float &wc)
 {
     const float4 *vp = vertex_ptr(p.vertices, p.vertices_bs, b);
     const float4 va = __ldg(vp + i0), vb = __ldg(vp + i1), vc = __ldg(vp + i2);
@@ -208,6 +212,8 @@ static __device__ __noinline__ void resolve_clipped(const FwdParams &p, int b, i
         long long e0, e1, e2;
         edge_values(t, px, py, e0, e1, e2);
         if (!covered(t, e0, e1, e2)) continue;
+        unsigned long long key;
+        if (!depth_key(sample_depth(t, px, py), 0u, key) || (uint32_t)(key >> 32) != depth) continue;
         float l0, l1, l2, b0, b1, b2;
         screen_bary(t, e0, e1, e2, l0, l1, l2);
         perspective_weights(t, l0, l1, l2, b0, b1, b2, wc);
@@ -308,7 +314,7 @@ __global__ void __launch_bounds__(256, KRES_CTAS) k_resolve(FwdParams p)
             perspective_weights(t, l0, l1, l2, B0, B1, b2, wc);
         } else {
             const FwdParams pc = p;      // keeps the kernel parameter block itself out of local memory
-            resolve_clipped(pc, b, i0, i1, i2, px, py, B0, B1, wc);
+            resolve_clipped(pc, b, i0, i1, i2, px, py, (uint32_t)(key >> 32), B0, B1, wc);
         }
         const float *cp = p.vertex_colors + (int64_t)b * p.vertex_colors_bs;
         const float *c0 = cp + (int64_t)i0 * CC, *c1 = cp + (int64_t)i1 * CC, *c2 = cp + (int64_t)i2 * CC;
