@@ -61,3 +61,43 @@ def test_fuzz_forward_backward(seed):
     for name, a, b in (("grad_vertices", gv.cpu().numpy(), ogv), ("grad_vertex_colors", gc.cpu().numpy(), ogc)):
         assert a.shape == b.shape, name
         assert np.abs(a - b).max() <= 1e-4 * max(np.abs(b).max(), 1e-12), name
+
+
+def _ordered_case(seed):
+    """Meshes past the threshold of the depth-ordered passes (>= 4096 faces per element) with real
+    overdraw, so that the nearest-first buckets, the depth pyramid and its culling all run."""
+    rng = np.random.RandomState(5000 + seed)
+    B = int(rng.randint(1, 4))
+    H, W = int(rng.randint(40, 200)), int(rng.randint(40, 200))
+    C = int(rng.choice([1, 3, 3, 4]))
+    F = int(rng.choice([4096, 5000, 9000, 16384]))
+    size = float(rng.choice([0.15, 0.3, 0.6, 1.2]))
+    sc = scenes.random_triangles(B, H, W, C, F, seed=seed, size=size, depth_ties=bool(rng.randint(2)),
+                                 w_range=(0.5, 2.0) if rng.randint(3) else (-0.2, 2.0))
+    sc = {k: np.ascontiguousarray(v).copy() for k, v in sc.items()}
+    if B > 1:
+        for k in ("background", "vertices", "vertex_colors", "faces"):
+            if rng.randint(4) == 0:
+                sc[k] = sc[k][:1].copy()
+    return sc, max(v.shape[0] for v in sc.values())
+
+
+@pytest.mark.parametrize("seed", range(32))
+def test_fuzz_depth_ordered_path(seed):
+    import torch
+    from dirt_b200 import rasterise_ops as ops
+    sc, B = _ordered_case(seed)
+    t = {k: torch.from_numpy(v).cuda() for k, v in sc.items()}
+    px, fid, gb = ops.forward_raw(t["background"], t["vertices"], t["vertex_colors"], t["faces"])
+    opx, ofid, ogb = golden.forward(sc["background"], sc["vertices"], sc["vertex_colors"], sc["faces"], threads=8)
+    assert np.array_equal(fid.cpu().numpy(), ofid), "face ids differ at %d pixels" % (fid.cpu().numpy() != ofid).sum()
+    np.testing.assert_allclose(px.cpu().numpy(), opx, rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(gb.cpu().numpy(), ogb, rtol=1e-5, atol=1e-6)
+    g = np.random.RandomState(seed).randn(*opx.shape).astype(np.float32)
+    V = sc["vertices"].shape[1]
+    sv, scol = sc["vertices"].shape[0] == 1 and B > 1, sc["vertex_colors"].shape[0] == 1 and B > 1
+    gv, gc, gbg = ops.backward_raw(t["faces"], px, torch.from_numpy(g).cuda(), fid, gb, V, shared_vertices=sv, shared_colors=scol)
+    ogv, ogc, ogbg = golden.backward(sc["faces"], opx, g, ofid, ogb, V, shared_vertices=sv, shared_colors=scol, threads=8)
+    assert np.array_equal(gbg.cpu().numpy(), ogbg)
+    for name, a, b in (("grad_vertices", gv.cpu().numpy(), ogv), ("grad_vertex_colors", gc.cpu().numpy(), ogc)):
+        assert np.abs(a - b).max() <= 1e-4 * max(np.abs(b).max(), 1e-12), name
