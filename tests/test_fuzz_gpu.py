@@ -101,3 +101,54 @@ def test_fuzz_depth_ordered_path(seed):
     assert np.array_equal(gbg.cpu().numpy(), ogbg)
     for name, a, b in (("grad_vertices", gv.cpu().numpy(), ogv), ("grad_vertex_colors", gc.cpu().numpy(), ogc)):
         assert np.abs(a - b).max() <= 1e-4 * max(np.abs(b).max(), 1e-12), name
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_fuzz_dilate(seed):
+    """dirt_dilate_silhouette (+grad) against oracle/dilate.py over ragged shapes and hole densities."""
+    import torch
+    import dirt_b200
+    from oracle import dilate as odil
+    rng = np.random.RandomState(7000 + seed)
+    shape = (int(rng.randint(1, 4)), int(rng.randint(1, 70)), int(rng.randint(1, 70)), int(rng.choice([1, 2, 3, 4, 6, 9, 16])))
+    x = rng.randn(*shape).astype(np.float32)
+    x[rng.uniform(size=shape[:3]) < rng.choice([0.0, 0.1, 0.5, 0.9, 1.0])] = -np.inf
+    xt = torch.from_numpy(x).cuda().requires_grad_(True)
+    out = dirt_b200.dilate_silhouette(xt)
+    assert np.array_equal(out.detach().cpu().numpy(), odil.dilate(x))
+    g = rng.randn(*shape).astype(np.float32)
+    out.backward(torch.from_numpy(g).cuda())
+    np.testing.assert_allclose(xt.grad.cpu().numpy(), odil.dilate_grad(x, g), rtol=1e-6, atol=1e-6)
+
+
+@pytest.mark.parametrize("seed", range(16))
+def test_fuzz_shared_mesh_backward(seed):
+    """dirt_rasterise_backward_shared against the oracle's per-frame gradients folded on the host."""
+    import torch
+    from dirt_b200 import rasterise_ops as ops
+    rng = np.random.RandomState(9000 + seed)
+    B, H, W = int(rng.randint(1, 5)), int(rng.randint(8, 90)), int(rng.randint(8, 90))
+    C = int(rng.choice([1, 3, 3, 4, 7]))
+    F = int(rng.choice([1, 12, 200, 5000]))
+    one = scenes.random_triangles(1, H, W, C, F, seed=seed, size=float(rng.choice([0.05, 0.4, 1.5])))
+    world = one["vertices"][0].astype(np.float64)
+    V = world.shape[0]
+    M = np.stack([np.eye(4) + 0.05 * rng.randn(4, 4) for _ in range(B)])
+    sc = {"background": rng.uniform(0, 1, (B, H, W, C)).astype(np.float32),
+          "vertices": np.einsum("vi,bij->bvj", world, M).astype(np.float32),
+          "vertex_colors": one["vertex_colors"].copy(), "faces": np.ascontiguousarray(one["faces"]).copy()}
+    t = {k: torch.from_numpy(v).cuda() for k, v in sc.items()}
+    px, fid, gb = ops.forward_raw(t["background"], t["vertices"], t["vertex_colors"], t["faces"])
+    opx, ofid, ogb = golden.forward(sc["background"], sc["vertices"], sc["vertex_colors"], sc["faces"], threads=4)
+    assert np.array_equal(fid.cpu().numpy(), ofid)
+    g = rng.randn(B, H, W, C).astype(np.float32)
+    packed, gbg = ops.backward_shared_raw(t["faces"], px, torch.from_numpy(g).cuda(), fid, gb, V,
+                                          torch.from_numpy(M.astype(np.float32)).cuda())
+    ogv, ogc, ogbg = golden.backward(sc["faces"], opx, g, ofid, ogb, V, shared_colors=B > 1, threads=4)
+    want_v = np.einsum("bvj,bij->vi", ogv.astype(np.float64), M.astype(np.float32).astype(np.float64))
+    want_c = ogc.astype(np.float64).sum(0)
+    got = packed.cpu().numpy()
+    assert np.array_equal(gbg.cpu().numpy(), ogbg)
+    assert np.abs(got[:, :4] - want_v).max() <= 1e-4 * max(np.abs(want_v).max(), 1e-12)
+    assert np.abs(got[:, 4:4 + C] - want_c.reshape(V, C)).max() <= 1e-4 * max(np.abs(want_c).max(), 1e-12)
+    assert not got[:, 4 + C:].any()
