@@ -152,3 +152,57 @@ def test_fuzz_shared_mesh_backward(seed):
     assert np.abs(got[:, :4] - want_v).max() <= 1e-4 * max(np.abs(want_v).max(), 1e-12)
     assert np.abs(got[:, 4:4 + C] - want_c.reshape(V, C)).max() <= 1e-4 * max(np.abs(want_c).max(), 1e-12)
     assert not got[:, 4 + C:].any()
+
+
+def _extreme_case(seed):
+    """Geometry at the edges of the clip volume and of the number range: corners exactly on the near
+    / far plane, w a hair above zero (window positions hit the guard-band clamp), huge coordinates,
+    degenerate faces (repeated corner, zero area), frames that are one pixel wide or very wide."""
+    rng = np.random.RandomState(11000 + seed)
+    B = int(rng.randint(1, 3))
+    H, W = [(1, 300), (300, 1), (5, 1031), (64, 64), (97, 33), (17, 200)][seed % 6]
+    C = int(rng.choice([1, 3]))
+    F = int(rng.choice([6, 60, 600]))
+    sc = scenes.random_triangles(B, H, W, C, F, seed=seed, size=float(rng.choice([0.3, 1.0, 3.0])), w_range=(-0.1, 2.0))
+    sc = {k: np.ascontiguousarray(v).copy() for k, v in sc.items()}
+    v = sc["vertices"]
+    V = v.shape[1]
+    pick = lambda frac: rng.uniform(size=(B, V)) < frac
+    m = pick(0.08); v[m, 2] = v[m, 3]                                   # exactly on the far plane
+    m = pick(0.08); v[m, 2] = -v[m, 3]                                  # exactly on the near plane
+    m = pick(0.05); v[m, 3] = rng.choice([1e-7, 1e-5, 1e-3], size=m.sum()).astype(np.float32)   # w -> 0+
+    m = pick(0.03); v[m, :2] *= 1e6                                     # far outside the guard band
+    m = pick(0.02); v[m, 3] = 0.0
+    f = sc["faces"]
+    k = max(1, F // 12)
+    idx = rng.randint(0, F, k)
+    f[:, idx, 1] = f[:, idx, 0]                                         # repeated corner
+    idx = rng.randint(0, F, k)
+    v[:, f[0, idx, 2]] = v[:, f[0, idx, 1]]                             # coincident corners: zero area
+    return sc
+
+
+@pytest.mark.parametrize("seed", range(48))
+def test_fuzz_extreme_geometry(seed):
+    import torch
+    from dirt_b200 import rasterise_ops as ops
+    sc = _extreme_case(seed)
+    t = {k: torch.from_numpy(v).cuda() for k, v in sc.items()}
+    px, fid, gb = ops.forward_raw(t["background"], t["vertices"], t["vertex_colors"], t["faces"])
+    opx, ofid, ogb = golden.forward(sc["background"], sc["vertices"], sc["vertex_colors"], sc["faces"], threads=4)
+    assert np.array_equal(fid.cpu().numpy(), ofid), "face ids differ at %d pixels" % (fid.cpu().numpy() != ofid).sum()
+    fin = np.isfinite(opx)
+    assert np.array_equal(np.isfinite(px.cpu().numpy()), fin)
+    np.testing.assert_allclose(px.cpu().numpy()[fin], opx[fin], rtol=1e-5, atol=1e-6)
+    fin = np.isfinite(ogb)
+    assert np.array_equal(np.isfinite(gb.cpu().numpy()), fin)
+    np.testing.assert_allclose(gb.cpu().numpy()[fin], ogb[fin], rtol=1e-5, atol=1e-6)
+    g = np.random.RandomState(seed).randn(*opx.shape).astype(np.float32)
+    V = sc["vertices"].shape[1]
+    gv, gc, gbg = ops.backward_raw(t["faces"], px, torch.from_numpy(g).cuda(), fid, gb, V)
+    ogv, ogc, ogbg = golden.backward(sc["faces"], opx, g, ofid, ogb, V, threads=4)
+    assert np.array_equal(gbg.cpu().numpy(), ogbg)
+    for name, a, b in (("grad_vertices", gv.cpu().numpy(), ogv), ("grad_vertex_colors", gc.cpu().numpy(), ogc)):
+        fin = np.isfinite(b)
+        assert np.array_equal(np.isfinite(a), fin), name
+        assert np.abs(a[fin] - b[fin]).max() <= 1e-4 * max(np.abs(b[fin]).max(), 1e-12), name
