@@ -206,3 +206,40 @@ def test_fuzz_extreme_geometry(seed):
         fin = np.isfinite(b)
         assert np.array_equal(np.isfinite(a), fin), name
         assert np.abs(a[fin] - b[fin]).max() <= 1e-4 * max(np.abs(b[fin]).max(), 1e-12), name
+
+
+@pytest.mark.parametrize("seed", range(4))
+@pytest.mark.parametrize("name", ["oceanic", "oceanic_still_cloud", "oceanic_no_cloud", "oceanic_simple_proxy", "oceanic_opt_flow", "hill"])
+def test_fuzz_scene_cameras(name, seed):
+    """The scene stages under random cameras, frame sizes and jitter, against the C/C++ oracle with the
+    bars of tests/test_scene_shaders.py (mean <= 1e-6, <= 0.2 % of the pixels beyond 1e-4)."""
+    import torch
+    import dirt_b200
+    import test_scene_shaders as ts
+    rng = np.random.RandomState(13000 + 17 * seed + len(name))
+    B, H, W = int(rng.randint(1, 3)), int(rng.randint(8, 60)), int(rng.randint(8, 90))
+    if name == "hill":
+        C, Cb = int(rng.choice([1, 3])), int(rng.choice([1, 3, 4]))
+        _, v, c, f = ts.quad(B, H, W, C)
+        tex = np.stack([ts.terrain_texture(H, W) for _ in range(B)])[..., :Cb]
+        tex = np.ascontiguousarray(tex + 0.02 * rng.randn(*tex.shape).astype(np.float32))
+        cam = ts.HILL_CAM.copy()
+        cam[9:12] = [rng.uniform(-3, 3), rng.uniform(-1, 1), rng.uniform(1.5, 6.0)]
+        ref = golden.scene("hill", tex, v, f, cam, channels=C)
+        out = dirt_b200.hill_batch(torch.from_numpy(tex).cuda(), torch.from_numpy(v).cuda(), torch.from_numpy(c).cuda(),
+                                   torch.from_numpy(f).cuda(), cam, channels=C).cpu().numpy()
+        scale = 1.0
+    else:
+        C = 3
+        bg, v, c, f = ts.quad(B, H, W, C, seed=seed, noise=float(rng.choice([0.0, 0.3, 1.0])))
+        base = np.array(ts.CAM_A if rng.randint(2) else ts.CAM_B, np.float64)
+        cam = base + rng.randn(16) * np.array([40, 30, 40, 0.1, 0.2, 0.1, 2, 0.3, 1, 0.05, 20, 5, 10, 0.1, 0.1, 0.1])
+        cam[1] = max(cam[1], 85.0)                       # stay above the swell
+        cam = cam.astype(np.float32)
+        ref = golden.scene(name, bg, v, f, cam)
+        out = getattr(dirt_b200, name + "_batch")(torch.from_numpy(bg).cuda(), torch.from_numpy(v).cuda(), torch.from_numpy(c).cuda(),
+                                                  torch.from_numpy(f).cuda(), cam).cpu().numpy()
+        scale = max(1.0, float(np.nanmax(np.abs(ref)))) if name == "oceanic_opt_flow" else 1.0
+    assert out.shape == ref.shape
+    mean, beyond = ts._stats(out / scale, ref / scale, 1e-4)
+    assert mean <= 1e-6 and beyond <= 0.002, (name, seed, mean, beyond)
