@@ -243,3 +243,21 @@ def test_fuzz_scene_cameras(name, seed):
     assert out.shape == ref.shape
     mean, beyond = ts._stats(out / scale, ref / scale, 1e-4)
     assert mean <= 1e-6 and beyond <= 0.002, (name, seed, mean, beyond)
+
+
+@pytest.mark.parametrize("F,size", [(4000, 3.0), (3000, 30.0), (9000, 2.0)])
+def test_work_list_overflow_paths(F, size):
+    """More large / clipped triangles than the workspace's lists hold (their capacities bound memory,
+    not correctness): the in-thread fallbacks of the large-triangle list and of the tile queues
+    must give the same image."""
+    import torch
+    from dirt_b200 import rasterise_ops as ops
+    sc = scenes.random_triangles(1, 64, 80, 3, F, seed=F, size=size, w_range=(-0.6, 1.0))
+    sc = {k: np.ascontiguousarray(v).copy() for k, v in sc.items()}
+    t = {k: torch.from_numpy(v).cuda() for k, v in sc.items()}
+    px, fid, gb = ops.forward_raw(t["background"], t["vertices"], t["vertex_colors"], t["faces"])
+    opx, ofid, ogb = golden.forward(sc["background"], sc["vertices"], sc["vertex_colors"], sc["faces"], threads=8)
+    assert (ofid >= 0).mean() > 0.9
+    assert np.array_equal(fid.cpu().numpy(), ofid), "face ids differ at %d pixels" % (fid.cpu().numpy() != ofid).sum()
+    np.testing.assert_allclose(px.cpu().numpy(), opx, rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(gb.cpu().numpy(), ogb, rtol=1e-5, atol=1e-6)
