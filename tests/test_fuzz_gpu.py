@@ -261,3 +261,30 @@ def test_work_list_overflow_paths(F, size):
     assert np.array_equal(fid.cpu().numpy(), ofid), "face ids differ at %d pixels" % (fid.cpu().numpy() != ofid).sum()
     np.testing.assert_allclose(px.cpu().numpy(), opx, rtol=1e-5, atol=1e-6)
     np.testing.assert_allclose(gb.cpu().numpy(), ogb, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("seed", range(16))
+def test_fuzz_vertex_normals(seed):
+    """dirt_vertex_normals (+grad) on random topology against oracle/lighting.py (float64) and, for
+    the gradient, against float64 autograd of the reference's formula."""
+    import torch
+    from dirt_b200 import lighting
+    from oracle import lighting as ol
+    from test_lighting import _torch_reference
+    rng = np.random.RandomState(15000 + seed)
+    Bn, V, D = int(rng.randint(1, 4)), int(rng.randint(3, 400)), int(rng.choice([3, 4]))
+    F = int(rng.randint(1, 4 * V))
+    v = rng.randn(Bn, V, D).astype(np.float32)
+    f = np.stack([rng.permutation(V)[:3] for _ in range(F)]).astype(np.int32)            # three distinct corners
+    vt = torch.tensor(v, device="cuda", requires_grad=True)
+    ft = torch.tensor(f, device="cuda")
+    out = lighting.vertex_normals(vt, ft)
+    np.testing.assert_allclose(out.detach().cpu().numpy(), ol.vertex_normals(v[..., :3], f), atol=5e-6)
+    g = torch.tensor(rng.randn(Bn, V, 3).astype(np.float32), device="cuda")
+    out.backward(g)
+    v64 = torch.tensor(v, dtype=torch.float64, device="cuda", requires_grad=True)
+    _torch_reference(v64, ft, True).backward(g.double())
+    exp, got = v64.grad.cpu().numpy(), vt.grad.cpu().numpy()
+    assert np.abs(got[..., :3] - exp[..., :3]).max() <= 2e-4 * np.abs(exp).max()
+    if D == 4:
+        assert not got[..., 3].any()
