@@ -112,3 +112,51 @@ def test_full_size_c5_shared_height_field():
                                 t["vertices"][b:b + 1], t["vertex_colors"], t["faces"])
     assert torch.equal(f1[0], fid[b]) and torch.equal(p1[0], px[b])
     _check_against_oracle(sc, px, fid, gb, g, gv, None if shared_c else gc, gbg, elements=(1,), shared=True)
+
+
+def test_offsets_beyond_2_31_elements():
+    """B=6 frames of 16384 x 8192 x 3: 2.4e9 pixel values (> 2^31 elements, byte offsets > 2^33).  Every
+    element draws a pixel-aligned rectangle (two triangles) of its own constant colour, so the exact
+    result is known in closed form: coverage = the rectangle, once (shared diagonal), colour exact,
+    background elsewhere; grad_background = grad_pixels outside, 0 inside; the colour gradient of
+    the four corners sums to the sum of grad_pixels over the rectangle."""
+    import torch
+    from dirt_b200 import rasterise_ops as ops
+    B, H, W, C = 6, 16384, 8192, 3
+    free, _ = torch.cuda.mem_get_info()
+    if free < 90 * 2 ** 30:
+        pytest.skip("needs ~70 GB of device memory")
+    rects = [(128 * (b + 1), 256 * (b + 1), W - 64 * (b + 3), H - 512 * (b + 1)) for b in range(B)]     # x0, y0 (from bottom), x1, y1
+    v = np.zeros((B, 4, 4), np.float32)
+    for b, (x0, y0, x1, y1) in enumerate(rects):
+        corners = [(x0, y0), (x1, y0), (x1, y1), (x0, y1)]
+        v[b, :, 0] = [cx * 2.0 / W - 1.0 for cx, _ in corners]
+        v[b, :, 1] = [cy * 2.0 / H - 1.0 for _, cy in corners]
+        v[b, :, 2] = 0.1 * b - 0.3
+        v[b, :, 3] = 1.0
+    cols = np.stack([np.full((4, C), 0.25 + 0.125 * b, np.float32) for b in range(B)])
+    faces = np.tile(np.array([[0, 1, 2], [0, 2, 3]], np.int32), (B, 1, 1))
+    bg = torch.rand(1, H, W, C, device="cuda")
+    px, fid, gb = ops.forward_raw(bg, torch.from_numpy(v).cuda(), torch.from_numpy(cols).cuda(), torch.from_numpy(faces).cuda())
+    torch.cuda.synchronize()
+    g = torch.empty(B, H, W, C, device="cuda").normal_(generator=torch.Generator(device="cuda").manual_seed(0))
+    gv, gc, gbg = ops.backward_raw(torch.from_numpy(faces).cuda(), px, g, fid, gb, 4)
+    torch.cuda.synchronize()
+    for b, (x0, y0, x1, y1) in enumerate(rects):
+        r0, r1 = H - y1, H - y0                       # tensor rows run downwards
+        inside = torch.zeros(H, W, dtype=torch.bool, device="cuda")
+        inside[r0:r1, x0:x1] = True
+        assert torch.equal(fid[b] >= 0, inside), "coverage of element %d" % b
+        assert int((fid[b][r0:r1, x0:x1] > 1).sum()) == 0
+        assert bool((px[b][r0:r1, x0:x1] == 0.25 + 0.125 * b).all())
+        assert torch.equal(torch.where(inside[..., None], torch.zeros((), device="cuda"), px[b]),
+                           torch.where(inside[..., None], torch.zeros((), device="cuda"), bg[0]))
+        assert torch.equal(gbg[b], torch.where(inside[..., None], torch.zeros((), device="cuda"), g[b]))
+        want = g[b][r0:r1, x0:x1].double().sum(dim=(0, 1))
+        scale = g[b][r0:r1, x0:x1].double().abs().sum(dim=(0, 1))
+        assert ((gc[b].double().sum(0) - want).abs() / scale).max().item() < 1e-5
+        del inside
+    assert torch.isfinite(gv).all()
+    del px, fid, gb, g, gv, gc, gbg, bg
+    ops.release_workspaces()
+    torch.cuda.empty_cache()
