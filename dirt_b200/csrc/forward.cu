@@ -191,6 +191,94 @@ __global__ void __launch_bounds__(kTileThreads) k_tile_raster(FwdParams p)
     }
 }
 
+// Small meshes (at most kSmallMeshFaces faces per element: the reference's own samples -- a quad, a
+// cube -- and the full-screen quads of the scene ops): no key clear, no setup pass, no binning.
+// blockIdx.y walks the batch; a CTA sets up every face of its element once (clipped faces as their
+// fan triangles) into shared memory, then walks 16x16 tiles (listing per tile the triangles whose box
+// touches it), thread = pixel, the running minimum in a register, and stores the key of EVERY pixel -- so the launch also stands in for the clear.
+// Same set-up, coverage and depth functions as the other paths: same keys.
+#ifndef KSMALLF
+#define KSMALLF 32
+#endif
+constexpr int kSmallMeshFaces = KSMALLF;
+__global__ void __launch_bounds__(kTileThreads) k_small_raster(FwdParams p)
+{
+    __shared__ TriSetup s_tri[3 * kSmallMeshFaces];
+    __shared__ uint32_t s_face[3 * kSmallMeshFaces];
+    __shared__ uint8_t s_list[3 * kSmallMeshFaces];
+    __shared__ int s_n, s_m;
+    const int tiles = p.tiles_x * p.tiles_y;
+    for (int b = blockIdx.y; b < p.B; b += gridDim.y) {
+        if (threadIdx.x == 0) s_n = 0;
+        __syncthreads();
+        if ((int)threadIdx.x < p.F) {
+            const int f = threadIdx.x;
+            const int32_t *fp = p.faces + (int64_t)b * p.faces_bs + 3 * (int64_t)f;
+            const int i0 = __ldg(fp), i1 = __ldg(fp + 1), i2 = __ldg(fp + 2);
+            if ((unsigned)i0 < (unsigned)p.V && (unsigned)i1 < (unsigned)p.V && (unsigned)i2 < (unsigned)p.V) {
+                const int4 *pp = proj_ptr(p, b);
+                TriSetup t;
+                bool slow;
+                if (setup_from_proj(__ldg(pp + i0), __ldg(pp + i1), __ldg(pp + i2), p.W, p.H, t, slow)) {
+                    const int slot = atomicAdd(&s_n, 1);
+                    s_tri[slot] = t;
+                    s_face[slot] = (uint32_t)f;
+                } else if (slow) {
+                    const float4 *vp = vertex_ptr(p.vertices, p.vertices_bs, b);
+                    const float4 va = __ldg(vp + i0), vb = __ldg(vp + i1), vc = __ldg(vp + i2);
+                    if (classify_face(va, vb, vc) == 2) {
+                        ClipVert poly[6];
+                        const int n = clip_face(va, vb, vc, poly);
+                        for (int s = 1; s + 1 < n; ++s) {
+                            if (!setup_fan(poly, s, p.W, p.H, t)) continue;
+                            const int slot = atomicAdd(&s_n, 1);
+                            s_tri[slot] = t;
+                            s_face[slot] = (uint32_t)f;
+                        }
+                    }
+                }
+            }
+        }
+        __syncthreads();
+        const int n = s_n;
+        unsigned long long *kb = p.keys + (size_t)b * p.H * p.W;
+        // more than a handful of triangles: each tile first lists the ones whose box touches it
+        const bool cull = n > 4;
+        for (int tl = blockIdx.x; tl < tiles; tl += gridDim.x) {
+            const int ty = tl / p.tiles_x, tx = tl - ty * p.tiles_x;
+            const int px = tx * kTile + (threadIdx.x & (kTile - 1)), py = ty * kTile + (threadIdx.x >> 4);
+            int m = n;
+            if (cull) {
+                if (threadIdx.x == 0) s_m = 0;
+                __syncthreads();
+                if ((int)threadIdx.x < n) {
+                    const TriSetup &t = s_tri[threadIdx.x];
+                    if (t.xmax >= tx * kTile && t.xmin < (tx + 1) * kTile && t.ymax >= ty * kTile && t.ymin < (ty + 1) * kTile)
+                        s_list[atomicAdd(&s_m, 1)] = (uint8_t)threadIdx.x;
+                }
+                __syncthreads();
+                m = s_m;
+            }
+            if (px < p.W && py < p.H) {
+                unsigned long long best = kKeyEmpty;
+                for (int k = 0; k < m; ++k) {
+                    const int j = cull ? s_list[k] : k;
+                    const TriSetup &t = s_tri[j];
+                    if (px < t.xmin || px > t.xmax || py < t.ymin || py > t.ymax) continue;
+                    long long e0, e1, e2;
+                    edge_values(t, px, py, e0, e1, e2);
+                    if (!covered(t, e0, e1, e2)) continue;
+                    unsigned long long key;
+                    if (depth_key(sample_depth(t, px, py), s_face[j], key)) best = min(best, key);
+                }
+                kb[(size_t)(p.H - 1 - py) * p.W + px] = best;
+            }
+            if (cull) __syncthreads();      // the list is about to be rewritten
+        }
+        __syncthreads();        // the staged triangles are about to be replaced
+    }
+}
+
 // Barycentrics of pixel (px, py) on a face that went through the clipper (rare): finds the
 // fan triangle whose fragment won the pixel and folds the fan weights back onto the face's own
 // corners.  Normally exactly one fan triangle covers the pixel; when clipped corners land beyond
@@ -346,11 +434,39 @@ static inline int grid_for(long long work, int block, int sm_count, int waves)
     return (int)g;
 }
 
+static cudaError_t launch_resolve(const FwdParams &p, cudaStream_t stream, uint64_t *launches, StageTimer &tm)
+{
+    const dim3 g((unsigned)(((long long)p.H * p.W + 256 * kResolvePix - 1) / (256 * kResolvePix)), (unsigned)(p.B < 65535 ? p.B : 65535));
+    tm.begin(kStageResolve, stream);
+    switch (p.C) {
+        case 1: k_resolve<1><<<g, 256, 0, stream>>>(p); break;
+        case 3: k_resolve<3><<<g, 256, 0, stream>>>(p); break;
+        default: k_resolve<0><<<g, 256, 0, stream>>>(p); break;
+    }
+    tm.end(kStageResolve, stream);
+    *launches += 1;
+    return cudaGetLastError();
+}
+
 cudaError_t launch_forward(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_t *launches, StageTimer &tm)
 {
     cudaError_t e;
     const size_t npix_total = (size_t)p.B * p.H * p.W;
     const size_t ntiles = (size_t)p.B * p.tiles_x * p.tiles_y;
+    if (p.F > 0 && p.F <= kSmallMeshFaces) {
+        // small meshes: project, one raster launch that writes every key, resolve
+        launch_project(p, sm_count, stream, tm);
+        const int tiles = p.tiles_x * p.tiles_y;
+        const int gy = p.B < 65535 ? p.B : 65535;
+        int gx = (sm_count * 8 + gy - 1) / gy;
+        if (gx > tiles) gx = tiles;
+        if (gx < 1) gx = 1;
+        tm.begin(kStageTileRaster, stream);
+        k_small_raster<<<dim3((unsigned)gx, (unsigned)gy), kTileThreads, 0, stream>>>(p);
+        tm.end(kStageTileRaster, stream);
+        *launches += 2;
+        return launch_resolve(p, stream, launches, tm);
+    }
     // S0: keys := EMPTY; counters, tile_count, tile_cursor := 0 (contiguous in the workspace)
     tm.begin(kStageClear, stream);
     if ((e = cudaMemsetAsync(p.keys, 0xFF, npix_total * sizeof(unsigned long long), stream)) != cudaSuccess) return e;
@@ -373,16 +489,7 @@ cudaError_t launch_forward(const FwdParams &p, int sm_count, cudaStream_t stream
         tm.end(kStageTileRaster, stream);
         *launches += 5;        // k_project is counted here, the setup launches in launch_setup
     }
-    const dim3 g((unsigned)(((long long)p.H * p.W + 256 * kResolvePix - 1) / (256 * kResolvePix)), (unsigned)(p.B < 65535 ? p.B : 65535));
-    tm.begin(kStageResolve, stream);
-    switch (p.C) {
-        case 1: k_resolve<1><<<g, 256, 0, stream>>>(p); break;
-        case 3: k_resolve<3><<<g, 256, 0, stream>>>(p); break;
-        default: k_resolve<0><<<g, 256, 0, stream>>>(p); break;
-    }
-    tm.end(kStageResolve, stream);
-    *launches += 1;
-    return cudaGetLastError();
+    return launch_resolve(p, stream, launches, tm);
 }
 
 }  // namespace dirt

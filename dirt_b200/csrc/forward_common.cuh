@@ -129,6 +129,7 @@ __device__ inline bool setup_from_ref(const FwdParams &p, int b, uint32_t ref, T
     return setup_fan(poly, (int)fan, p.W, p.H, t);
 }
 
+void launch_project(const FwdParams &p, int sm_count, cudaStream_t stream, StageTimer &tm);
 void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_t *launches, StageTimer &tm);
 
 }  // namespace dirt

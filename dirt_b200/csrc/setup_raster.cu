@@ -374,9 +374,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
     }
 }
 
-void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_t *launches, StageTimer &tm)
+void launch_project(const FwdParams &p, int sm_count, cudaStream_t stream, StageTimer &tm)
 {
-    const long long nfaces = (long long)p.B * p.F;
     const int nbatch = p.vertices_bs == 0 ? 1 : p.B;
     const long long nverts = (long long)nbatch * p.V;
     tm.begin(kStageProject, stream);
@@ -387,6 +386,12 @@ void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_
         k_project<<<(int)gv, 256, 0, stream>>>(p, nbatch);
     }
     tm.end(kStageProject, stream);
+}
+
+void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_t *launches, StageTimer &tm)
+{
+    const long long nfaces = (long long)p.B * p.F;
+    launch_project(p, sm_count, stream, tm);
     long long g = (nfaces + kWarpsPerCta * 32 - 1) / (kWarpsPerCta * 32);
     const long long cap = (long long)sm_count * kCtasPerSm;        // resident CTAs: work is claimed dynamically
     if (g > cap) g = cap;
