@@ -400,10 +400,9 @@ __global__ void __launch_bounds__(256, KRES_CTAS) k_resolve(FwdParams p)
                 screen_bary(t, e0, e1, e2, l0, l1, l2);
             }
             perspective_weights(t, l0, l1, l2, B0, B1, b2, wc);
-        } else {
-            const FwdParams pc = p;      // keeps the kernel parameter block itself out of local memory
-            resolve_clipped(pc, b, i0, i1, i2, px, py, (uint32_t)(key >> 32), B0, B1, wc);
         }
+        // else: a corner went through the clipper (rare) -- k_resolve_clipped rewrites this pixel; calling
+        // the clip path from here costs the whole kernel registers and a stack frame
         const float *cp = p.vertex_colors + (int64_t)b * p.vertex_colors_bs;
         const float *c0 = cp + (int64_t)i0 * CC, *c1 = cp + (int64_t)i1 * CC, *c2 = cp + (int64_t)i2 * CC;
         for (int c = 0; c < CC; ++c) {
@@ -419,6 +418,44 @@ __global__ void __launch_bounds__(256, KRES_CTAS) k_resolve(FwdParams p)
             reinterpret_cast<float4 *>(p.gbuffer)[i] = make_float4(B0, B1, wc, zq);
         }
     }
+    }
+}
+
+// S4b: the pixels won by faces that went through the clipper.  Does nothing unless k_project met a
+// vertex that needs the clip path (counters[kCtrSlow]); then one thread per pixel re-derives the
+// weights through the clipped fan and rewrites colour and G-buffer with the formulas of k_resolve.
+__global__ void __launch_bounds__(256) k_resolve_clipped(FwdParams p)
+{
+    if (p.counters[kCtrSlow] == 0u) return;
+    const FwdParams pc = p;      // resolve_clipped takes a reference: keep the parameter block itself out of local memory
+    const int npix = pc.H * pc.W, CC = pc.C;
+    for (int b = blockIdx.y; b < pc.B; b += gridDim.y) {
+        const unsigned long long *kb = pc.keys + (size_t)b * npix;
+        const int4 *pp = proj_ptr(pc, b);
+        for (int o = blockIdx.x * blockDim.x + threadIdx.x; o < npix; o += gridDim.x * blockDim.x) {
+            const unsigned long long key = kb[o];
+            if (key == kKeyEmpty) continue;
+            const int f = (int)(uint32_t)(key & 0xFFFFFFFFull);
+            const int32_t *fp = pc.faces + (int64_t)b * pc.faces_bs + 3 * (int64_t)f;
+            const int i0 = __ldg(fp), i1 = __ldg(fp + 1), i2 = __ldg(fp + 2);
+            if (__ldg(pp + i0).x != kProjSlow && __ldg(pp + i1).x != kProjSlow && __ldg(pp + i2).x != kProjSlow) continue;
+            const int row = o / pc.W, px = o - row * pc.W, py = pc.H - 1 - row;
+            float B0 = 0.f, B1 = 0.f, wc = 1.f;
+            resolve_clipped(pc, b, i0, i1, i2, px, py, (uint32_t)(key >> 32), B0, B1, wc);
+            const size_t i = (size_t)b * npix + o;
+            float *out = pc.pixels + i * CC;
+            const float *cp = pc.vertex_colors + (int64_t)b * pc.vertex_colors_bs;
+            const float *c0 = cp + (int64_t)i0 * CC, *c1 = cp + (int64_t)i1 * CC, *c2 = cp + (int64_t)i2 * CC;
+            for (int c = 0; c < CC; ++c) {
+                const float k2 = __ldg(c2 + c);
+                const float t0 = fsub(__ldg(c0 + c), k2), t1 = fsub(__ldg(c1 + c), k2);
+                out[c] = fadd(fadd(k2, fmul(B0, t0)), fmul(B1, t1));
+            }
+            if (pc.face_id) {
+                const float zq = fmul(__uint2float_rn((uint32_t)(key >> 32)), kDepthScaleInv);
+                reinterpret_cast<float4 *>(pc.gbuffer)[i] = make_float4(B0, B1, wc, zq);
+            }
+        }
     }
 }
 
@@ -443,8 +480,13 @@ static cudaError_t launch_resolve(const FwdParams &p, cudaStream_t stream, uint6
         case 3: k_resolve<3><<<g, 256, 0, stream>>>(p); break;
         default: k_resolve<0><<<g, 256, 0, stream>>>(p); break;
     }
+    {
+        long long gx = ((long long)p.H * p.W + 255) / 256;
+        if (gx > 1024) gx = 1024;
+        k_resolve_clipped<<<dim3((unsigned)gx, (unsigned)(p.B < 64 ? p.B : 64)), 256, 0, stream>>>(p);
+    }
     tm.end(kStageResolve, stream);
-    *launches += 1;
+    *launches += 2;
     return cudaGetLastError();
 }
 
@@ -455,6 +497,7 @@ cudaError_t launch_forward(const FwdParams &p, int sm_count, cudaStream_t stream
     const size_t ntiles = (size_t)p.B * p.tiles_x * p.tiles_y;
     if (p.F > 0 && p.F <= kSmallMeshFaces) {
         // small meshes: project, one raster launch that writes every key, resolve
+        if ((e = cudaMemsetAsync(p.counters, 0, kCtrCount * sizeof(uint32_t), stream)) != cudaSuccess) return e;
         launch_project(p, sm_count, stream, tm);
         const int tiles = p.tiles_x * p.tiles_y;
         const int gy = p.B < 65535 ? p.B : 65535;

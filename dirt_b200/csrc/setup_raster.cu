@@ -62,6 +62,7 @@ __global__ void __launch_bounds__(256) k_project(FwdParams p, int nbatch)
             if (project_corner(c.x, c.y, c.z, c.w, halfW, halfH, X, Y, zw, rw))
                 r = make_int4(X, Y, __float_as_int(zw), __float_as_int(rw));
         }
+        if (r.x == kProjSlow) p.counters[kCtrSlow] = 1u;      // k_resolve_clipped has work (benign race: everyone writes 1)
         const_cast<int4 *>(p.proj)[(int64_t)b * p.V + v] = r;
     }
 }

@@ -8,6 +8,7 @@ O=gpurun_out
 python -m pytest tests -m gpu -x -q > $O/final_tests.log 2>&1; tail -2 $O/final_tests.log
 python bench.py > $O/final_bench.json 2> $O/final_bench.err || exit 1
 python tools/stages.py headline c4 c3 c2 c1 > $O/final_stages.txt 2>&1 || exit 1
+python tools/scene_bench.py > $O/final_scene_bench.json 2> $O/final_scene_bench.err
 python bench.py --workload c5 --no-cpu-baseline > $O/final_bench_c5.json 2> $O/final_bench_c5.err
 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > /dev/null 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/final_launches.csv \
