@@ -429,7 +429,7 @@ __global__ void __launch_bounds__(256) k_resolve_clipped(FwdParams p)
     if (p.counters[kCtrSlow] == 0u) return;
     const FwdParams pc = p;      // resolve_clipped takes a reference: keep the parameter block itself out of local memory
     const int npix = pc.H * pc.W, CC = pc.C;
-    for (int b = blockIdx.y; b < pc.B; b += gridDim.y) {
+    for (int b = 0; b < pc.B; ++b) {
         const unsigned long long *kb = pc.keys + (size_t)b * npix;
         const int4 *pp = proj_ptr(pc, b);
         for (int o = blockIdx.x * blockDim.x + threadIdx.x; o < npix; o += gridDim.x * blockDim.x) {
@@ -481,9 +481,11 @@ static cudaError_t launch_resolve(const FwdParams &p, cudaStream_t stream, uint6
         default: k_resolve<0><<<g, 256, 0, stream>>>(p); break;
     }
     {
+        // a small grid: in the usual case every CTA returns at once, and a launch of many thousands of
+        // empty CTAs would cost more than the few microseconds of the launch itself
         long long gx = ((long long)p.H * p.W + 255) / 256;
-        if (gx > 1024) gx = 1024;
-        k_resolve_clipped<<<dim3((unsigned)gx, (unsigned)(p.B < 64 ? p.B : 64)), 256, 0, stream>>>(p);
+        if (gx > 592) gx = 592;
+        k_resolve_clipped<<<(unsigned)gx, 256, 0, stream>>>(p);
     }
     tm.end(kStageResolve, stream);
     *launches += 2;
