@@ -139,6 +139,12 @@ int current_sm_count(int *out)
 }  // namespace
 
 namespace dirt { void note_launches(uint64_t n) { g_launches += n; } }
+namespace dirt {
+int set_error(int status, const char *what, cudaError_t e)
+{
+    return e == cudaSuccess ? fail(status, "%s", what) : fail(status, "%s: %s", what, cudaGetErrorString(e));
+}
+}
 
 extern "C" {
 

@@ -7,6 +7,8 @@
 #include "../../include/dirt_b200.h"
 #include <cuda_runtime.h>
 
+namespace dirt { int set_error(int status, const char *what, cudaError_t e); }    // capi.cu
+
 namespace {
 
 struct Arena {
@@ -35,7 +37,16 @@ template <typename T> T *arena_take(Arena &a, size_t count)
 }
 inline size_t extent(int64_t stride, int64_t block, int batch) { return (size_t)(stride == 0 ? block : stride * (int64_t)(batch - 1) + block); }
 
-#define HOST_TRY(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { cudaStreamDestroy(st); return DIRT_STATUS_CUDA_ERROR; } } while (0)
+#define HOST_TRY(expr) do { cudaError_t e_ = (expr); if (e_ != cudaSuccess) { cudaStreamDestroy(st); return dirt::set_error(DIRT_STATUS_CUDA_ERROR, "host staging copy", e_); } } while (0)
+
+// the current device, or a recorded error: a process without a usable GPU is told so in words
+int current_device(int *dev)
+{
+    const cudaError_t e = cudaGetDevice(dev);
+    if (e != cudaSuccess) return dirt::set_error(DIRT_STATUS_CUDA_ERROR, "no usable CUDA device (there is no CPU path)", e);
+    if (*dev < 0 || *dev >= 64) return dirt::set_error(DIRT_STATUS_CUDA_ERROR, "device ordinal out of range", cudaSuccess);
+    return DIRT_STATUS_OK;
+}
 
 }  // namespace
 
@@ -43,13 +54,13 @@ extern "C" {
 
 int dirt_rasterise_forward_host(const DirtForwardArgs *h)
 {
-    if (!h) return DIRT_STATUS_INVALID_ARGUMENT;
+    if (!h) return dirt::set_error(DIRT_STATUS_INVALID_ARGUMENT, "null arguments", cudaSuccess);
     const DirtShape &s = h->shape;
     const size_t ws_bytes = dirt_workspace_bytes(&s);
-    if (ws_bytes == 0) return DIRT_STATUS_INVALID_ARGUMENT;
+    if (ws_bytes == 0) return dirt::set_error(DIRT_STATUS_INVALID_ARGUMENT, "invalid shape", cudaSuccess);
     if (s.batch == 0) return DIRT_STATUS_OK;
     int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DIRT_STATUS_CUDA_ERROR;
+    if (int rc_ = current_device(&dev)) return rc_;
     std::lock_guard<std::mutex> lock(g_mu);
     Arena &A = g_arena[dev];
     const size_t npix = (size_t)s.batch * s.height * s.width;
@@ -60,9 +71,9 @@ int dirt_rasterise_forward_host(const DirtForwardArgs *h)
     const bool aux = h->face_id != nullptr;
     size_t need = pad(ws_bytes) + pad(n_bg * 4) + pad(n_v * 4) + pad(n_c * 4) + pad(n_f * 4) + pad(npix * s.channels * 4) +
                   (aux ? pad(npix * 4) + pad(npix * 16) : 0);
-    if (arena_reserve(A, need) != cudaSuccess) return DIRT_STATUS_CUDA_ERROR;
+    if (cudaError_t e_ = arena_reserve(A, need)) return dirt::set_error(DIRT_STATUS_CUDA_ERROR, "device staging allocation", e_);
     cudaStream_t st;
-    if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) return DIRT_STATUS_CUDA_ERROR;
+    if (cudaError_t e_ = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking)) return dirt::set_error(DIRT_STATUS_CUDA_ERROR, "stream creation", e_);
     DirtForwardArgs d = *h;
     d.workspace = arena_take<char>(A, ws_bytes); d.workspace_bytes = ws_bytes;
     float *bg = arena_take<float>(A, n_bg), *v = arena_take<float>(A, n_v), *c = arena_take<float>(A, n_c);
@@ -88,12 +99,12 @@ int dirt_rasterise_forward_host(const DirtForwardArgs *h)
 
 int dirt_rasterise_backward_host(const DirtBackwardArgs *h)
 {
-    if (!h) return DIRT_STATUS_INVALID_ARGUMENT;
+    if (!h) return dirt::set_error(DIRT_STATUS_INVALID_ARGUMENT, "null arguments", cudaSuccess);
     const DirtShape &s = h->shape;
     if (s.batch == 0) return DIRT_STATUS_OK;
-    if (s.batch < 0 || s.height <= 0 || s.width <= 0 || s.channels <= 0) return DIRT_STATUS_INVALID_ARGUMENT;
+    if (s.batch < 0 || s.height <= 0 || s.width <= 0 || s.channels <= 0) return dirt::set_error(DIRT_STATUS_INVALID_ARGUMENT, "invalid shape", cudaSuccess);
     int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DIRT_STATUS_CUDA_ERROR;
+    if (int rc_ = current_device(&dev)) return rc_;
     std::lock_guard<std::mutex> lock(g_mu);
     Arena &A = g_arena[dev];
     const size_t npix = (size_t)s.batch * s.height * s.width, nimg = npix * s.channels;
@@ -101,9 +112,9 @@ int dirt_rasterise_backward_host(const DirtBackwardArgs *h)
     const size_t n_gv = extent(h->grad_vertices_bstride, (int64_t)s.vertex_count * 4, s.batch);
     const size_t n_gc = extent(h->grad_vertex_colors_bstride, (int64_t)s.vertex_count * s.channels, s.batch);
     size_t need = pad(n_f * 4) + 3 * pad(nimg * 4) + pad(npix * 4) + pad(npix * 16) + pad(n_gv * 4) + pad(n_gc * 4);
-    if (arena_reserve(A, need) != cudaSuccess) return DIRT_STATUS_CUDA_ERROR;
+    if (cudaError_t e_ = arena_reserve(A, need)) return dirt::set_error(DIRT_STATUS_CUDA_ERROR, "device staging allocation", e_);
     cudaStream_t st;
-    if (cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking) != cudaSuccess) return DIRT_STATUS_CUDA_ERROR;
+    if (cudaError_t e_ = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking)) return dirt::set_error(DIRT_STATUS_CUDA_ERROR, "stream creation", e_);
     DirtBackwardArgs d = *h;
     int32_t *f = arena_take<int32_t>(A, n_f);
     float *px = arena_take<float>(A, nimg), *g = arena_take<float>(A, nimg), *gbg = arena_take<float>(A, nimg);
@@ -130,7 +141,7 @@ int dirt_rasterise_backward_host(const DirtBackwardArgs *h)
 int dirt_release_host_staging(void)
 {
     int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return DIRT_STATUS_CUDA_ERROR;
+    if (int rc_ = current_device(&dev)) return rc_;
     std::lock_guard<std::mutex> lock(g_mu);
     Arena &A = g_arena[dev];
     if (A.base) cudaFree(A.base);
