@@ -111,3 +111,24 @@ def test_lattice_soup_matches_the_oracle_bit_for_bit(H, W, F, sub):
     assert np.array_equal(gbg.cpu().numpy(), ogbg)
     for a, b in ((gv.cpu().numpy(), ogv), (gc.cpu().numpy(), ogc)):
         assert np.abs(a - b).max() <= 1e-4 * max(np.abs(b).max(), 1e-12)
+
+
+@settings(max_examples=80, deadline=None)
+@given(point, point, point, st.integers(-6, 6), st.integers(-6, 6))
+def test_coverage_moves_with_the_triangle_by_whole_pixels(p0, p1, p2, kx, ky):
+    """Shifting every corner by whole pixels shifts the covered set by the same pixels (where both
+    stay inside the frame): the fill rule depends on sub-pixel position only, never on where in the
+    frame a sample lies."""
+    assume(_cross(p0, p1, p2) != 0)
+    pts = np.array([p0, p1, p2])
+    a = _coverage(_clip(pts), [[0, 1, 2]]) >= 0
+    b = _coverage(_clip(pts + np.array([kx, ky]) * SUB), [[0, 1, 2]]) >= 0
+    # rows run downwards: +ky pixels up is -ky rows
+    ys, xs = np.nonzero(a)
+    ys2, xs2 = ys - ky, xs + kx
+    keep = (ys2 >= 0) & (ys2 < N) & (xs2 >= 0) & (xs2 < N)
+    assert b[ys2[keep], xs2[keep]].all(), "a covered pixel was lost by the shift"
+    ys, xs = np.nonzero(b)
+    ys0, xs0 = ys + ky, xs - kx
+    keep = (ys0 >= 0) & (ys0 < N) & (xs0 >= 0) & (xs0 < N)
+    assert a[ys0[keep], xs0[keep]].all(), "the shift covered a pixel it should not"
