@@ -35,6 +35,10 @@ constexpr int kWarpsPerCta = 8;
 #ifndef KPRE0
 #define KPRE0 0
 #endif
+#ifndef KHIZ8
+#define KHIZ8 0      // > 0 (experimental, unmeasured): faces that pass the pyramid test get a second, warp-cooperative
+                     // test against every 8-px tile of their box when it has at most KHIZ8 of them (tools/sim_cull.py)
+#endif
 #ifndef KLDCG
 #define KLDCG 0      // 1: the depth pre-load bypasses L1 (sees the reductions of this launch)
 #endif
@@ -236,13 +240,18 @@ static __device__ __noinline__ void setup_clipped(const FwdParams &p, int b, int
 // True when no fragment of t can win a pixel: its smallest possible depth is beyond the
 // hierarchical depth buffer in every tile the bounding box touches.  The plane depth is monotone
 // in dx and in dy under round-to-nearest, so its minimum over the box is taken at a corner.
-__device__ __forceinline__ bool hidden_by_hiz(const FwdParams &p, int b, const TriSetup &t)
+__device__ __forceinline__ uint32_t hiz_dmin(const TriSetup &t)
 {
     const float dx = t.dzdx >= 0.0f ? 0.0f : __int2float_rn(t.xmax - t.xmin);
     const float dy = t.dzdy >= 0.0f ? 0.0f : __int2float_rn(t.ymax - t.ymin);
     float zw = fadd(fadd(t.zref, fmul(t.dzdx, dx)), fmul(t.dzdy, dy));
     zw = fminf(fmaxf(zw, 0.0f), 1.0f);
-    const uint32_t dmin = __float2uint_rz(fadd(fmul(zw, 16777215.0f), 0.5f));
+    return __float2uint_rz(fadd(fmul(zw, 16777215.0f), 0.5f));
+}
+
+__device__ __forceinline__ bool hidden_by_hiz(const FwdParams &p, int b, const TriSetup &t)
+{
+    const uint32_t dmin = hiz_dmin(t);
     // the level at which the box spans at most 3 x 3 tiles: nine independent loads
     const int ext = max(t.xmax - t.xmin, t.ymax - t.ymin);
     int l = 0;
@@ -305,6 +314,10 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
         // ---- setup: one face per lane -------------------------------------------------------
         int nlines = 0;                  // > 0: this lane's face is line-sampled by the warp
         uint32_t dims = 0;
+#if KHIZ8
+        uint32_t hz_box = 0, hz_dmin = 0;     // box in 8-px tiles: tx0 | ty0 << 11 | (nx - 1) << 22 | (ny - 1) << 27; 0 = no second test
+        int hz_b = 0;
+#endif
         if (i < total) {
             const long long flat = ordered ? (long long)p.order[first_entry + i] : i;
             const int b = (int)(flat / p.F), f = (int)(flat - (long long)b * p.F);
@@ -327,6 +340,17 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
                     {   // few-but-fat triangles are better off pixel-parallel in the tile path
                         nlines = max(t.xmax - t.xmin, t.ymax - t.ymin) + 1;     // the longer side of the bounding box
                         dims = write_record(recs + lane * kRecWords, t, (uint32_t)f, (uint32_t)b, p.H, p.W);
+#if KHIZ8
+                        if (use_hiz && ((nlines - 1) >> kHizLog2) > 1) {          // the first test ran above the 8-px level
+                            const int tx0 = t.xmin >> kHizLog2, ty0 = t.ymin >> kHizLog2;
+                            const int nx = (t.xmax >> kHizLog2) - tx0 + 1, ny = (t.ymax >> kHizLog2) - ty0 + 1;
+                            if (nx <= 32 && ny <= 32 && nx * ny <= KHIZ8 && tx0 < 2048 && ty0 < 2048) {
+                                hz_box = (uint32_t)tx0 | (uint32_t)ty0 << 11 | (uint32_t)(nx - 1) << 22 | (uint32_t)(ny - 1) << 27 | 0u;
+                                hz_dmin = hiz_dmin(t) | 0x80000000u;          // bit 31: "test me" (a box at tile 0,0 of 1x1 packs to 0)
+                                hz_b = b;
+                            }
+                        }
+#endif
                     } else
                         push_big(t, b, (uint32_t)f, 0u, p);
                 } else if (slow) {
@@ -338,6 +362,29 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
             }
         }
         // the r-th line-sampled face of the batch, in lane order, is the face of lane owner_lane[r]
+#if KHIZ8
+        if (use_hiz) {
+            // second test, the whole warp on one face at a time: every 8-px tile of its box
+            unsigned todo = __ballot_sync(kFullMask, (hz_dmin >> 31) != 0u);
+            const int ntx = (p.W + (1 << kHizLog2) - 1) >> kHizLog2, nty = (p.H + (1 << kHizLog2) - 1) >> kHizLog2;
+            while (todo) {
+                const int src = __ffs(todo) - 1;
+                todo &= todo - 1u;
+                const uint32_t box = __shfl_sync(kFullMask, hz_box, src);
+                const uint32_t dmin = __shfl_sync(kFullMask, hz_dmin, src) & 0x00FFFFFFu;
+                const int bb = __shfl_sync(kFullMask, hz_b, src);
+                const int tx0 = (int)(box & 2047u), ty0 = (int)((box >> 11) & 2047u);
+                const int nx = (int)((box >> 22) & 31u) + 1, n = nx * ((int)(box >> 27) + 1);
+                const uint32_t *hz = p.hiz + p.hiz_off[0] + ((size_t)bb * nty + ty0) * ntx + tx0;
+                bool visible = false;
+                for (int q = lane; q < n; q += 32) {
+                    const int dy = q / nx, dx = q - dy * nx;
+                    visible |= __ldg(hz + dy * ntx + dx) >= dmin;          // equal depth: the face index decides
+                }
+                if (!__any_sync(kFullMask, visible) && lane == src) nlines = 0;      // hidden: its record is never read
+            }
+        }
+#endif
         const bool sampled = nlines > 0;
         const unsigned owners = __ballot_sync(kFullMask, sampled);
         if (sampled) owner_lane[__popc(owners & ((1u << lane) - 1u))] = (uint8_t)lane;
