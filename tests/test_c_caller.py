@@ -33,6 +33,7 @@ def test_c_caller_compiles_links_and_fails_loudly_without_a_gpu(tmp_path):
 
 
 @pytest.mark.gpu
+@pytest.mark.skipif(shutil.which("gcc") is None, reason="no gcc")
 def test_c_caller_renders_the_readme_square(tmp_path):
     exe = _build(tmp_path)
     r = subprocess.run([exe], capture_output=True, text=True)
