@@ -7,10 +7,11 @@ Two kinds of fixture:
                         (README.md:46-70 / README.md:104, tests/multi_gpu_test.py:8-17): inputs
                         and the expected image, written down from the reference text -- these
                         pin the oracle AND the CUDA path to the reference.
-  cylinder.npz, cube.npz, clip.npz
+  cylinder.npz, cube.npz, clip.npz, folded_fan.npz
                         outputs of the oracle (oracle/golden_raster.c) on the reference's
                         deterministic scenes that store no expectation (tests/rasterise_tests.py:
-                        11-89, samples/simple.py:15-74) and on a near-plane-crossing scene.
+                        11-89, samples/simple.py:15-74), on a near-plane-crossing scene and on three faces whose
+                        clipped fans fold over themselves at the guard band (tests/scenes.py).
                         The reference cannot run here (no TensorFlow, no GL), so these are
                         regression pins of the written spec (docs/RASTER_SPEC.md,
                         docs/GRADIENT_SPEC.md), not reference outputs; parity of attribute values
@@ -57,6 +58,7 @@ def main():
     np.savez_compressed(os.path.join(HERE, "cylinder.npz"), **oracle_case(scenes.cylinder(), 0))
     np.savez_compressed(os.path.join(HERE, "cube.npz"), **oracle_case(scenes.cube(B=2, H=64, W=64), 1))
     np.savez_compressed(os.path.join(HERE, "clip.npz"), **oracle_case(scenes.near_crossing(B=1, H=48, W=64), 2))
+    np.savez_compressed(os.path.join(HERE, "folded_fan.npz"), **oracle_case(scenes.folded_fans(), 3))
     np.savez_compressed(os.path.join(HERE, "scenes.npz"), **scene_cases())
     for f in sorted(os.listdir(HERE)):
         if f.endswith(".npz"):

@@ -262,3 +262,25 @@ def hill(B, H, W, C=3, n=708, seed=0):
     sc["world"] = world.astype(np.float32)
     sc["matrices"] = Ms.astype(np.float32)
     return sc
+
+
+# Three faces with a corner behind the eye (w < 0: outside the near AND the far plane).  Clipping leaves
+# polygon corners with w -> 0 whose window positions hit the guard-band clamp, so the fan folds over
+# itself and two of its triangles cover the same pixels (found by tests/test_fuzz_gpu.py, seeds 18 and 23).
+FOLDED_FAN_FACES = [
+    [[-4.520687580108643, -6.046390533447266, -1.3254375457763672, 1.7913875579833984],
+     [0.820976972579956, 0.5507926344871521, 0.3445732891559601, 0.39526867866516113],
+     [0.5961543321609497, 0.04113024100661278, -0.1284199357032776, -0.191458597779274]],
+    [[0.04086809232831001, 0.1765381395816803, -0.10965538769960403, -0.1991819143295288],
+     [0.2568352222442627, 0.22824278473854065, 0.24783971905708313, -0.2613210082054138],
+     [-0.15913863480091095, 0.3746587634086609, -0.5689247250556946, 0.8287256956100464]],
+    [[0.7668004035949707, -0.1253456324338913, -1.4441827535629272, 1.92557692527771],
+     [0.86167973279953, 0.03097062185406685, -1.4628005027770996, 1.9504005908966064],
+     [-0.02990591526031494, 0.011887836270034313, 0.031696148216724396, -0.04226153343915939]],
+]
+
+
+def folded_fans(H=74, W=76, C=3, seed=0):
+    rng = np.random.RandomState(seed)
+    v = np.asarray(FOLDED_FAN_FACES, np.float32).reshape(1, 9, 4)
+    return _pack(rng.uniform(0, 1, (1, H, W, C)), v, rng.uniform(0, 1, (1, 9, C)), np.arange(9).reshape(1, 3, 3))

@@ -10,7 +10,7 @@ import pytest
 from oracle import golden
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-ORACLE_CASES = ["cylinder", "cube", "clip"]
+ORACLE_CASES = ["cylinder", "cube", "clip", "folded_fan"]
 
 
 def _load(name):

@@ -131,17 +131,7 @@ def test_clipped_fans_that_fold_over_themselves_at_the_guard_band():
     """Found by tests/test_fuzz_gpu.py: a corner behind the eye (w < 0, outside near AND far) leaves
     polygon corners with w -> 0 whose window positions are clamped; the fan then overlaps itself
     and the attributes must come from the fan triangle that won the depth test (RASTER_SPEC 2.3)."""
-    faces3 = [
-        [[-4.520687580108643, -6.046390533447266, -1.3254375457763672, 1.7913875579833984],
-         [0.820976972579956, 0.5507926344871521, 0.3445732891559601, 0.39526867866516113],
-         [0.5961543321609497, 0.04113024100661278, -0.1284199357032776, -0.191458597779274]],
-        [[0.04086809232831001, 0.1765381395816803, -0.10965538769960403, -0.1991819143295288],
-         [0.2568352222442627, 0.22824278473854065, 0.24783971905708313, -0.2613210082054138],
-         [-0.15913863480091095, 0.3746587634086609, -0.5689247250556946, 0.8287256956100464]],
-        [[0.7668004035949707, -0.1253456324338913, -1.4441827535629272, 1.92557692527771],
-         [0.86167973279953, 0.03097062185406685, -1.4628005027770996, 1.9504005908966064],
-         [-0.02990591526031494, 0.011887836270034313, 0.031696148216724396, -0.04226153343915939]],
-    ]
+    faces3 = scenes.FOLDED_FAN_FACES
     rng = np.random.RandomState(0)
     for (H, W) in ((74, 76), (36, 92)):
         v = np.asarray(faces3, np.float32).reshape(1, 9, 4)
