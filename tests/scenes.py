@@ -159,6 +159,16 @@ def uv_sphere_mesh(n_lat, n_lon):
 def sphere(B, H, W, C=3, n_lat=224, n_lon=224, fill=0.6, seeds=(1, 2, 3, 4)):
     """Bumpy sphere, random per-element rotation (SURVEY 8(d) c4/headline recipe):
     n_lat = n_lon = 224 gives F = 99,904 ~ 100k faces, V = 49,954."""
+    return sphere_frames(B, H, W, C, n_lat, n_lon, fill, seeds, frame=0)
+
+
+def sphere_frames(B, H, W, C=3, n_lat=224, n_lon=224, fill=0.6, seeds=(1, 2, 3, 4), frame=0, step_deg=0.25, noise_px=0.0,
+                  vertices_only=False):
+    """Frame `frame` of a sequence that starts at sphere(): every element's object turns by a further
+    frame * step_deg degrees about the camera's y axis, and (noise_px > 0) every vertex is displaced by
+    Gaussian noise worth ~noise_px pixels on screen, fresh per frame -- the way an inverse-rendering loop
+    (tests/optimize_sequence.py:293-352) re-renders a scene whose parameters moved a little.  Colours,
+    faces and background are those of frame 0."""
     verts, faces = uv_sphere_mesh(n_lat, n_lon)
     V = len(verts)
     verts = verts * (1 + 0.1 * np.random.RandomState(seeds[0]).randn(V, 1).clip(-2.5, 2.5))
@@ -169,11 +179,16 @@ def sphere(B, H, W, C=3, n_lat=224, n_lon=224, fill=0.6, seeds=(1, 2, 3, 4)):
     near = 0.1
     right = near * (1.0 / np.sqrt(z * z - 1)) / r_ndc
     P = perspective_projection(near, 20., right, H / W)
+    if frame and noise_px > 0:
+        verts = verts + np.random.RandomState(1000 + frame).randn(V, 3) * (noise_px * 2.0 / (W * r_ndc))
     vh = np.concatenate([verts, np.ones((V, 1))], 1)
     vs = np.empty((B, V, 4), np.float32)
+    turn = pad_3x3_to_4x4(rodrigues([0., np.deg2rad(step_deg * frame), 0.]))
     for b in range(B):
-        M = pad_3x3_to_4x4(rodrigues(rr.randn(3))) @ translation([0., 0., -z]) @ P
+        M = pad_3x3_to_4x4(rodrigues(rr.randn(3))) @ turn @ translation([0., 0., -z]) @ P
         vs[b] = vh @ M
+    if vertices_only:
+        return vs
     cols = np.random.RandomState(seeds[2]).uniform(0, 1, size=(B, V, C)).astype(np.float32)
     bg = np.random.RandomState(seeds[3]).uniform(0, 1, size=(B, H, W, C)).astype(np.float32)
     return _pack(bg, vs, cols, np.broadcast_to(faces, (B,) + faces.shape))
