@@ -7,7 +7,11 @@ input.  Prints ONE JSON line (rank 0).  Under torchrun (N > 1) every rank render
 shard (weak scaling, no data-path collective; the `c5` shared-mesh workload adds the NCCL
 allreduce of the vertex gradients).
 
-  value         whole-job Mpix/s, inputs resident in HBM, CUDA events, max over ranks
+  value         whole-job Mpix/s, inputs resident in HBM, CUDA events, max over ranks.  The geometry MOVES
+                between steps (4 pre-uploaded vertex sets, 0.25 degrees apart) and the forward carries
+                its visibility hint from call to call; --static / --no-hint give the round-1 protocol
+  extra         c4 and c5 (with / without / overlapped allreduce) device-resident, and the e2e through
+                the host-buffer C ABI
   e2e           same metric through the public API with pinned HOST inputs: H2D of the step's
                 inputs and D2H of its results inside the timed region
   roofline      dominant kernel: algorithmic bytes per launch / its mean duration (CUDA events
@@ -253,10 +257,60 @@ def bind_to_gpu_numa(index):
         return "skipped: %s" % (str(e)[:80] or type(e).__name__)
 
 
+FRAMES = 4            # vertex sets of the timed loops: the geometry moves between steps
+FRAME_STEP_DEG = 0.25
+
+
+def frame_order(n):
+    """0 1 2 3 2 1 | 0 1 ...: every step renders the neighbour of the frame before it."""
+    return list(range(n)) + list(range(n - 2, 0, -1))
+
+
+def build_frames(wl, B, rank):
+    """Vertex sets 1..FRAMES-1 of the sphere workloads: every element's object turned a further
+    FRAME_STEP_DEG degrees per frame (tests/scenes.py:sphere_frames), the way an inverse-rendering loop
+    re-renders a scene whose parameters moved a little (tests/optimize_sequence.py:293-352)."""
+    import scenes
+    seeds = (1, 2 + 10 * rank, 3 + 10 * rank, 4 + 10 * rank)
+    return [scenes.sphere_frames(B, wl["H"], wl["W"], wl["C"], wl["n_lat"], wl["n_lon"], seeds=seeds, frame=k,
+                                 step_deg=FRAME_STEP_DEG, vertices_only=True) for k in range(1, FRAMES)]
+
+
+def time_steps(step, steps, warmup, barrier, max_over_ranks):
+    """W untimed + K timed calls of step(i) bracketed by barrier + synchronize; returns ms per step (max over ranks)."""
+    import torch
+    for i in range(warmup):
+        step(i)
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for i in range(steps):
+        step(warmup + i)
+    ev1.record()
+    barrier()
+    return max_over_ranks(ev0.elapsed_time(ev1)) / steps
+
+
+def stage_profile(step, nprof):
+    """Per-stage device times per step (CUDA events recorded inside the library around each kernel)."""
+    import torch
+    from dirt_b200 import _lib
+    lib = _lib.load()
+    _lib.check(lib.dirt_profile_reset())
+    _lib.check(lib.dirt_profile_enable(1))
+    for i in range(nprof):
+        step(i)
+        torch.cuda.synchronize()
+        _lib.check(lib.dirt_profile_collect())
+    _lib.check(lib.dirt_profile_enable(0))
+    times = _lib.stage_times()
+    return {k: ms / nprof for k, (ms, n) in times.items()}, {k: n / nprof for k, (ms, n) in times.items()}
+
+
 def run_ours(args, wl, rank, world, local_rank):
     import torch
     import torch.distributed as dist
-    from dirt_b200 import rasterise_ops as ops, _lib
+    from dirt_b200 import rasterise_ops as ops, _lib, sharding
     import dirt_b200
 
     if not torch.cuda.is_available():
@@ -267,32 +321,6 @@ def run_ours(args, wl, rank, world, local_rank):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     lib = _lib.load()
-
-    B, H, W, C = wl["B"], wl["H"], wl["W"], wl["C"]
-    shared = bool(wl.get("shared"))
-    sc = build_scene(wl, B, seed_shift=0 if shared else 10 * rank)     # a shared mesh is the same on every rank
-    if shared:
-        # each rank renders its own frames of the camera path
-        from dirt_b200 import sharding
-        full = build_scene(wl, B * world)
-        lo, hi = sharding.shard_range(B * world, rank, world)
-        sc = {k: (v if k in ("faces", "vertex_colors", "world") else v[lo:hi]) for k, v in full.items()}
-        del full
-    V, F = sc["vertices"].shape[1], sc["faces"].shape[1]
-    host = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for k, v in sc.items()}
-    host["target"] = torch.from_numpy(np.random.RandomState(7 + rank).uniform(0, 1, (B, H, W, C)).astype(np.float32)).pin_memory()
-    d = {k: v.to(dev) for k, v in host.items()}
-    grad_pixels = torch.from_numpy(np.random.RandomState(5 + rank).randn(B, H, W, C).astype(np.float32)).to(dev)
-
-    def step():
-        px, fid, gb = ops.forward_raw(d["background"], d["vertices"], d["vertex_colors"], d["faces"], want_aux=True)
-        if not shared:
-            return ops.backward_raw(d["faces"], px, grad_pixels, fid, gb, V)
-        # shared mesh: the backward folds each frame's clip-space vertex gradient to world space
-        # with that frame's matrix and sums position + colour gradients over the frames into one
-        # packed [V, 8] buffer, which ONE allreduce then sums over the ranks in place
-        packed, gbg = ops.backward_shared_raw(d["faces"], px, grad_pixels, fid, gb, V, d["matrices"])
-        return sharding.allreduce_packed(packed, C)
 
     def barrier():
         if world > 1:
@@ -306,19 +334,55 @@ def run_ours(args, wl, rank, world, local_rank):
             return float(t.item())
         return ms
 
+    B, H, W, C = wl["B"], wl["H"], wl["W"], wl["C"]
+    shared = bool(wl.get("shared"))
+    sc = build_scene(wl, B, seed_shift=0 if shared else 10 * rank)     # a shared mesh is the same on every rank
+    if shared:
+        # each rank renders its own frames of the camera path
+        full = build_scene(wl, B * world)
+        lo, hi = sharding.shard_range(B * world, rank, world)
+        sc = {k: (v if k in ("faces", "vertex_colors", "world") else v[lo:hi]) for k, v in full.items()}
+        del full
+    V, F = sc["vertices"].shape[1], sc["faces"].shape[1]
+    host = {k: torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for k, v in sc.items()}
+    host["target"] = torch.from_numpy(np.random.RandomState(7 + rank).uniform(0, 1, (B, H, W, C)).astype(np.float32)).pin_memory()
+    d = {k: v.to(dev) for k, v in host.items()}
+    grad_pixels = torch.from_numpy(np.random.RandomState(5 + rank).randn(B, H, W, C).astype(np.float32)).to(dev)
+    # The geometry MOVES between steps (sphere workloads): FRAMES pre-uploaded vertex sets, visited 0 1 2 3 2 1 0 ...
+    # The forward keeps a visibility hint between calls (DirtForwardArgs.visibility_hint): identical inputs every
+    # step would be its best case, a sequence of slightly different frames is the case it is made for.
+    moving = not shared and not args.static
+    host_frames = [host["vertices"]] + ([torch.from_numpy(v).pin_memory() for v in build_frames(wl, B, rank)] if moving else [])
+    dev_frames = [h.to(dev) for h in host_frames]
+    order = frame_order(len(dev_frames))
+    nframes = len(dev_frames)
+    hint = ops.visibility_hint(dev, B, F, key="bench") if (F >= ops.HINT_MIN_FACES and not args.no_hint) else None
+
+    def step(i):
+        v = dev_frames[order[i % len(order)]]
+        px, fid, gb = ops.forward_raw(d["background"], v, d["vertex_colors"], d["faces"], want_aux=True, hint=hint)
+        if not shared:
+            return ops.backward_raw(d["faces"], px, grad_pixels, fid, gb, V)
+        # shared mesh: the backward folds each frame's clip-space vertex gradient to world space
+        # with that frame's matrix and sums position + colour gradients over the frames into one
+        # packed [V, 8] buffer, which ONE allreduce then sums over the ranks in place
+        packed, gbg = ops.backward_shared_raw(d["faces"], px, grad_pixels, fid, gb, V, d["matrices"])
+        return sharding.allreduce_packed(packed, C)
+
     clocks = ClockSampler(local_rank)
     if rank == 0:
         clocks.start()                      # nvidia-smi needs ~1 s to deliver its first sample
-    for _ in range(max(args.warmup, 3)):
-        step()
+    warm = max(args.warmup, 3)
+    for i in range(warm):
+        step(i)
     barrier()
     n0 = _lib.launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     t_timed = time.time()
     ev0.record()
-    for _ in range(args.steps):
-        step()
+    for i in range(args.steps):
+        step(warm + i)
     ev1.record()
     barrier()
     ms_total = max_over_ranks(ev0.elapsed_time(ev1))
@@ -328,25 +392,16 @@ def run_ours(args, wl, rank, world, local_rank):
     window = "timed region"
     if ms_total < 1500.0:
         window = "timed region + untimed continuation of the same steps (timed region shorter than the sampling period)"
-        for _ in range(int(min(5000, 1500.0 / max(ms_total / args.steps, 1e-3)))):    # same count on every rank
-            step()
+        for i in range(int(min(5000, 1500.0 / max(ms_total / args.steps, 1e-3)))):    # same count on every rank
+            step(i)
         barrier()
     clock_info = clocks.stop(t_timed, window) if rank == 0 else None
     ms_step = ms_total / args.steps
     value = world * B * H * W / (ms_step * 1e-3) / 1e6
 
     # ---- per-kernel durations, measured live with CUDA events inside the library -------------
-    _lib.check(lib.dirt_profile_reset())
-    _lib.check(lib.dirt_profile_enable(1))
-    nprof = min(args.steps, 10)
-    for _ in range(nprof):
-        step()
-        torch.cuda.synchronize()
-        _lib.check(lib.dirt_profile_collect())
-    _lib.check(lib.dirt_profile_enable(0))
-    times = _lib.stage_times()
-    stages = {k: ms / nprof for k, (ms, n) in times.items()}                      # per step
-    per_step_launches = {k: n / nprof for k, (ms, n) in times.items()}
+    nprof = min(args.steps, 12)
+    stages, per_step_launches = stage_profile(step, nprof)
     per_kernel, fwd_bytes, bwd_bytes = algorithmic_bytes(B, H, W, C, V, F, shared)
     dominant = max(per_kernel, key=lambda k: stages.get(k, 0.0))
     peak, peak_src = hbm_peak()
@@ -362,12 +417,13 @@ def run_ours(args, wl, rank, world, local_rank):
                 "step_algorithmic_bytes": fwd_bytes + bwd_bytes,
                 "step_achieved_GBps": (fwd_bytes + bwd_bytes) / (ms_step * 1e-3) / 1e9,
                 "step_frac": (fwd_bytes + bwd_bytes) / (ms_step * 1e-3) / 1e9 / peak,
+                "per_kernel_frac": {k: (per_kernel[k] / (stages[k] * 1e-3) / 1e9 / peak if stages.get(k, 0) > 0 else None) for k in per_kernel},
                 "binding_pipes_ncu": ncu_pipes("k_" + dominant, args.workload),
                 "note": "k_setup is bound by instruction issue, k_grad_assemble / k_resolve by the LSU data pipe "
-                        "(profiles/r1_bench_ncu.md); HBM is the stated roofline, not what limits them"}
+                        "(profiles/); HBM is the stated roofline, not what limits them"}
 
     # ---- e2e: public API, pinned host inputs, H2D + D2H inside the timed region -------------
-    # Every step uploads ITS inputs (vertices, colours, faces; see below for the background) from
+    # Every step uploads ITS inputs (this step's vertices, colours, faces; see below for the background) from
     # pinned host memory and reads back its loss and gradients.  Steps are software-pipelined over two buffer sets
     # and three streams (upload i+1 | compute i | download i-1), the way a training loop feeds a
     # GPU; the target image of the loss stays resident.
@@ -391,7 +447,8 @@ def run_ours(args, wl, rank, world, local_rank):
         with torch.cuda.stream(s_in):
             s_in.wait_event(free[slot])                 # the step that last used this buffer set has finished
             for k in in_keys:
-                dev_in[slot][k].copy_(host[k], non_blocking=True)
+                src = host_frames[order[i % len(order)]] if k == "vertices" else host[k]
+                dev_in[slot][k].copy_(src, non_blocking=True)
             ready[slot].record(s_in)
 
     def e2e_compute(i):
@@ -438,7 +495,7 @@ def run_ours(args, wl, rank, world, local_rank):
             done[slot].synchronize()
         losses.append(float(out_loss[(n - 1) % 2]))
 
-    e2e_steps = max(2, min(args.steps, 10))
+    e2e_steps = max(2, min(args.steps, 12))
     e2e_run(3)
     barrier()
     ev0.record()
@@ -457,31 +514,173 @@ def run_ours(args, wl, rank, world, local_rank):
     e2e = {"value": world * B * H * W / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": e2e_steps, "last_loss": losses[-1],
            "path": ("dirt_b200.rasterise_batch_shared" if shared else "dirt_b200.rasterise_batch") +
-                   " + autograd backward; each step uploads its inputs from pinned host "
+                   " + autograd backward; each step uploads its inputs (that step's vertex set) from pinned host "
                    "memory and downloads loss + gradients; double-buffered over copy/compute/copy streams" + bg_note}
+
+    extra = {}
+    # ---- e2e through the host-buffer C ABI (what a non-torch caller pays): every tensor crosses the bus ----
+    if rank == 0 and not shared and not args.no_extras:
+        extra["e2e_host_abi"] = host_abi_e2e(lib, host, host_frames, order, B, H, W, C, V, F)
+    del dev_in, out_gv, out_gc
+    # ---- the other device-resident configs of BASELINE.json, so that a driver-run number exists for them ----
+    if args.workload == "headline" and not args.no_extras:
+        del d, dev_frames, grad_pixels
+        torch.cuda.empty_cache()
+        extra["c4"] = extra_sphere(WORKLOADS["c4"], args, rank, world, dev, barrier, max_over_ranks)
+        torch.cuda.empty_cache()
+        extra["c5"] = extra_c5(WORKLOADS["c5"], args, rank, world, dev, barrier, max_over_ranks)
+        torch.cuda.empty_cache()
 
     cpu_base = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         if _ORIG_AFFINITY:
             os.sched_setaffinity(0, _ORIG_AFFINITY)      # the CPU baseline may use every host core again
         cpu_base = cpu_baseline_run(wl, 12.0)
+        one = cpu_baseline_run(wl, 3.0, threads=1)
+        cpu_base["single_thread"] = {k: one[k] for k in ("value", "unit", "cores", "sample", "seconds_per_run")}
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     if rank != 0:
         return
     print(json.dumps({
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warm,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": args.workload + ": " + wl["desc"], "batch_per_gpu": B, "height": H, "width": W, "channels": C,
                    "vertices": V, "faces": F,
+                   "geometry": ("moves between steps: %d pre-uploaded vertex sets, each element's object turned a further %.2f deg "
+                                "(<= 0.7 px on screen) per frame, visited 0 1 2 3 2 1 0 ...; the forward carries its visibility "
+                                "hint from call to call" % (nframes, FRAME_STEP_DEG)) if moving
+                               else "static (the same inputs every step)" + ("" if hint is None else "; visibility hint carried from call to call"),
+                   "visibility_hint": hint is not None,
                    "sharding": ("frames across ranks; one packed all_reduce of [V,4+C] shared-mesh gradients per step" if shared
                                 else "batch elements across ranks, no data-path collective"),
                    "l2": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2; no explicit flush" % ((fwd_bytes + bwd_bytes) / 1e6),
                    "host": numa},
         "roofline": roofline, "stages_ms": stages, "cpu_baseline": cpu_base, "e2e": e2e, "gpu_launches": int(launches),
-        "clocks": clock_info}))
+        "clocks": clock_info, "extra": extra}))
+
+
+def host_abi_e2e(lib, host, host_frames, order, B, H, W, C, V, F, steps=3):
+    """fwd+bwd through dirt_rasterise_forward_host / dirt_rasterise_backward_host: plain HOST pointers in and out,
+    pixels, aux buffers and all gradients returned to the host -- the cost a caller without device memory pays."""
+    import torch
+    from dirt_b200 import _lib
+    px = torch.empty((B, H, W, C), dtype=torch.float32).pin_memory()
+    fid = torch.empty((B, H, W), dtype=torch.int32).pin_memory()
+    gb = torch.empty((B, H, W, 4), dtype=torch.float32).pin_memory()
+    g = torch.ones((B, H, W, C), dtype=torch.float32).pin_memory()
+    gv = torch.empty((B, V, 4), dtype=torch.float32).pin_memory()
+    gc = torch.empty((B, V, C), dtype=torch.float32).pin_memory()
+    gbg = torch.empty((B, H, W, C), dtype=torch.float32).pin_memory()
+    shape = _lib.DirtShape(B, H, W, C, V, F)
+
+    def once(i):
+        v = host_frames[order[i % len(order)]]
+        fa = _lib.DirtForwardArgs(shape, host["background"].data_ptr(), H * W * C, v.data_ptr(), V * 4,
+                                  host["vertex_colors"].data_ptr(), V * C, host["faces"].data_ptr(), F * 3,
+                                  px.data_ptr(), fid.data_ptr(), gb.data_ptr(), None, 0, None, 0)
+        _lib.check(lib.dirt_rasterise_forward_host(ctypes.byref(fa)))
+        ba = _lib.DirtBackwardArgs(shape, host["faces"].data_ptr(), F * 3, px.data_ptr(), g.data_ptr(), fid.data_ptr(), gb.data_ptr(),
+                                   gv.data_ptr(), V * 4, gc.data_ptr(), V * C, gbg.data_ptr())
+        _lib.check(lib.dirt_rasterise_backward_host(ctypes.byref(ba)))
+
+    once(0)
+    t0 = time.perf_counter()
+    for i in range(steps):
+        once(1 + i)
+    sec = (time.perf_counter() - t0) / steps
+    img, aux = B * H * W * C * 4, B * H * W * 20
+    mesh = B * (V * 16 + V * C * 4 + F * 12)
+    lib.dirt_release_host_staging()
+    return {"value": B * H * W / sec / 1e6, "unit": UNIT, "ms_per_step": sec * 1e3, "steps": steps,
+            "h2d_bytes_per_step": img + mesh + B * F * 12 + 2 * img + aux, "d2h_bytes_per_step": img + aux + B * V * (16 + 4 * C) + img,
+            "path": "dirt_rasterise_forward_host + dirt_rasterise_backward_host on pinned host buffers (synchronous; pixels, "
+                    "face_id, gbuffer and every gradient returned to the host), wall clock, N=1 rank 0 only"}
+
+
+def extra_sphere(wl, args, rank, world, dev, barrier, max_over_ranks):
+    """Device-resident fwd+bwd of another sphere config (BASELINE.json config 4), same protocol as the headline."""
+    import torch
+    from dirt_b200 import rasterise_ops as ops
+    B, H, W, C = wl["B"], wl["H"], wl["W"], wl["C"]
+    sc = build_scene(wl, B, seed_shift=10 * rank)
+    V, F = sc["vertices"].shape[1], sc["faces"].shape[1]
+    d = {k: torch.from_numpy(np.ascontiguousarray(v)).to(dev) for k, v in sc.items()}
+    frames = [d["vertices"]] + [torch.from_numpy(v).to(dev) for v in build_frames(wl, B, rank)]
+    order = frame_order(len(frames))
+    g = torch.randn((B, H, W, C), device=dev)
+    hint = None if args.no_hint else ops.visibility_hint(dev, B, F, key="bench-" + str(H))
+
+    def step(i):
+        px, fid, gb = ops.forward_raw(d["background"], frames[order[i % len(order)]], d["vertex_colors"], d["faces"], hint=hint)
+        return ops.backward_raw(d["faces"], px, g, fid, gb, V)
+
+    steps = min(args.steps, 10)
+    ms = time_steps(step, steps, 3, barrier, max_over_ranks)
+    stages, _ = stage_profile(step, 6)
+    return {"workload": wl["desc"] + "; geometry moves between steps as in the headline", "value": world * B * H * W / (ms * 1e-3) / 1e6,
+            "unit": UNIT, "ms_per_step": ms, "steps": steps, "stages_ms": {k: v for k, v in stages.items() if v > 0}}
+
+
+def extra_c5(wl, args, rank, world, dev, barrier, max_over_ranks):
+    """Config c5 (shared hill mesh, frames sharded over the ranks): the step with its packed allreduce issued
+    synchronously, without it, and split into two frame groups whose first allreduce overlaps the second group's
+    kernels (side stream); the only NCCL traffic on this path's data."""
+    import torch
+    import torch.distributed as dist
+    from dirt_b200 import rasterise_ops as ops, sharding, _lib
+    B, H, W, C = wl["B"], wl["H"], wl["W"], wl["C"]
+    full = build_scene(wl, B * world)
+    lo, hi = sharding.shard_range(B * world, rank, world)
+    sc = {k: (v if k in ("faces", "vertex_colors", "world") else v[lo:hi]) for k, v in full.items()}
+    del full
+    V, F = sc["vertices"].shape[1], sc["faces"].shape[1]
+    d = {k: torch.from_numpy(np.ascontiguousarray(v)).to(dev) for k, v in sc.items()}
+    g = torch.randn((B, H, W, C), device=dev)
+    side = torch.cuda.Stream(dev)
+    main = torch.cuda.current_stream(dev)
+
+    def fwd_bwd(sl):
+        px, fid, gb = ops.forward_raw(d["background"][sl], d["vertices"][sl], d["vertex_colors"], d["faces"])
+        return ops.backward_shared_raw(d["faces"], px, g[sl], fid, gb, V, d["matrices"][sl])[0]
+
+    def step_sync(i):
+        return sharding.allreduce_packed(fwd_bwd(slice(0, B)), C)
+
+    def step_local(i):
+        return fwd_bwd(slice(0, B))
+
+    def step_overlap(i):
+        # group 0's gradients travel while group 1 renders; the two sums are added after the second collective
+        p0 = fwd_bwd(slice(0, B // 2))
+        ev = torch.cuda.Event()
+        ev.record(main)
+        with torch.cuda.stream(side):
+            side.wait_event(ev)
+            p0.record_stream(side)
+            w0 = dist.all_reduce(p0, async_op=True) if world > 1 else None
+        p1 = fwd_bwd(slice(B // 2, B))
+        if world > 1:
+            dist.all_reduce(p1)
+            w0.wait()
+        main.wait_stream(side)
+        return p0.add_(p1)
+
+    steps = min(args.steps, 10)
+    out = {"workload": wl["desc"], "frames_per_gpu": B, "allreduce_bytes": V * lib_stride(C) * 4, "unit": UNIT}
+    for name, fn in (("sync_allreduce", step_sync), ("no_allreduce", step_local), ("overlapped_two_groups", step_overlap)):
+        ms = time_steps(fn, steps, 3, barrier, max_over_ranks)
+        out[name] = {"ms_per_step": ms, "value": world * B * H * W / (ms * 1e-3) / 1e6}
+    out["allreduce_exposed_ms"] = out["sync_allreduce"]["ms_per_step"] - out["no_allreduce"]["ms_per_step"]
+    out["nccl"] = {k: os.environ[k] for k in os.environ if k.startswith("NCCL_")}
+    return out
+
+
+def lib_stride(C):
+    from dirt_b200 import _lib
+    return int(_lib.load().dirt_shared_grad_stride(C))
 
 
 def main():
@@ -492,6 +691,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="headline", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--static", action="store_true", help="identical inputs every step (round-1 protocol)")
+    ap.add_argument("--no-hint", action="store_true", help="do not carry the visibility hint between calls")
+    ap.add_argument("--no-extras", action="store_true", help="skip extra.c4 / extra.c5 / extra.e2e_host_abi")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

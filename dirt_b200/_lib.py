@@ -13,7 +13,8 @@ LIB_PATH = os.environ.get("DIRT_B200_LIB") or os.path.join(_HERE, "libdirt_b200.
 
 STATUS_NAMES = {0: "OK", -1: "INVALID_ARGUMENT", -2: "CUDA_ERROR", -3: "WORKSPACE_TOO_SMALL", -4: "UNSUPPORTED"}
 MAX_CHANNELS = 16
-ABI_VERSION = 1
+ABI_VERSION = 2
+BACKWARD_DETERMINISTIC = 1
 
 _f32p = ctypes.c_void_p
 _i64 = ctypes.c_int64
@@ -31,7 +32,8 @@ class DirtForwardArgs(ctypes.Structure):
                 ("vertex_colors", _f32p), ("vertex_colors_bstride", _i64),
                 ("faces", _f32p), ("faces_bstride", _i64),
                 ("pixels", _f32p), ("face_id", _f32p), ("gbuffer", _f32p),
-                ("workspace", ctypes.c_void_p), ("workspace_bytes", ctypes.c_size_t)]
+                ("workspace", ctypes.c_void_p), ("workspace_bytes", ctypes.c_size_t),
+                ("visibility_hint", ctypes.c_void_p), ("visibility_hint_bytes", ctypes.c_size_t)]
 
 
 class DirtBackwardArgs(ctypes.Structure):
@@ -40,14 +42,18 @@ class DirtBackwardArgs(ctypes.Structure):
                 ("pixels", _f32p), ("grad_pixels", _f32p), ("face_id", _f32p), ("gbuffer", _f32p),
                 ("grad_vertices", _f32p), ("grad_vertices_bstride", _i64),
                 ("grad_vertex_colors", _f32p), ("grad_vertex_colors_bstride", _i64),
-                ("grad_background", _f32p)]
+                ("grad_background", _f32p),
+                ("vertices", _f32p), ("vertices_bstride", _i64),
+                ("workspace", ctypes.c_void_p), ("workspace_bytes", ctypes.c_size_t),
+                ("flags", ctypes.c_uint32)]
 
 
 class DirtSharedBackwardArgs(ctypes.Structure):
     _fields_ = [("shape", DirtShape),
                 ("faces", _f32p), ("faces_bstride", _i64),
                 ("pixels", _f32p), ("grad_pixels", _f32p), ("face_id", _f32p), ("gbuffer", _f32p),
-                ("clip_from_world", _f32p), ("grad_shared", _f32p), ("grad_background", _f32p)]
+                ("clip_from_world", _f32p), ("grad_shared", _f32p), ("grad_background", _f32p),
+                ("workspace", ctypes.c_void_p), ("workspace_bytes", ctypes.c_size_t), ("flags", ctypes.c_uint32)]
 
 
 class DirtSceneArgs(ctypes.Structure):
@@ -63,6 +69,11 @@ EXPORTS = {
     "dirt_abi_version": (ctypes.c_int, []),
     "dirt_last_error": (ctypes.c_char_p, []),
     "dirt_workspace_bytes": (ctypes.c_size_t, [ctypes.POINTER(DirtShape)]),
+    "dirt_visibility_hint_bytes": (ctypes.c_size_t, [ctypes.POINTER(DirtShape)]),
+    "dirt_backward_workspace_bytes": (ctypes.c_size_t, [ctypes.POINTER(DirtShape)]),
+    "dirt_deterministic_workspace_bytes": (ctypes.c_size_t, [ctypes.POINTER(DirtShape)]),
+    "dirt_workspace_create": (ctypes.c_int, [ctypes.POINTER(DirtShape), ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_size_t)]),
+    "dirt_workspace_destroy": (ctypes.c_int, [ctypes.c_void_p]),
     "dirt_rasterise_forward": (ctypes.c_int, [ctypes.POINTER(DirtForwardArgs), ctypes.c_void_p]),
     "dirt_rasterise_backward": (ctypes.c_int, [ctypes.POINTER(DirtBackwardArgs), ctypes.c_void_p]),
     "dirt_shared_grad_stride": (ctypes.c_int, [ctypes.c_int]),

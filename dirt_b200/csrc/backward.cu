@@ -91,7 +91,24 @@ __device__ __forceinline__ void red_add3(float *dst, float a, float b, float c)
     }
 }
 
-template <int C>
+// Deterministic mode (DirtBackwardArgs.flags & DIRT_BACKWARD_DETERMINISTIC; GRADIENT_SPEC 5): fp32 atomics make the
+// sums depend on the order in which warps arrive.  Integer addition does not: pass DET == 1 finds the largest
+// |contribution| of the call (a maximum is order-free too), pass DET == 2 converts every contribution to fixed point
+// with the power-of-two scale that maximum allows and accumulates in 64-bit integers, k_det_finish converts back.
+// Within a warp the per-face sums are a fixed shuffle tree in every mode.
+__device__ __forceinline__ float det_scale(unsigned max_bits)
+{
+    // |value| * scale < 2^35 and at most 2^27 contributions per sum: no overflow of the 63-bit accumulator
+    int e = (int)(max_bits >> 23) - 127;
+    e = e < -90 ? -90 : (e > 127 ? 127 : e);
+    return ldexpf(1.0f, 33 - e);
+}
+__device__ __forceinline__ void det_add(long long *dst, float v, float scale)
+{
+    atomicAdd(reinterpret_cast<unsigned long long *>(dst), (unsigned long long)__float2ll_rn(v * scale));
+}
+
+template <int C, int DET>
 #ifndef KBWD_CTAS
 #define KBWD_CTAS 5
 #endif
@@ -126,6 +143,8 @@ __global__ void __launch_bounds__(kThreads, KBWD_CTAS) k_grad_assemble(BwdParams
     const int x = (int)blockIdx.x * kTX - 1 + lx, r = (int)blockIdx.y * kTY - 1 + ly;
     const float halfW = 0.5f * (float)W, halfH = 0.5f * (float)H;
     const float4 *gbuf_all = reinterpret_cast<const float4 *>(p.gbuffer);
+    float det_mpos = 0.0f, det_mcol = 0.0f;                       // DET == 1: largest |contribution| seen by this thread
+    const float det_spos = DET == 2 ? det_scale(p.det_max[0]) : 1.0f, det_scol = DET == 2 ? det_scale(p.det_max[1]) : 1.0f;
 
     for (int b = blockIdx.z; b < p.B; b += gridDim.z) {
         const size_t base = (size_t)b * H * W;
@@ -218,7 +237,7 @@ __global__ void __launch_bounds__(kThreads, KBWD_CTAS) k_grad_assemble(BwdParams
                                    gx * __ldg(M + 8) + gy * __ldg(M + 9) + gw * __ldg(M + 11),
                                    gx * __ldg(M + 12) + gy * __ldg(M + 13) + gw * __ldg(M + 15));
             };
-            if (C == 1 || C == 3) {
+            if (DET == 0 && (C == 1 || C == 3)) {
                 constexpr int NQ = 3 + (C > 0 ? C : 1);
                 float v[3 * NQ];
     #pragma unroll
@@ -253,25 +272,89 @@ __global__ void __launch_bounds__(kThreads, KBWD_CTAS) k_grad_assemble(BwdParams
                     const float bk = k == 0 ? B0 : (k == 1 ? B1 : B2);
                     v[k * 3] = gxv * bk; v[k * 3 + 1] = gyv * bk; v[k * 3 + 2] = gwv * bk;
                 }
-                const bool leader = peer_reduce(peers, v);
-                if (act) {
+                const bool leader = peer_reduce(peers, v) && act;
+                int vi[3] = {0, 0, 0};
+                if (leader) {
+    #pragma unroll
                     for (int k = 0; k < 3; ++k) {
-                        const int vi = __ldg(fp + k);
+                        vi[k] = __ldg(fp + k);
+                        if (v[k * 3] != 0.0f || v[k * 3 + 1] != 0.0f || v[k * 3 + 2] != 0.0f) {
+                            const float4 q = packed ? to_world(v[k * 3], v[k * 3 + 1], v[k * 3 + 2]) : make_float4(v[k * 3], v[k * 3 + 1], 0.0f, v[k * 3 + 2]);
+                            if (DET == 0) {
+                                if (packed) atomicAdd(reinterpret_cast<float4 *>(p.grad_packed + (int64_t)vi[k] * p.packed_stride), q);
+                                else atomicAdd(gv + vi[k], q);
+                            } else if (DET == 1) {
+                                det_mpos = fmaxf(det_mpos, fmaxf(fmaxf(fabsf(q.x), fabsf(q.y)), fmaxf(fabsf(q.z), fabsf(q.w))));
+                            } else {
+                                long long *a = p.det_pos + 4 * ((packed || p.grad_vertices_bs == 0 ? 0 : (int64_t)b * p.V) + vi[k]);
+                                det_add(a, q.x, det_spos); det_add(a + 1, q.y, det_spos); det_add(a + 2, q.z, det_spos); det_add(a + 3, q.w, det_spos);
+                            }
+                        }
+                    }
+                }
+                // colours, three channels at a time: summed per face across the warp like the position part (a deferred
+                // G-buffer call has 9+ channels and few, large faces: one scalar atomic per pixel, vertex and channel
+                // would all land on the same few addresses)
+                for (int c0 = 0; c0 < CC; c0 += 3) {
+    #pragma unroll
+                    for (int k = 0; k < 3; ++k) {
                         const float bk = k == 0 ? B0 : (k == 1 ? B1 : B2);
-                        const bool moved = leader && (v[k * 3] != 0.0f || v[k * 3 + 1] != 0.0f || v[k * 3 + 2] != 0.0f);
-                        if (packed) {
-                            float *row = p.grad_packed + (int64_t)vi * p.packed_stride;
-                            if (moved) atomicAdd(reinterpret_cast<float4 *>(row), to_world(v[k * 3], v[k * 3 + 1], v[k * 3 + 2]));
-                            for (int c = 0; c < CC; ++c) atomicAdd(row + 4 + c, g[c] * bk);
-                        } else {
-                            if (moved) atomicAdd(gv + vi, make_float4(v[k * 3], v[k * 3 + 1], 0.0f, v[k * 3 + 2]));
-                            for (int c = 0; c < CC; ++c) atomicAdd(gc + (int64_t)vi * CC + c, g[c] * bk);
+    #pragma unroll
+                        for (int j = 0; j < 3; ++j) v[k * 3 + j] = (act && c0 + j < CC) ? g[c0 + j] * bk : 0.0f;
+                    }
+                    peer_reduce(peers, v);
+                    if (leader) {
+    #pragma unroll
+                        for (int k = 0; k < 3; ++k) {
+                            float *dst = packed ? p.grad_packed + (int64_t)vi[k] * p.packed_stride + 4 + c0 : gc + (int64_t)vi[k] * CC + c0;
+                            long long *a = DET == 2 ? p.det_col + ((packed || p.grad_vertex_colors_bs == 0 ? 0 : (int64_t)b * p.V) + vi[k]) * CC + c0 : nullptr;
+    #pragma unroll
+                            for (int j = 0; j < 3; ++j)
+                                if (c0 + j < CC) {
+                                    if (DET == 0) atomicAdd(dst + j, v[k * 3 + j]);
+                                    else if (DET == 1) det_mcol = fmaxf(det_mcol, fabsf(v[k * 3 + j]));
+                                    else det_add(a + j, v[k * 3 + j], det_scol);
+                                }
                         }
                     }
                 }
             }
         }
         __syncthreads();        // the staged region is about to be overwritten
+    }
+    if (DET == 1) {
+        // non-negative floats order like their bit patterns
+        const unsigned mp = __reduce_max_sync(kFull, __float_as_uint(det_mpos)), mc = __reduce_max_sync(kFull, __float_as_uint(det_mcol));
+        if (lane == 0) {
+            if (mp) atomicMax(p.det_max, mp);
+            if (mc) atomicMax(p.det_max + 1, mc);
+        }
+    }
+}
+
+// Deterministic mode, last pass: fixed point -> float.  One thread per output value.
+__global__ void __launch_bounds__(256) k_det_finish(BwdParams p)
+{
+    const float rpos = 1.0f / det_scale(p.det_max[0]), rcol = 1.0f / det_scale(p.det_max[1]);
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p.grad_packed) {
+        const long long n = (long long)p.V * p.packed_stride;
+        if (i >= n) return;
+        const int v = (int)(i / p.packed_stride), j = (int)(i - (long long)v * p.packed_stride);
+        float out = 0.0f;
+        if (j < 4) out = __ll2float_rn(p.det_pos[4 * (long long)v + j]) * rpos;
+        else if (j < 4 + p.C) out = __ll2float_rn(p.det_col[(long long)v * p.C + (j - 4)]) * rcol;
+        p.grad_packed[i] = out;
+        return;
+    }
+    const long long nbv = p.grad_vertices_bs == 0 ? 1 : p.B, nbc = p.grad_vertex_colors_bs == 0 ? 1 : p.B;
+    const long long npos = nbv * p.V * 4, ncol = nbc * p.V * p.C;
+    if (i < npos) {
+        const long long b = i / ((long long)p.V * 4), r = i - b * (long long)p.V * 4;
+        p.grad_vertices[b * p.grad_vertices_bs + r] = __ll2float_rn(p.det_pos[i]) * rpos;
+    } else if (i < npos + ncol) {
+        const long long k = i - npos, b = k / ((long long)p.V * p.C), r = k - b * (long long)p.V * p.C;
+        p.grad_vertex_colors[b * p.grad_vertex_colors_bs + r] = __ll2float_rn(p.det_col[k]) * rcol;
     }
 }
 
@@ -283,8 +366,10 @@ cudaError_t launch_backward(const BwdParams &p, int sm_count, cudaStream_t strea
     if (p.grad_packed) {
         if ((e = cudaMemsetAsync(p.grad_packed, 0, (size_t)p.V * p.packed_stride * sizeof(float), stream)) != cudaSuccess) return e;
     } else {
-        if ((e = cudaMemsetAsync(p.grad_vertices, 0, nbv * p.V * 4 * sizeof(float), stream)) != cudaSuccess) return e;
-        if ((e = cudaMemsetAsync(p.grad_vertex_colors, 0, nbc * p.V * p.C * sizeof(float), stream)) != cudaSuccess) return e;
+        // one [V,*] block per batch element, `stride` elements apart (the blocks may be padded: clear each one)
+        const size_t wv = (size_t)p.V * 4 * sizeof(float), wc = (size_t)p.V * p.C * sizeof(float);
+        if (wv && (e = cudaMemset2DAsync(p.grad_vertices, nbv > 1 ? (size_t)p.grad_vertices_bs * sizeof(float) : wv, 0, wv, nbv, stream)) != cudaSuccess) return e;
+        if (wc && (e = cudaMemset2DAsync(p.grad_vertex_colors, nbc > 1 ? (size_t)p.grad_vertex_colors_bs * sizeof(float) : wc, 0, wc, nbc, stream)) != cudaSuccess) return e;
     }
     tm.end(kStageGradClear, stream);
     if ((long long)p.B * p.H * p.W == 0) return cudaSuccess;
@@ -297,10 +382,23 @@ cudaError_t launch_backward(const BwdParams &p, int sm_count, cudaStream_t strea
     if (gz < 1) gz = 1;
     const dim3 grid((p.W + kTX - 1) / kTX, (p.H + kTY - 1) / kTY, (unsigned)gz);
     tm.begin(kStageGradAssemble, stream);
+    if (p.det_pos) {
+        // deterministic mode: measure, accumulate in fixed point, convert (the clears above are redundant but harmless)
+        const size_t nacc = (p.grad_packed ? (size_t)p.V * (4 + p.C) : nbv * p.V * 4 + nbc * p.V * p.C);
+        if ((e = cudaMemsetAsync(p.det_max, 0, 2 * sizeof(unsigned), stream)) != cudaSuccess) return e;
+        if ((e = cudaMemsetAsync(p.det_pos, 0, nacc * sizeof(long long), stream)) != cudaSuccess) return e;
+        k_grad_assemble<0, 1><<<grid, kThreads, 0, stream>>>(p);
+        k_grad_assemble<0, 2><<<grid, kThreads, 0, stream>>>(p);
+        const size_t nout = p.grad_packed ? (size_t)p.V * p.packed_stride : nacc;
+        if (nout) k_det_finish<<<(unsigned)((nout + 255) / 256), 256, 0, stream>>>(p);
+        tm.end(kStageGradAssemble, stream);
+        *launches += 3;
+        return cudaGetLastError();
+    }
     switch (p.C) {
-        case 1: k_grad_assemble<1><<<grid, kThreads, 0, stream>>>(p); break;
-        case 3: k_grad_assemble<3><<<grid, kThreads, 0, stream>>>(p); break;
-        default: k_grad_assemble<0><<<grid, kThreads, 0, stream>>>(p); break;
+        case 1: k_grad_assemble<1, 0><<<grid, kThreads, 0, stream>>>(p); break;
+        case 3: k_grad_assemble<3, 0><<<grid, kThreads, 0, stream>>>(p); break;
+        default: k_grad_assemble<0, 0><<<grid, kThreads, 0, stream>>>(p); break;
     }
     tm.end(kStageGradAssemble, stream);
     *launches += 1;

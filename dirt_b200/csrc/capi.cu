@@ -160,7 +160,18 @@ size_t dirt_workspace_bytes(const DirtShape *shape)
     return workspace_layout(*shape).total;
 }
 
-int dirt_rasterise_forward(const DirtForwardArgs *a, void *stream)
+size_t dirt_visibility_hint_bytes(const DirtShape *shape)
+{
+    if (!shape || check_shape(*shape) != DIRT_STATUS_OK) return 0;
+    return align_up(dirt::kHintHeaderWords * sizeof(uint32_t) + (size_t)shape->batch * shape->face_count);
+}
+
+}  // extern "C"
+
+namespace {
+
+// aux_only: the stateless backward re-derives face_id / gbuffer; no colour is read or written
+int forward_impl(const DirtForwardArgs *a, void *stream, bool aux_only)
 {
     if (!a) return fail(DIRT_STATUS_INVALID_ARGUMENT, "null arguments");
     const DirtShape &s = a->shape;
@@ -168,13 +179,13 @@ int dirt_rasterise_forward(const DirtForwardArgs *a, void *stream)
     if (rc) return rc;
     const int64_t npix = (int64_t)s.height * s.width;
     // the four OP_REQUIRES shape checks of rasterise_egl.cpp:310-321 become stride checks here
-    if ((rc = check_stride(a->background_bstride, npix * s.channels, "background"))) return rc;
+    if (!aux_only && (rc = check_stride(a->background_bstride, npix * s.channels, "background"))) return rc;
     if ((rc = check_stride(a->vertices_bstride, (int64_t)s.vertex_count * 4, "vertices"))) return rc;
-    if ((rc = check_stride(a->vertex_colors_bstride, (int64_t)s.vertex_count * s.channels, "vertex_colors"))) return rc;
+    if (!aux_only && (rc = check_stride(a->vertex_colors_bstride, (int64_t)s.vertex_count * s.channels, "vertex_colors"))) return rc;
     if ((rc = check_stride(a->faces_bstride, (int64_t)s.face_count * 3, "faces"))) return rc;
     if (s.batch == 0) return DIRT_STATUS_OK;
-    if (!a->background || !a->pixels) return fail(DIRT_STATUS_INVALID_ARGUMENT, "background and pixels must not be null");
-    if (s.face_count > 0 && (!a->vertices || !a->vertex_colors || !a->faces))
+    if (!aux_only && (!a->background || !a->pixels)) return fail(DIRT_STATUS_INVALID_ARGUMENT, "background and pixels must not be null");
+    if (s.face_count > 0 && (!a->vertices || (!aux_only && !a->vertex_colors) || !a->faces))
         return fail(DIRT_STATUS_INVALID_ARGUMENT, "vertices, vertex_colors and faces must not be null when face_count > 0");
     if ((a->face_id == nullptr) != (a->gbuffer == nullptr))
         return fail(DIRT_STATUS_INVALID_ARGUMENT, "face_id and gbuffer must be both null or both set");
@@ -185,6 +196,12 @@ int dirt_rasterise_forward(const DirtForwardArgs *a, void *stream)
         return fail(DIRT_STATUS_WORKSPACE_TOO_SMALL, "workspace of %zu bytes given, %zu needed", a->workspace_bytes, L.total);
     if ((uintptr_t)a->workspace & (kAlign - 1))
         return fail(DIRT_STATUS_INVALID_ARGUMENT, "workspace must be %zu-byte aligned", kAlign);
+    if (a->visibility_hint) {
+        const size_t need = dirt_visibility_hint_bytes(&s);
+        if (a->visibility_hint_bytes < need)
+            return fail(DIRT_STATUS_INVALID_ARGUMENT, "visibility_hint of %zu bytes given, %zu needed", a->visibility_hint_bytes, need);
+        if ((uintptr_t)a->visibility_hint & 15u) return fail(DIRT_STATUS_INVALID_ARGUMENT, "visibility_hint must be 16-byte aligned");
+    }
     int sms = 0;
     if ((rc = current_sm_count(&sms))) return rc;
 
@@ -195,7 +212,7 @@ int dirt_rasterise_forward(const DirtForwardArgs *a, void *stream)
     p.vertices = a->vertices;           p.vertices_bs = a->vertices_bstride;
     p.vertex_colors = a->vertex_colors; p.vertex_colors_bs = a->vertex_colors_bstride;
     p.faces = a->faces;                 p.faces_bs = a->faces_bstride;
-    p.pixels = a->pixels; p.face_id = a->face_id; p.gbuffer = a->gbuffer;
+    p.pixels = aux_only ? nullptr : a->pixels; p.face_id = a->face_id; p.gbuffer = a->gbuffer;
     char *ws = static_cast<char *>(a->workspace);
     p.keys = reinterpret_cast<unsigned long long *>(ws + L.keys);
     p.proj = reinterpret_cast<const int4 *>(ws + L.proj);
@@ -211,6 +228,10 @@ int dirt_rasterise_forward(const DirtForwardArgs *a, void *stream)
     // depth-ordered passes pay off on meshes with real depth complexity; flat face numbers are 32-bit
     const bool ordered = s.face_count >= dirt::kOrderMinFaces && s.batch <= 65535 && (unsigned long long)s.batch * s.face_count < (1ull << 32);
     p.order = ordered ? reinterpret_cast<uint32_t *>(ws + L.order) : nullptr;
+    // the hint orders the depth-ordered passes; without them it is neither read nor written
+    const bool hinted = ordered && a->visibility_hint != nullptr;
+    p.hint_hdr = hinted ? static_cast<uint32_t *>(a->visibility_hint) : nullptr;
+    p.vis_flags = hinted ? static_cast<uint8_t *>(a->visibility_hint) + dirt::kHintHeaderWords * sizeof(uint32_t) : nullptr;
     p.bucket_of = reinterpret_cast<uint8_t *>(ws + L.bucket_of);
     p.pivots = reinterpret_cast<float *>(ws + L.pivots);
     p.bucket_count = reinterpret_cast<uint32_t *>(ws + L.bucket_count);
@@ -227,6 +248,60 @@ int dirt_rasterise_forward(const DirtForwardArgs *a, void *stream)
     return DIRT_STATUS_OK;
 }
 
+// Deterministic mode: carves the fixed-point accumulators out of `ws` (dirt_deterministic_workspace_bytes).
+int place_deterministic(dirt::BwdParams &p, const DirtShape &s, void *ws, size_t ws_bytes, size_t offset, bool packed)
+{
+    const size_t need = offset + align_up(kAlign + (size_t)s.batch * s.vertex_count * (4 + s.channels) * sizeof(long long));
+    if (!ws || ws_bytes < need)
+        return fail(DIRT_STATUS_WORKSPACE_TOO_SMALL, "deterministic backward: workspace of %zu bytes given, %zu needed", ws ? ws_bytes : (size_t)0, need);
+    if ((uintptr_t)ws & (kAlign - 1)) return fail(DIRT_STATUS_INVALID_ARGUMENT, "workspace must be %zu-byte aligned", kAlign);
+    char *base = static_cast<char *>(ws) + offset;
+    p.det_max = reinterpret_cast<unsigned *>(base);
+    p.det_pos = reinterpret_cast<long long *>(base + kAlign);
+    const size_t nbv = (packed || p.grad_vertices_bs == 0) ? 1 : (size_t)s.batch;
+    p.det_col = p.det_pos + nbv * s.vertex_count * 4;
+    return DIRT_STATUS_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int dirt_rasterise_forward(const DirtForwardArgs *a, void *stream) { return forward_impl(a, stream, false); }
+
+size_t dirt_backward_workspace_bytes(const DirtShape *shape)
+{
+    if (!shape || check_shape(*shape) != DIRT_STATUS_OK) return 0;
+    const size_t npix = (size_t)shape->batch * shape->height * shape->width;
+    return align_up(workspace_layout(*shape).total) + align_up(npix * sizeof(int32_t)) + align_up(npix * 4 * sizeof(float));
+}
+
+size_t dirt_deterministic_workspace_bytes(const DirtShape *shape)
+{
+    if (!shape || check_shape(*shape) != DIRT_STATUS_OK) return 0;
+    return align_up(kAlign + (size_t)shape->batch * shape->vertex_count * (4 + shape->channels) * sizeof(long long));
+}
+
+int dirt_workspace_create(const DirtShape *shape, void **workspace, size_t *workspace_bytes)
+{
+    if (!workspace) return fail(DIRT_STATUS_INVALID_ARGUMENT, "null arguments");
+    *workspace = nullptr;
+    // covers dirt_workspace_bytes(shape), the stateless and the deterministic backward
+    const size_t n = dirt_backward_workspace_bytes(shape) + dirt_deterministic_workspace_bytes(shape);
+    if (n == 0) return fail(DIRT_STATUS_INVALID_ARGUMENT, "invalid shape");
+    const cudaError_t e = cudaMalloc(workspace, n);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaMalloc (workspace)");
+    if (workspace_bytes) *workspace_bytes = n;
+    return DIRT_STATUS_OK;
+}
+
+int dirt_workspace_destroy(void *workspace)
+{
+    if (!workspace) return DIRT_STATUS_OK;
+    const cudaError_t e = cudaFree(workspace);
+    return e == cudaSuccess ? DIRT_STATUS_OK : cuda_fail(e, "cudaFree (workspace)");
+}
+
 int dirt_rasterise_backward(const DirtBackwardArgs *a, void *stream)
 {
     if (!a) return fail(DIRT_STATUS_INVALID_ARGUMENT, "null arguments");
@@ -237,12 +312,37 @@ int dirt_rasterise_backward(const DirtBackwardArgs *a, void *stream)
     if ((rc = check_stride(a->grad_vertices_bstride, (int64_t)s.vertex_count * 4, "grad_vertices"))) return rc;
     if ((rc = check_stride(a->grad_vertex_colors_bstride, (int64_t)s.vertex_count * s.channels, "grad_vertex_colors"))) return rc;
     if (s.batch == 0) return DIRT_STATUS_OK;
-    if (!a->pixels || !a->grad_pixels || !a->face_id || !a->gbuffer)
-        return fail(DIRT_STATUS_INVALID_ARGUMENT, "pixels, grad_pixels, face_id and gbuffer must not be null");
+    if (!a->pixels || !a->grad_pixels) return fail(DIRT_STATUS_INVALID_ARGUMENT, "pixels and grad_pixels must not be null");
+    if ((a->face_id == nullptr) != (a->gbuffer == nullptr))
+        return fail(DIRT_STATUS_INVALID_ARGUMENT, "face_id and gbuffer must be both given (from the forward) or both null (re-derived from vertices)");
     if (s.vertex_count > 0 && (!a->grad_vertices || !a->grad_vertex_colors))
         return fail(DIRT_STATUS_INVALID_ARGUMENT, "grad_vertices and grad_vertex_colors must not be null");
     if (s.face_count > 0 && !a->faces) return fail(DIRT_STATUS_INVALID_ARGUMENT, "faces must not be null");
-    if (((uintptr_t)a->gbuffer & 15u) || ((uintptr_t)a->grad_vertices & 15u) || ((a->grad_vertices_bstride * 4) & 15))
+    const int32_t *face_id = a->face_id;
+    const float *gbuffer = a->gbuffer;
+    if (!face_id) {
+        // stateless mode: visibility is re-derived with the forward's kernels (same keys, same G-buffer)
+        const size_t need = dirt_backward_workspace_bytes(&s);
+        if (!a->workspace || a->workspace_bytes < need)
+            return fail(DIRT_STATUS_WORKSPACE_TOO_SMALL, "backward without face_id / gbuffer: workspace of %zu bytes given, %zu needed",
+                        a->workspace ? a->workspace_bytes : (size_t)0, need);
+        if ((uintptr_t)a->workspace & (kAlign - 1)) return fail(DIRT_STATUS_INVALID_ARGUMENT, "workspace must be %zu-byte aligned", kAlign);
+        if (s.face_count > 0 && !a->vertices)
+            return fail(DIRT_STATUS_INVALID_ARGUMENT, "backward without face_id / gbuffer needs vertices");
+        const size_t npix = (size_t)s.batch * s.height * s.width;
+        char *ws = static_cast<char *>(a->workspace);
+        const size_t fwd_bytes = align_up(workspace_layout(s).total);
+        DirtForwardArgs f = {};
+        f.shape = s;
+        f.vertices = a->vertices; f.vertices_bstride = a->vertices_bstride;
+        f.faces = a->faces;       f.faces_bstride = a->faces_bstride;
+        f.face_id = reinterpret_cast<int32_t *>(ws + fwd_bytes);
+        f.gbuffer = reinterpret_cast<float *>(ws + fwd_bytes + align_up(npix * sizeof(int32_t)));
+        f.workspace = ws; f.workspace_bytes = fwd_bytes;
+        if ((rc = forward_impl(&f, stream, true))) return rc;
+        face_id = f.face_id; gbuffer = f.gbuffer;
+    }
+    if (((uintptr_t)gbuffer & 15u) || ((uintptr_t)a->grad_vertices & 15u) || ((a->grad_vertices_bstride * 4) & 15))
         return fail(DIRT_STATUS_INVALID_ARGUMENT, "gbuffer and grad_vertices must be 16-byte aligned");
     int sms = 0;
     if ((rc = current_sm_count(&sms))) return rc;
@@ -250,11 +350,14 @@ int dirt_rasterise_backward(const DirtBackwardArgs *a, void *stream)
     dirt::BwdParams p;
     p.B = s.batch; p.H = s.height; p.W = s.width; p.C = s.channels; p.V = s.vertex_count; p.F = s.face_count;
     p.faces = a->faces; p.faces_bs = a->faces_bstride;
-    p.pixels = a->pixels; p.grad_pixels = a->grad_pixels; p.face_id = a->face_id; p.gbuffer = a->gbuffer;
+    p.pixels = a->pixels; p.grad_pixels = a->grad_pixels; p.face_id = face_id; p.gbuffer = gbuffer;
     p.grad_vertices = a->grad_vertices;           p.grad_vertices_bs = a->grad_vertices_bstride;
     p.grad_vertex_colors = a->grad_vertex_colors; p.grad_vertex_colors_bs = a->grad_vertex_colors_bstride;
     p.grad_background = a->grad_background;
     p.matrices = nullptr; p.grad_packed = nullptr; p.packed_stride = 0;
+    p.det_pos = nullptr; p.det_col = nullptr; p.det_max = nullptr;
+    if (a->flags & DIRT_BACKWARD_DETERMINISTIC)
+        if ((rc = place_deterministic(p, s, a->workspace, a->workspace_bytes, a->face_id ? 0 : align_up(dirt_backward_workspace_bytes(&s)), false))) return rc;
     uint64_t n = 0;
     cudaError_t e = dirt::launch_backward(p, sms, static_cast<cudaStream_t>(stream), &n, g_timer);
     g_launches += n;
@@ -297,6 +400,9 @@ int dirt_rasterise_backward_shared(const DirtSharedBackwardArgs *a, void *stream
     p.grad_vertex_colors = nullptr; p.grad_vertex_colors_bs = 0;
     p.grad_background = a->grad_background;
     p.matrices = a->clip_from_world; p.grad_packed = a->grad_shared; p.packed_stride = stride;
+    p.det_pos = nullptr; p.det_col = nullptr; p.det_max = nullptr;
+    if (a->flags & DIRT_BACKWARD_DETERMINISTIC)
+        if ((rc = place_deterministic(p, s, a->workspace, a->workspace_bytes, 0, true))) return rc;
     uint64_t n = 0;
     cudaError_t e = dirt::launch_backward(p, sms, static_cast<cudaStream_t>(stream), &n, g_timer);
     g_launches += n;
@@ -362,9 +468,18 @@ int dirt_dilate_silhouette_grad(const float *x, const float *grad_out, float *gr
     return e == cudaSuccess ? DIRT_STATUS_OK : cuda_fail(e, "dilate grad launch");
 }
 
+int g_prof_device = -1;      // the events live on the device that was current when profiling was first enabled
+
 int dirt_profile_enable(int enable)
 {
     std::lock_guard<std::mutex> lock(g_prof_mu);
+    if (enable) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess) return fail(DIRT_STATUS_CUDA_ERROR, "dirt_profile_enable: no CUDA device");
+        if (g_prof_device >= 0 && dev != g_prof_device)
+            return fail(DIRT_STATUS_UNSUPPORTED, "stage profiling is per process and bound to device %d; current device is %d", g_prof_device, dev);
+        g_prof_device = dev;
+    }
     if (enable && !g_timer.ev[0][0][0]) {
         for (int s = 0; s < dirt::kStageCount; ++s)
             for (int r = 0; r < dirt::StageTimer::kSlots; ++r)

@@ -76,6 +76,7 @@ int dirt_rasterise_forward_host(const DirtForwardArgs *h)
     if (cudaError_t e_ = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking)) return dirt::set_error(DIRT_STATUS_CUDA_ERROR, "stream creation", e_);
     DirtForwardArgs d = *h;
     d.workspace = arena_take<char>(A, ws_bytes); d.workspace_bytes = ws_bytes;
+    d.visibility_hint = nullptr; d.visibility_hint_bytes = 0;      // a device-side, persistent buffer: not part of the host-buffer calls
     float *bg = arena_take<float>(A, n_bg), *v = arena_take<float>(A, n_v), *c = arena_take<float>(A, n_c);
     int32_t *f = arena_take<int32_t>(A, n_f);
     d.pixels = arena_take<float>(A, npix * s.channels);
@@ -111,7 +112,11 @@ int dirt_rasterise_backward_host(const DirtBackwardArgs *h)
     const size_t n_f = extent(h->faces_bstride, (int64_t)s.face_count * 3, s.batch);
     const size_t n_gv = extent(h->grad_vertices_bstride, (int64_t)s.vertex_count * 4, s.batch);
     const size_t n_gc = extent(h->grad_vertex_colors_bstride, (int64_t)s.vertex_count * s.channels, s.batch);
-    size_t need = pad(n_f * 4) + 3 * pad(nimg * 4) + pad(npix * 4) + pad(npix * 16) + pad(n_gv * 4) + pad(n_gc * 4);
+    const bool stateless = h->face_id == nullptr && h->gbuffer == nullptr;      // visibility re-derived from vertices
+    const size_t n_v = stateless ? extent(h->vertices_bstride, (int64_t)s.vertex_count * 4, s.batch) : 0;
+    const size_t ws_bytes = stateless ? dirt_backward_workspace_bytes(&s) : 0;
+    if (stateless && (!h->vertices || ws_bytes == 0)) return dirt::set_error(DIRT_STATUS_INVALID_ARGUMENT, "backward without face_id / gbuffer needs vertices", cudaSuccess);
+    size_t need = pad(n_f * 4) + 3 * pad(nimg * 4) + pad(npix * 4) + pad(npix * 16) + pad(n_gv * 4) + pad(n_gc * 4) + pad(n_v * 4) + pad(ws_bytes);
     if (cudaError_t e_ = arena_reserve(A, need)) return dirt::set_error(DIRT_STATUS_CUDA_ERROR, "device staging allocation", e_);
     cudaStream_t st;
     if (cudaError_t e_ = cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking)) return dirt::set_error(DIRT_STATUS_CUDA_ERROR, "stream creation", e_);
@@ -124,9 +129,19 @@ int dirt_rasterise_backward_host(const DirtBackwardArgs *h)
     if (n_f) HOST_TRY(cudaMemcpyAsync(f, h->faces, n_f * 4, cudaMemcpyHostToDevice, st));
     HOST_TRY(cudaMemcpyAsync(px, h->pixels, nimg * 4, cudaMemcpyHostToDevice, st));
     HOST_TRY(cudaMemcpyAsync(g, h->grad_pixels, nimg * 4, cudaMemcpyHostToDevice, st));
-    HOST_TRY(cudaMemcpyAsync(fid, h->face_id, npix * 4, cudaMemcpyHostToDevice, st));
-    HOST_TRY(cudaMemcpyAsync(gb, h->gbuffer, npix * 16, cudaMemcpyHostToDevice, st));
     d.faces = f; d.pixels = px; d.grad_pixels = g; d.face_id = fid; d.gbuffer = gb;
+    d.vertices = nullptr; d.workspace = nullptr; d.workspace_bytes = 0;
+    d.flags = h->flags & ~DIRT_BACKWARD_DETERMINISTIC;      // the host-buffer calls offer the default summation only
+    if (stateless) {
+        float *v = arena_take<float>(A, n_v);
+        d.workspace = arena_take<char>(A, ws_bytes); d.workspace_bytes = ws_bytes;
+        if (n_v) HOST_TRY(cudaMemcpyAsync(v, h->vertices, n_v * 4, cudaMemcpyHostToDevice, st));
+        d.vertices = v; d.face_id = nullptr; d.gbuffer = nullptr;
+    } else {
+        if (!h->face_id || !h->gbuffer) { cudaStreamDestroy(st); return dirt::set_error(DIRT_STATUS_INVALID_ARGUMENT, "face_id and gbuffer must be both given or both null", cudaSuccess); }
+        HOST_TRY(cudaMemcpyAsync(fid, h->face_id, npix * 4, cudaMemcpyHostToDevice, st));
+        HOST_TRY(cudaMemcpyAsync(gb, h->gbuffer, npix * 16, cudaMemcpyHostToDevice, st));
+    }
     d.grad_vertices = gv; d.grad_vertex_colors = gc; d.grad_background = h->grad_background ? gbg : nullptr;
     int rc = dirt_rasterise_backward(&d, st);
     if (rc != DIRT_STATUS_OK) { cudaStreamDestroy(st); return rc; }

@@ -223,6 +223,7 @@ __global__ void __launch_bounds__(256) k_depth_split2(FwdParams p, float min_ove
     if (t < 2) s_cnt[t] = 0;
     __syncthreads();
     const float pivot = p.pivots[b * kMaxBuckets];
+    const uint32_t gen = hint_generation(p);
     const int front = use_facing ? (int)p.pivots[b * kMaxBuckets + kMaxBuckets - 1] : 0;
     const int f0 = blockIdx.x * kChunkFaces, f1 = min(f0 + kChunkFaces, p.F);
     uint32_t rank[kChunkFaces / 256];
@@ -231,9 +232,16 @@ __global__ void __launch_bounds__(256) k_depth_split2(FwdParams p, float min_ove
     for (int j = 0; j < kChunkFaces / 256; ++j) {
         const int f = f0 + t + j * 256;
         if (f < f1) {
-            int facing = 0;
-            const float z = face_near_depth(p, b, f, nullptr, use_facing ? &facing : nullptr);
-            const int k = (front == 0 || facing == front || z == 0.0f) ? (z >= pivot ? 1 : 0) : 1;
+            int k;
+            if (gen) {
+                // hinted: the faces that won a pixel in the previous call go first, everything else behind the
+                // pyramid they leave (no depth is looked at: one byte per face)
+                k = p.vis_flags[(size_t)b * p.F + f] == (uint8_t)gen ? 0 : 1;
+            } else {
+                int facing = 0;
+                const float z = face_near_depth(p, b, f, nullptr, use_facing ? &facing : nullptr);
+                k = (front == 0 || facing == front || z == 0.0f) ? (z >= pivot ? 1 : 0) : 1;
+            }
             kbits |= (uint32_t)k << j;
             rank[j] = atomicAdd(&s_cnt[k], 1u);
         }

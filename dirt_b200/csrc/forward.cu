@@ -5,19 +5,20 @@
 // (csrc/rasterise_egl.cu:16-129) and the three device-to-device mesh copies (:365-367).
 // One launch per stage covers the whole batch; nothing is serial over batch elements.
 //
-// Stages (all on the caller's stream):
-//   S0  clear      keys := EMPTY, counters := 0
-//   S1  setup      1 thread / (element, face): clip, project, snap, edge setup.  Three size classes:
-//                  bbox height <= kInlineRows: the thread walks the rows' spans itself, 64-bit
-//                  atomicMin on the key buffer; bbox <= kSpanDim^2: the whole warp does (lane =
-//                  row); larger: appended to the large-triangle list for S2/S3.
-//   S2a bin_count  1 warp / large triangle: exact tile/triangle overlap test, per-tile counters
-//   S2b bin_alloc  1 thread / tile: reserve a contiguous, 16-byte aligned queue segment
-//   S2c bin_fill   1 warp / large triangle: write face references into the tile queues
+// Stages (all on the caller's stream; DESIGN.md section 3 has the table):
+//   S0  clear       keys := EMPTY, counters := 0
+//   S0b project     (setup_raster.cu) one record per vertex
+//   S1a order       (depth_order.cu) faces split into "first" (hinted or nearest) and "rest"
+//   S1  setup       (setup_raster.cu) lane = face set-up, then lane = scan line; 64-bit atomicMin on the
+//                   key buffer; the second launch tests faces and 8-line chunks against the depth pyramid
+//   S2a bin_count   1 warp / large triangle: exact tile/triangle overlap test, per-tile counters
+//   S2b bin_alloc   1 thread / tile: reserve a contiguous, 16-byte aligned queue segment
+//   S2c bin_fill    1 warp / large triangle: write face references into the tile queues
 //   S3  tile_raster 1 CTA / 16x16 tile: queue segment -> shared memory (bulk async copy),
-//                  per-entry setup into shared memory, per-pixel register min of the key
-//   S4  resolve    1 thread / pixel: key -> face -> perspective-correct interpolation ->
-//                  pixels (+ face_id, gbuffer), background where uncovered
+//                   per-entry setup into shared memory, per-pixel register min of the key
+//   S3s small_raster meshes of <= 32 faces: one launch instead of S0, S1, S2, S3
+//   S4  resolve     1 thread / pixel: key -> face -> perspective-correct interpolation ->
+//                   pixels (+ face_id, gbuffer), background where uncovered
 #include "forward_common.cuh"
 
 namespace dirt {
@@ -323,6 +324,8 @@ __global__ void __launch_bounds__(256, KRES_CTAS) k_resolve(FwdParams p)
 {
     const int CC = C > 0 ? C : p.C;
     const int npix = p.H * p.W;
+    // visibility hint for the next call on this mesh: faces that win a pixel are stamped with the next generation
+    const uint8_t stamp = p.vis_flags ? (uint8_t)hint_next_generation(hint_generation(p)) : (uint8_t)0;
     // kResolvePix pixels per thread: a CTA that resolves only 256 pixels is launch-rate bound.
     // The gather chain key -> face -> corners is software-pipelined over those pixels: the key of
     // pixel j+2 and the corner indices of pixel j+1 are in flight while pixel j is shaded.
@@ -357,8 +360,10 @@ __global__ void __launch_bounds__(256, KRES_CTAS) k_resolve(FwdParams p)
         float *out = p.pixels + i * CC;
         if (key == kKeyEmpty) {
             // the reference never clears the colour buffer: background shows through
-            const float *bg = p.background + (int64_t)b * p.background_bs + (size_t)o * CC;
-            for (int c = 0; c < CC; ++c) out[c] = __ldg(bg + c);
+            if (p.pixels) {       // (null: the stateless backward re-derives face_id / gbuffer only)
+                const float *bg = p.background + (int64_t)b * p.background_bs + (size_t)o * CC;
+                for (int c = 0; c < CC; ++c) out[c] = __ldg(bg + c);
+            }
             if (p.face_id) {
                 p.face_id[i] = -1;
                 reinterpret_cast<float4 *>(p.gbuffer)[i] = make_float4(0.f, 0.f, 0.f, 1.0f);
@@ -368,6 +373,11 @@ __global__ void __launch_bounds__(256, KRES_CTAS) k_resolve(FwdParams p)
         const int f = (int)(uint32_t)(key & 0xFFFFFFFFull);
         const int4 *pp = proj_ptr(p, b);
         const int4 ra = __ldg(pp + i0), rb = __ldg(pp + i1), rc = __ldg(pp + i2);
+        if (p.vis_flags) {
+            // a visible face covers many pixels: look before storing (a byte load that hits L1 / L2)
+            uint8_t *fl = p.vis_flags + ((size_t)b * p.F + (uint32_t)f);
+            if (*fl != stamp) *fl = stamp;
+        }
         float B0 = 0.f, B1 = 0.f, wc = 1.f;
         if (ra.x != kProjSlow && rb.x != kProjSlow && rc.x != kProjSlow) {
             // the pixel is known to be covered: only the sign and 1/area of the setup are needed
@@ -403,13 +413,15 @@ __global__ void __launch_bounds__(256, KRES_CTAS) k_resolve(FwdParams p)
         }
         // else: a corner went through the clipper (rare) -- k_resolve_clipped rewrites this pixel; calling
         // the clip path from here costs the whole kernel registers and a stack frame
-        const float *cp = p.vertex_colors + (int64_t)b * p.vertex_colors_bs;
-        const float *c0 = cp + (int64_t)i0 * CC, *c1 = cp + (int64_t)i1 * CC, *c2 = cp + (int64_t)i2 * CC;
-        for (int c = 0; c < CC; ++c) {
-            // smooth varying (csrc/shaders.cpp:23,29), arranged so constant colours are exact
-            const float k2 = __ldg(c2 + c);
-            const float t0 = fsub(__ldg(c0 + c), k2), t1 = fsub(__ldg(c1 + c), k2);
-            out[c] = fadd(fadd(k2, fmul(B0, t0)), fmul(B1, t1));
+        if (p.pixels) {
+            const float *cp = p.vertex_colors + (int64_t)b * p.vertex_colors_bs;
+            const float *c0 = cp + (int64_t)i0 * CC, *c1 = cp + (int64_t)i1 * CC, *c2 = cp + (int64_t)i2 * CC;
+            for (int c = 0; c < CC; ++c) {
+                // smooth varying (csrc/shaders.cpp:23,29), arranged so constant colours are exact
+                const float k2 = __ldg(c2 + c);
+                const float t0 = fsub(__ldg(c0 + c), k2), t1 = fsub(__ldg(c1 + c), k2);
+                out[c] = fadd(fadd(k2, fmul(B0, t0)), fmul(B1, t1));
+            }
         }
         if (p.face_id) {
             p.face_id[i] = f;
@@ -426,6 +438,11 @@ __global__ void __launch_bounds__(256, KRES_CTAS) k_resolve(FwdParams p)
 // weights through the clipped fan and rewrites colour and G-buffer with the formulas of k_resolve.
 __global__ void __launch_bounds__(256) k_resolve_clipped(FwdParams p)
 {
+    if (p.hint_hdr && blockIdx.x == 0 && threadIdx.x == 0) {
+        // k_resolve has stamped this call's visible faces with the next generation: publish it
+        const uint32_t next = hint_next_generation(hint_generation(p));
+        *reinterpret_cast<uint4 *>(p.hint_hdr) = make_uint4(kHintMagic, (uint32_t)p.B, (uint32_t)p.F, next);
+    }
     if (p.counters[kCtrSlow] == 0u) return;
     const FwdParams pc = p;      // resolve_clipped takes a reference: keep the parameter block itself out of local memory
     const int npix = pc.H * pc.W, CC = pc.C;
@@ -443,13 +460,15 @@ __global__ void __launch_bounds__(256) k_resolve_clipped(FwdParams p)
             float B0 = 0.f, B1 = 0.f, wc = 1.f;
             resolve_clipped(pc, b, i0, i1, i2, px, py, (uint32_t)(key >> 32), B0, B1, wc);
             const size_t i = (size_t)b * npix + o;
-            float *out = pc.pixels + i * CC;
-            const float *cp = pc.vertex_colors + (int64_t)b * pc.vertex_colors_bs;
-            const float *c0 = cp + (int64_t)i0 * CC, *c1 = cp + (int64_t)i1 * CC, *c2 = cp + (int64_t)i2 * CC;
-            for (int c = 0; c < CC; ++c) {
-                const float k2 = __ldg(c2 + c);
-                const float t0 = fsub(__ldg(c0 + c), k2), t1 = fsub(__ldg(c1 + c), k2);
-                out[c] = fadd(fadd(k2, fmul(B0, t0)), fmul(B1, t1));
+            if (pc.pixels) {
+                float *out = pc.pixels + i * CC;
+                const float *cp = pc.vertex_colors + (int64_t)b * pc.vertex_colors_bs;
+                const float *c0 = cp + (int64_t)i0 * CC, *c1 = cp + (int64_t)i1 * CC, *c2 = cp + (int64_t)i2 * CC;
+                for (int c = 0; c < CC; ++c) {
+                    const float k2 = __ldg(c2 + c);
+                    const float t0 = fsub(__ldg(c0 + c), k2), t1 = fsub(__ldg(c1 + c), k2);
+                    out[c] = fadd(fadd(k2, fmul(B0, t0)), fmul(B1, t1));
+                }
             }
             if (pc.face_id) {
                 const float zq = fmul(__uint2float_rn((uint32_t)(key >> 32)), kDepthScaleInv);

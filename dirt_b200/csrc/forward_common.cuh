@@ -55,6 +55,16 @@ __device__ __forceinline__ bool plan_is_ordered(const FwdParams &p, float min_ov
     return __uint_as_float(p.counters[kCtrOverdraw]) >= min_overdraw * (float)p.B;
 }
 
+// Generation of a usable visibility hint (1..255), or 0: none given, or its header is not that of
+// this shape (first use, another mesh) -- then the faces are ordered by depth as without a hint.
+__device__ __forceinline__ uint32_t hint_generation(const FwdParams &p)
+{
+    if (!p.hint_hdr) return 0u;
+    const uint4 h = *reinterpret_cast<const uint4 *>(p.hint_hdr);
+    return (h.x == kHintMagic && h.y == (uint32_t)p.B && h.z == (uint32_t)p.F && h.w >= 1u && h.w <= 255u) ? h.w : 0u;
+}
+__device__ __forceinline__ uint32_t hint_next_generation(uint32_t gen) { return gen % 255u + 1u; }
+
 // TriSetup from three projected records.  Returns false if culled; `slow` is set when a corner
 // needs the general path (then t is untouched).
 __device__ __forceinline__ bool setup_from_proj(const int4 &a, const int4 &b, const int4 &c, int W, int H,

@@ -41,11 +41,17 @@ struct FwdParams {
     unsigned long long *work_next; // [kMaxBuckets] next unclaimed entry of each setup launch; inside the zeroed region
     uint32_t *bucket_cursor;     // [kMaxBuckets * B]
     uint32_t *bucket_base;       // [kMaxBuckets + 1] first entry of each bucket in `order`
+    // visibility hint (optional, caller-owned, persistent between calls; see include/dirt_b200.h): which faces won a
+    // pixel in the previous call on this mesh.  Only ORDERS the work (those faces are sampled first), never decides it.
+    uint32_t *hint_hdr;          // [kHintHeaderWords] magic, B, F, generation; nullptr: no hint
+    uint8_t *vis_flags;          // [B*F] generation in which the face last won a pixel
     uint32_t *hiz;               // max depth24 per tile (window space, y up); level l has (8 << l)-px tiles and
     uint32_t hiz_off[4];         // starts at hiz + hiz_off[l], laid out [B][tiles_y(l)][tiles_x(l)]
 };
 
 constexpr int kMaxBuckets = 8;
+constexpr int kHintHeaderWords = 64;             // 256 bytes: the flags behind it stay 256-byte aligned
+constexpr uint32_t kHintMagic = 0x54524944u;     // "DIRT"
 constexpr int kHizLog2 = 3;      // hierarchical-depth tile edge at level 0: 8 px
 constexpr int kHizLevels = 4;    // 8, 16, 32, 64 px
 constexpr int kOrderMinFaces = 4096;   // per element; below this one unordered pass is cheaper
@@ -65,6 +71,10 @@ struct BwdParams {
     const float *matrices;       // [B,4,4] clip = world @ M_b
     float *grad_packed;
     int packed_stride;
+    // deterministic mode (det_pos != nullptr): fixed-point accumulators and the call's largest |contribution|
+    long long *det_pos;          // [nbv*V*4] (packed: [V*4]); det_col follows it in the same allocation
+    long long *det_col;          // [nbc*V*C] (packed: [V*C])
+    unsigned *det_max;           // [2] float bits: position, colour
 };
 
 enum Stage {

@@ -35,10 +35,6 @@ constexpr int kWarpsPerCta = 8;
 #ifndef KPRE0
 #define KPRE0 0
 #endif
-#ifndef KHIZ8
-#define KHIZ8 0      // > 0 (experimental, unmeasured): faces that pass the pyramid test get a second, warp-cooperative
-                     // test against every 8-px tile of their box when it has at most KHIZ8 of them (tools/sim_cull.py)
-#endif
 #ifndef KLDCG
 #define KLDCG 0      // 1: the depth pre-load bypasses L1 (sees the reductions of this launch)
 #endif
@@ -86,7 +82,7 @@ __global__ void __launch_bounds__(256) k_project(FwdParams p, int nbatch)
 //                            first_line << 9 (m1 = last position of a line; axis 1: lines are columns)
 //   row 2: sc0 sc1 sc2 face  sc_k = edge step per +1 line
 //   row 3: inv0 inv1 inv2 base_hi   inv_k = 256 / |sa_k| as float (0 when sa_k == 0)
-//   row 4: zref dzdx dzdy -
+//   row 4: zref dzdx dzdy xy  xy = xmin | ymin << 16 (both below 2^15)
 constexpr int kRecWords = 20;
 
 __device__ __forceinline__ uint32_t pick3(const uint32_t (&v)[3], int i) { return i == 0 ? v[0] : (i == 1 ? v[1] : v[2]); }
@@ -125,7 +121,7 @@ __device__ __forceinline__ uint32_t write_record(uint32_t *rec, const TriSetup &
     row[1] = make_uint4(pick3(sa, up), pick3(sa, dn), pick3(sa, re), dims);
     row[2] = make_uint4(pick3(sc, up), pick3(sc, dn), pick3(sc, re), face);
     row[3] = make_uint4(pick3(inv, up), pick3(inv, dn), pick3(inv, re), (uint32_t)(base >> 32));
-    row[4] = make_uint4(__float_as_uint(t.zref), __float_as_uint(t.dzdx), __float_as_uint(t.dzdy), 0u);
+    row[4] = make_uint4(__float_as_uint(t.zref), __float_as_uint(t.dzdx), __float_as_uint(t.dzdy), (uint32_t)t.xmin | (uint32_t)t.ymin << 16);
     return dims;
 }
 
@@ -147,16 +143,17 @@ __device__ __forceinline__ uint32_t load_depth_word(const unsigned long long *kp
     return v;
 }
 
-// Samples line `g` of the warp's batch, a line of the triangle in `rec` (a row when axis == 0,
-// a column when axis == 1).
-template <bool PRELOAD>
-__device__ __forceinline__ void sample_line(const uint32_t *rec, int g, const FwdParams &p)
+// Samples line `j - (first >> 9)` of the triangle in `rec` (a row when axis == 0, a column when
+// axis == 1); FIRST: j counts the lines of the warp's batch and the record's dims word carries the
+// number of the triangle's first line, otherwise j is the line of the triangle itself.
+template <bool PRELOAD, bool FIRST>
+__device__ __forceinline__ void sample_line(const uint32_t *rec, int j, const FwdParams &p)
 {
     const uint4 *row = reinterpret_cast<const uint4 *>(rec);
     const uint4 rA = row[0], rSA = row[1], rSC = row[2], rINV = row[3];
     const uint32_t face = rSC.w;
     const int axis = (int)(rSA.w >> 8) & 1, m1 = (int)(rSA.w & 0xFFu);      // m1: last position along the line
-    const int j = g - (int)(rSA.w >> 9);
+    if (FIRST) j -= (int)(rSA.w >> 9);
     const float fj = __int2float_rn(j);
     // Edge along the line: a + sa * c >= 0 with sa = +-256 * s.  The bound on c is
     // ceil(na / s) with na = ceil(-a / 256) (nested ceilings), and
@@ -270,22 +267,82 @@ __device__ __forceinline__ bool hidden_by_hiz(const FwdParams &p, int b, const T
     return m < dmin;          // equal depth: the face index decides
 }
 
+// Second-level occlusion test (launches that have a depth pyramid).  Can any sample of lines ja .. jb
+// of the triangle in `rec` still win a pixel?  The lines are eight (or fewer) neighbouring rows or
+// columns that share one row / column of 8-px pyramid tiles.  Their samples lie inside the rectangle
+// [lo, hi] x [ja, jb]: lo / hi are bounds on the edge crossings over the chunk -- an edge's crossing is
+// linear in the line number, so it is bounded by its values at the two end lines -- evaluated in
+// float with a margin (conservative: never narrower than the exact spans of sample_line).  Per tile
+// the rectangle touches, the smallest depth the plane takes on the rectangle's part inside the tile
+// (at a corner: the plane evaluation is monotone in dx and in dy under round-to-nearest, and it is
+// the evaluation sample_line uses) is compared with the tile's maximum: strictly greater everywhere
+// means no fragment of these lines can pass the depth test (equal depth: the face index decides).
+__device__ __forceinline__ bool chunk_visible(const uint32_t *rec, int ja, int jb, const uint32_t *hz0, int ntx)
+{
+    const uint4 *row = reinterpret_cast<const uint4 *>(rec);
+    const uint4 rA = row[0], rSA = row[1], rSC = row[2], rINV = row[3], rZ = row[4];
+    const int axis = (int)(rSA.w >> 8) & 1, m1 = (int)(rSA.w & 0xFFu);
+    constexpr float k256th = 1.0f / 256.0f;
+    // slot 0 rises along the line (inside: c >= -a / sa), slot 1 falls (inside: c <= a / |sa|)
+    float flo, fhi;
+    {
+        const int a0 = (int)rA.x + (int)rSC.x * ja, a1 = (int)rA.x + (int)rSC.x * jb;
+        flo = -__int2float_rn(max(a0, a1)) * (__uint_as_float(rINV.x) * k256th);
+    }
+    {
+        const int a0 = (int)rA.y + (int)rSC.y * ja, a1 = (int)rA.y + (int)rSC.y * jb;
+        fhi = __int2float_rn(max(a0, a1)) * (__uint_as_float(rINV.y) * k256th);
+    }
+    {
+        const int a0 = (int)rA.z + (int)rSC.z * ja, a1 = (int)rA.z + (int)rSC.z * jb;
+        const float q = __int2float_rn(max(a0, a1)) * (__uint_as_float(rINV.z) * k256th);
+        const int sa = (int)rSA.z;
+        if (sa > 0) flo = fmaxf(flo, -q);
+        else if (sa < 0) fhi = fminf(fhi, q);
+        else if (max(a0, a1) < 0) return false;          // outside this edge on every line of the chunk
+    }
+    // |error| of the float crossings is below 2^-12 for |c| < 2^10; beyond that the clamp decides
+    const int lo = max(0, __float2int_rd(flo - 0.01f)), hi = min(m1, __float2int_ru(fhi + 0.01f));
+    if (lo > hi) return false;
+    const float zref = __uint_as_float(rZ.x), dzdx = __uint_as_float(rZ.y), dzdy = __uint_as_float(rZ.z);
+    const int xmin = (int)(rZ.w & 0xFFFFu), ymin = (int)(rZ.w >> 16);
+    const int o = axis ? ymin : xmin;                                  // absolute coordinate of position 0
+    const int tl = ((axis ? xmin : ymin) + ja) >> kHizLog2;            // the chunk's row / column of tiles
+    const float zl = axis ? dzdx : dzdy, zq = axis ? dzdy : dzdx;
+    const float fl = __int2float_rn(zl >= 0.0f ? ja : jb);
+    const uint32_t *hz = hz0 + (axis ? tl : tl * ntx);
+    const int step = axis ? ntx : 1;
+    for (int t = (o + lo) >> kHizLog2; t <= (o + hi) >> kHizLog2; ++t) {
+        const int q0 = max(lo, (t << kHizLog2) - o), q1 = min(hi, (t << kHizLog2) + (1 << kHizLog2) - 1 - o);
+        const float fc = __int2float_rn(zq >= 0.0f ? q0 : q1);
+        // (zref + dzdx * dx) + dzdy * dy, the operation order of sample_line / plane_depth()
+        float zw = axis ? fadd(fadd(zref, fmul(dzdx, fl)), fmul(dzdy, fc)) : fadd(fadd(zref, fmul(dzdx, fc)), fmul(dzdy, fl));
+        zw = fminf(fmaxf(zw, 0.0f), 1.0f);
+        const uint32_t dmin = __float2uint_rz(fadd(fmul(zw, 16777215.0f), 0.5f));
+        if (__ldg(hz + t * step) >= dmin) return true;
+    }
+    return false;
+}
+
 // ORDERED: the faces of depth buckets k0 .. k1 (depth_order.cu), nearest bucket first because work
-// is claimed in the order of `order`; tested against the hierarchical depth buffer when `use_hiz`
-// (every launch but the first).  Otherwise all faces in index order.
-template <bool ORDERED>
+// is claimed in the order of `order`.  HIZ (every ordered launch but the first): faces are tested
+// against the hierarchical depth buffer, and those that survive are sampled in CHUNKS of eight lines
+// that are tested again, each against the 8-px tiles it touches (chunk_visible).  Otherwise all
+// faces in index order.
+template <bool ORDERED, bool HIZ>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdParams p, int k0, int k1, int launch_index, float min_overdraw)
 {
     __shared__ __align__(16) uint32_t s_recs[kWarpsPerCta][32 * kRecWords];
     __shared__ uint8_t s_owner[kWarpsPerCta][32];
+    __shared__ uint32_t s_aux[HIZ ? kWarpsPerCta : 1][32];     // HIZ: element | (first line & 7) << 16 | (lines - 1) << 19
+    __shared__ uint16_t s_list[HIZ ? kWarpsPerCta : 1][32];    // HIZ: surviving chunks: owner lane | first line << 5 | (lines - 1) << 12
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t *recs = s_recs[warp];
     uint8_t *owner_lane = s_owner[warp];
     // ORDERED launches check the verdict of k_depth_pivots: without enough overdraw the launch of
     // bucket 0 samples every face in index order and the other buckets' launches do nothing.
     const bool ordered = ORDERED && plan_is_ordered(p, min_overdraw);
-    if (ORDERED && !ordered && launch_index > 0) return;
-    const bool use_hiz = ordered && launch_index > 0;
+    if (HIZ && !ordered) return;
     long long first_entry = 0, total = (long long)p.B * p.F;
     // entries of the very nearest bucket: nearly every fragment wins there, reading the depth
     // first only adds latency; later buckets (of this or a later launch) look before they reduce
@@ -303,21 +360,19 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
     // a handful of faces cannot fill the machine line by line (one warp would walk every span in
     // turn): then anything but tiny triangles goes to the pixel-parallel tile path
     const bool many_faces = (long long)p.B * p.F >= kFewFaces;
+    const int hz_ntx = (p.W + (1 << kHizLog2) - 1) >> kHizLog2, hz_nty = (p.H + (1 << kHizLog2) - 1) >> kHizLog2;
     unsigned long long claim = 0;
     if (lane == 0) claim = atomicAdd(work, 32ull);
     for (;;) {
         const long long i0 = (long long)__shfl_sync(kFullMask, claim, 0);
         if (i0 >= total) break;
         const long long i = i0 + lane;
-        const bool preload = i0 >= no_preload_below;
+        const bool preload = HIZ || i0 >= no_preload_below;
         if (lane == 0) claim = atomicAdd(work, 32ull);
         // ---- setup: one face per lane -------------------------------------------------------
         int nlines = 0;                  // > 0: this lane's face is line-sampled by the warp
+        int nunits = 0;                  // what the warp distributes: lines, or (HIZ) chunks of eight lines
         uint32_t dims = 0;
-#if KHIZ8
-        uint32_t hz_box = 0, hz_dmin = 0;     // box in 8-px tiles: tx0 | ty0 << 11 | (nx - 1) << 22 | (ny - 1) << 27; 0 = no second test
-        int hz_b = 0;
-#endif
         if (i < total) {
             const long long flat = ordered ? (long long)p.order[first_entry + i] : i;
             const int b = (int)(flat / p.F), f = (int)(flat - (long long)b * p.F);
@@ -330,7 +385,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
                 if (setup_from_proj(__ldg(pp + i0), __ldg(pp + i1), __ldg(pp + i2), p.W, p.H, t, slow)) {
                     const int ex = max(t.X0, max(t.X1, t.X2)) - min(t.X0, min(t.X1, t.X2));
                     const int ey = max(t.Y0, max(t.Y1, t.Y2)) - min(t.Y0, min(t.Y1, t.Y2));
-                    if (use_hiz && hidden_by_hiz(p, b, t)) {
+                    if (HIZ && hidden_by_hiz(p, b, t)) {
                         // dropped: cannot win any pixel
 #ifdef DIRT_STATS
                         atomicAdd(p.counters + 4, 1u);
@@ -340,17 +395,13 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
                     {   // few-but-fat triangles are better off pixel-parallel in the tile path
                         nlines = max(t.xmax - t.xmin, t.ymax - t.ymin) + 1;     // the longer side of the bounding box
                         dims = write_record(recs + lane * kRecWords, t, (uint32_t)f, (uint32_t)b, p.H, p.W);
-#if KHIZ8
-                        if (use_hiz && ((nlines - 1) >> kHizLog2) > 1) {          // the first test ran above the 8-px level
-                            const int tx0 = t.xmin >> kHizLog2, ty0 = t.ymin >> kHizLog2;
-                            const int nx = (t.xmax >> kHizLog2) - tx0 + 1, ny = (t.ymax >> kHizLog2) - ty0 + 1;
-                            if (nx <= 32 && ny <= 32 && nx * ny <= KHIZ8 && tx0 < 2048 && ty0 < 2048) {
-                                hz_box = (uint32_t)tx0 | (uint32_t)ty0 << 11 | (uint32_t)(nx - 1) << 22 | (uint32_t)(ny - 1) << 27 | 0u;
-                                hz_dmin = hiz_dmin(t) | 0x80000000u;          // bit 31: "test me" (a box at tile 0,0 of 1x1 packs to 0)
-                                hz_b = b;
-                            }
+                        nunits = nlines;
+                        if (HIZ) {
+                            // chunks are aligned to the pyramid's tiles along the axis the lines are counted on
+                            const int l0 = ((dims >> 8) & 1u) ? t.xmin : t.ymin;
+                            nunits = ((l0 + nlines - 1) >> kHizLog2) - (l0 >> kHizLog2) + 1;
+                            s_aux[warp][lane] = (uint32_t)b | (uint32_t)(l0 & 7) << 16 | (uint32_t)(nlines - 1) << 19;
                         }
-#endif
                     } else
                         push_big(t, b, (uint32_t)f, 0u, p);
                 } else if (slow) {
@@ -362,60 +413,68 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
             }
         }
         // the r-th line-sampled face of the batch, in lane order, is the face of lane owner_lane[r]
-#if KHIZ8
-        if (use_hiz) {
-            // second test, the whole warp on one face at a time: every 8-px tile of its box
-            unsigned todo = __ballot_sync(kFullMask, (hz_dmin >> 31) != 0u);
-            const int ntx = (p.W + (1 << kHizLog2) - 1) >> kHizLog2, nty = (p.H + (1 << kHizLog2) - 1) >> kHizLog2;
-            while (todo) {
-                const int src = __ffs(todo) - 1;
-                todo &= todo - 1u;
-                const uint32_t box = __shfl_sync(kFullMask, hz_box, src);
-                const uint32_t dmin = __shfl_sync(kFullMask, hz_dmin, src) & 0x00FFFFFFu;
-                const int bb = __shfl_sync(kFullMask, hz_b, src);
-                const int tx0 = (int)(box & 2047u), ty0 = (int)((box >> 11) & 2047u);
-                const int nx = (int)((box >> 22) & 31u) + 1, n = nx * ((int)(box >> 27) + 1);
-                const uint32_t *hz = p.hiz + p.hiz_off[0] + ((size_t)bb * nty + ty0) * ntx + tx0;
-                bool visible = false;
-                for (int q = lane; q < n; q += 32) {
-                    const int dy = q / nx, dx = q - dy * nx;
-                    visible |= __ldg(hz + dy * ntx + dx) >= dmin;          // equal depth: the face index decides
-                }
-                if (!__any_sync(kFullMask, visible) && lane == src) nlines = 0;      // hidden: its record is never read
-            }
-        }
-#endif
-        const bool sampled = nlines > 0;
+        const bool sampled = nunits > 0;
         const unsigned owners = __ballot_sync(kFullMask, sampled);
         if (sampled) owner_lane[__popc(owners & ((1u << lane) - 1u))] = (uint8_t)lane;
 #ifdef DIRT_STATS
         if (nlines) { atomicAdd(p.counters + 6, 1u); atomicAdd(p.counters + 7, (uint32_t)nlines); }
 #endif
-        // running sum of the line counts over the warp: record r owns lines excl .. excl + nlines - 1
-        int incl = nlines;
+        // running sum of the unit counts over the warp: record r owns units excl .. excl + nunits - 1
+        int incl = nunits;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
             const int n = __shfl_up_sync(kFullMask, incl, o);
             if (lane >= o) incl += n;
         }
         const int nall = __shfl_sync(kFullMask, incl, 31);
-        const int excl = incl - nlines;
+        const int excl = incl - nunits;
         if (sampled) recs[lane * kRecWords + 7] = dims | ((uint32_t)excl << 9);
         __syncwarp();
-        // ---- sampling: 32 lines at a time ---------------------------------------------------
-        // Line g belongs to the last record that starts at or before g.  Records start at
-        // distinct lines (every record has at least one), so one OR-reduction of "my record
-        // starts at line base + d" bits and two population counts find the owner of every lane.
+        // ---- sampling: 32 units at a time ---------------------------------------------------
+        // Unit g belongs to the last record that starts at or before g.  Records start at
+        // distinct units (every record has at least one), so one OR-reduction of "my record
+        // starts at unit base + d" bits and two population counts find the owner of every lane.
         const unsigned upto_lane = (2u << lane) - 1u;
         for (int base = 0; base < nall; base += 32) {
             const int d = excl - base;
             const unsigned starts = __reduce_or_sync(kFullMask, (sampled && (unsigned)d < 32u) ? 1u << d : 0u);
             const int before = __popc(__ballot_sync(kFullMask, sampled && d < 0));
             const int g = base + lane;
-            if (g < nall) {
-                const uint32_t *rec = recs + owner_lane[before + __popc(starts & upto_lane) - 1] * kRecWords;
-                if (preload) sample_line<true>(rec, g, p);
-                else sample_line<false>(rec, g, p);
+            if (!HIZ) {
+                if (g < nall) {
+                    const uint32_t *rec = recs + owner_lane[before + __popc(starts & upto_lane) - 1] * kRecWords;
+                    if (preload) sample_line<true, true>(rec, g, p);
+                    else sample_line<false, true>(rec, g, p);
+                }
+            } else {
+                // the lane's chunk: lines ja .. jb of its triangle; tested, and the survivors listed
+                bool visible = false;
+                uint32_t entry = 0;
+                if (g < nall) {
+                    const int ol = owner_lane[before + __popc(starts & upto_lane) - 1];
+                    const uint32_t *rec = recs + ol * kRecWords;
+                    const uint32_t aux = s_aux[warp][ol];
+                    const int ci = g - (int)(rec[7] >> 9);
+                    const int first = (ci << kHizLog2) - (int)((aux >> 16) & 7u);
+                    const int ja = max(first, 0), jb = min(first + 7, (int)(aux >> 19));
+                    const uint32_t *hz0 = p.hiz + p.hiz_off[0] + (size_t)(aux & 0xFFFFu) * hz_nty * hz_ntx;
+                    visible = chunk_visible(rec, ja, jb, hz0, hz_ntx);
+                    entry = (uint32_t)ol | (uint32_t)ja << 5 | (uint32_t)(jb - ja) << 12;
+#ifdef DIRT_STATS
+                    atomicAdd(p.counters + 9, 1u);
+                    if (visible) atomicAdd(p.counters + 10, (uint32_t)(jb - ja + 1));
+#endif
+                }
+                const unsigned alive = __ballot_sync(kFullMask, visible);
+                if (visible) s_list[warp][__popc(alive & ((1u << lane) - 1u))] = (uint16_t)entry;
+                __syncwarp();
+                const int nl = __popc(alive) << 3;
+                for (int e = lane; e < nl; e += 32) {
+                    const uint32_t en = s_list[warp][e >> 3];
+                    const int dj = e & 7;
+                    if (dj <= (int)(en >> 12)) sample_line<true, false>(recs + (en & 31u) * kRecWords, (int)((en >> 5) & 127u) + dj, p);
+                }
+                __syncwarp();     // the list is about to be overwritten
             }
         }
         __syncwarp();     // the records are about to be overwritten
@@ -457,21 +516,22 @@ void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_
                 tm.end(kStageHizBuild, stream);
             }
             tm.begin(kStageSetup, stream);
-            k_setup<true><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, plan.launch_first[j], plan.launch_first[j + 1] - 1, j, plan.min_overdraw);
+            if (j == 0) k_setup<true, false><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, plan.launch_first[j], plan.launch_first[j + 1] - 1, j, plan.min_overdraw);
+            else k_setup<true, true><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, plan.launch_first[j], plan.launch_first[j + 1] - 1, j, plan.min_overdraw);
             tm.end(kStageSetup, stream);
 #ifdef DIRT_STATS
-            uint32_t c[8], bb[kMaxBuckets + 1];
+            uint32_t c[12], bb[kMaxBuckets + 1];
             cudaStreamSynchronize(stream);
             cudaMemcpy(c, p.counters, sizeof(c), cudaMemcpyDeviceToHost);
             cudaMemcpy(bb, p.bucket_base, sizeof(bb), cudaMemcpyDeviceToHost);
-            printf("launch %d: faces %u | cumulative: culled tris %u (lines %u), sampled tris %u (lines %u)\n", j,
-                   bb[plan.launch_first[j + 1]] - bb[plan.launch_first[j]], c[4], c[5], c[6], c[7]);
+            printf("launch %d: faces %u | cumulative: culled tris %u (lines %u), sampled tris %u (lines %u), chunks tested %u, lines in surviving chunks %u\n", j,
+                   bb[plan.launch_first[j + 1]] - bb[plan.launch_first[j]], c[4], c[5], c[6], c[7], c[9], c[10]);
 #endif
         }
         *launches += (plan.n == 2 ? 2 : 4) + 2 * plan.nlaunch - 1;     // ordering kernels + setup launches + pyramid builds
     } else {
         tm.begin(kStageSetup, stream);
-        k_setup<false><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, 0, 0, 0, 0.0f);
+        k_setup<false, false><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, 0, 0, 0, 0.0f);
         tm.end(kStageSetup, stream);
         *launches += 1;
     }

@@ -69,6 +69,32 @@ def _workspace(device, nbytes):
 
 def release_workspaces():
     _workspaces.clear()
+    _hints.clear()
+
+
+# Visibility hints (DirtForwardArgs.visibility_hint): one persistent device buffer per mesh that is
+# rendered repeatedly -- keyed by device, stream, batch, face count and frame size (not by tensor
+# identity: a double-buffered training loop alternates between input buffers), the way the workspace
+# is keyed by device and stream.  A hint only orders the kernels' work (results are bit-identical
+# with any hint), so a key that stands for another mesh costs time, not correctness.
+HINT_MIN_FACES = 4096          # kOrderMinFaces of the library: smaller meshes take one unordered pass
+_HINT_SLOTS = 8
+_hints = {}
+
+
+def visibility_hint(device, B, F, key=None):
+    """The persistent hint buffer for (device, current stream, B, F, key); zeroed when first created."""
+    lib = _lib.load()
+    shape = DirtShape(B, 1, 1, 1, 0, F)
+    nbytes = int(lib.dirt_visibility_hint_bytes(ctypes.byref(shape)))
+    k = (device.index, torch.cuda.current_stream(device).cuda_stream, B, F, key)
+    h = _hints.pop(k, None)
+    if h is None or h.numel() < nbytes:
+        h = torch.zeros(nbytes, dtype=torch.uint8, device=device)
+    _hints[k] = h                       # most recently used last
+    while len(_hints) > _HINT_SLOTS:
+        _hints.pop(next(iter(_hints)))
+    return h
 
 
 def _bstride(t, B):
@@ -96,9 +122,11 @@ def _validate(background, vertices, vertex_colors, faces, height, width, channel
     return B
 
 
-def forward_raw(background, vertices, vertex_colors, faces, want_aux=True):
+def forward_raw(background, vertices, vertex_colors, faces, want_aux=True, hint=None):
     """One C-ABI forward call on batched, contiguous CUDA tensors.
     Returns (pixels [B,H,W,C], face_id [B,H,W] | None, gbuffer [B,H,W,4] | None).
+    `hint`: None (no visibility hint), a uint8 CUDA tensor of dirt_visibility_hint_bytes() bytes owned by
+    the caller, or "auto" (the module keeps one per mesh, see visibility_hint()).
     `background` may also be a PINNED HOST tensor: the resolve kernel reads the background only
     where no face covers the pixel, so reading it in place over PCIe moves just those bytes
     instead of the whole image (the reference uploads all of it, csrc/rasterise_egl.cu:16-50)."""
@@ -117,6 +145,8 @@ def forward_raw(background, vertices, vertex_colors, faces, want_aux=True):
     if nbytes == 0:
         _lib.check(-1)
     ws = _workspace(device, nbytes)
+    if isinstance(hint, str):
+        hint = visibility_hint(device, B, F, key=(H, W)) if (hint == "auto" and F >= HINT_MIN_FACES) else None
     args = DirtForwardArgs(
         shape,
         background.data_ptr(), _bstride(background, B),
@@ -125,16 +155,24 @@ def forward_raw(background, vertices, vertex_colors, faces, want_aux=True):
         faces.data_ptr(), _bstride(faces, B),
         pixels.data_ptr(),
         face_id.data_ptr() if want_aux else None, gbuffer.data_ptr() if want_aux else None,
-        ws.data_ptr(), ws.numel())
+        ws.data_ptr(), ws.numel(),
+        hint.data_ptr() if hint is not None else None, hint.numel() if hint is not None else 0)
     with torch.cuda.device(device):
         _lib.check(lib.dirt_rasterise_forward(ctypes.byref(args), torch.cuda.current_stream(device).cuda_stream))
     return pixels, face_id, gbuffer
 
 
+def deterministic_default():
+    """DIRT_B200_DETERMINISTIC=1 switches the autograd path to the deterministic backward (debugging aid)."""
+    import os
+    return os.environ.get("DIRT_B200_DETERMINISTIC", "0") not in ("", "0")
+
+
 def backward_raw(faces, pixels, grad_pixels, face_id, gbuffer, V, shared_vertices=False, shared_colors=False,
-                 want_grad_background=True):
+                 want_grad_background=True, vertices=None, deterministic=False):
     """One C-ABI backward call.  Returns (grad_vertices [B|1,V,4], grad_vertex_colors [B|1,V,C],
-    grad_background [B,H,W,C] | None)."""
+    grad_background [B,H,W,C] | None).  With face_id = gbuffer = None the call is stateless: it re-derives
+    both from `vertices` [B|1,V,4] with the forward's kernels (the mode the TF op pair uses)."""
     lib = _lib.load()
     device = pixels.device
     B, H, W, C = pixels.shape
@@ -145,18 +183,28 @@ def backward_raw(faces, pixels, grad_pixels, face_id, gbuffer, V, shared_vertice
     gbg = torch.empty((B, H, W, C), dtype=torch.float32, device=device) if want_grad_background else None
     if B == 0:
         return gv.zero_(), gc.zero_(), gbg
+    stateless = face_id is None and gbuffer is None
+    ws = None
+    if stateless or deterministic:
+        ws = _workspace(device, (lib.dirt_backward_workspace_bytes(ctypes.byref(shape)) if stateless else 0) +
+                        (lib.dirt_deterministic_workspace_bytes(ctypes.byref(shape)) if deterministic else 0))
     args = DirtBackwardArgs(
         shape, faces.data_ptr(), _bstride(faces, B),
-        pixels.data_ptr(), grad_pixels.data_ptr(), face_id.data_ptr(), gbuffer.data_ptr(),
+        pixels.data_ptr(), grad_pixels.data_ptr(),
+        None if face_id is None else face_id.data_ptr(), None if gbuffer is None else gbuffer.data_ptr(),
         gv.data_ptr(), 0 if (shared_vertices and B > 1) else V * 4,
         gc.data_ptr(), 0 if (shared_colors and B > 1) else V * C,
-        gbg.data_ptr() if want_grad_background else None)
+        gbg.data_ptr() if want_grad_background else None,
+        vertices.data_ptr() if stateless else None, _bstride(vertices, B) if stateless else 0,
+        ws.data_ptr() if ws is not None else None, ws.numel() if ws is not None else 0,
+        _lib.BACKWARD_DETERMINISTIC if deterministic else 0)
     with torch.cuda.device(device):
         _lib.check(lib.dirt_rasterise_backward(ctypes.byref(args), torch.cuda.current_stream(device).cuda_stream))
     return gv, gc, gbg
 
 
-def backward_shared_raw(faces, pixels, grad_pixels, face_id, gbuffer, V, clip_from_world, want_grad_background=True):
+def backward_shared_raw(faces, pixels, grad_pixels, face_id, gbuffer, V, clip_from_world, want_grad_background=True,
+                        deterministic=False):
     """Shared-mesh backward: one C-ABI call that folds every element's
     clip-space vertex gradient to world space with its matrix (clip_b = world @ M_b) and sums
     position and colour gradients over the batch into ONE packed buffer [V, stride]: columns 0..3
@@ -172,10 +220,14 @@ def backward_shared_raw(faces, pixels, grad_pixels, face_id, gbuffer, V, clip_fr
     m = clip_from_world.to(torch.float32).contiguous()
     if tuple(m.shape) != (B, 4, 4):
         raise _lib.InvalidArgumentError(-1, "clip_from_world must be [batch, 4, 4]")
+    shape = DirtShape(B, H, W, C, V, F)
+    ws = _workspace(device, lib.dirt_deterministic_workspace_bytes(ctypes.byref(shape))) if deterministic else None
     args = _lib.DirtSharedBackwardArgs(
-        DirtShape(B, H, W, C, V, F), faces.data_ptr(), _bstride(faces, B),
+        shape, faces.data_ptr(), _bstride(faces, B),
         pixels.data_ptr(), grad_pixels.data_ptr(), face_id.data_ptr(), gbuffer.data_ptr(),
-        m.data_ptr(), packed.data_ptr(), gbg.data_ptr() if want_grad_background else None)
+        m.data_ptr(), packed.data_ptr(), gbg.data_ptr() if want_grad_background else None,
+        ws.data_ptr() if deterministic else None, ws.numel() if deterministic else 0,
+        _lib.BACKWARD_DETERMINISTIC if deterministic else 0)
     with torch.cuda.device(device):
         _lib.check(lib.dirt_rasterise_backward_shared(ctypes.byref(args), torch.cuda.current_stream(device).cuda_stream))
     return packed, gbg
@@ -189,7 +241,7 @@ class _Rasterise(torch.autograd.Function):
     def forward(ctx, background, vertices, vertex_colors, faces):
         need_grad = any(ctx.needs_input_grad[:3])
         ctx.bg_on_host = not background.is_cuda
-        pixels, face_id, gbuffer = forward_raw(background, vertices, vertex_colors, faces, want_aux=need_grad)
+        pixels, face_id, gbuffer = forward_raw(background, vertices, vertex_colors, faces, want_aux=need_grad, hint="auto")
         if need_grad:
             ctx.save_for_backward(faces, pixels, face_id, gbuffer)
             ctx.meta = (background.shape[0], vertices.shape[0], vertex_colors.shape[0], vertices.shape[1])
@@ -203,7 +255,7 @@ class _Rasterise(torch.autograd.Function):
         grad_pixels = grad_pixels.contiguous().to(torch.float32)
         gv, gc, gbg = backward_raw(faces, pixels, grad_pixels, face_id, gbuffer, V,
                                    shared_vertices=(v_b == 1 and B > 1), shared_colors=(c_b == 1 and B > 1),
-                                   want_grad_background=ctx.needs_input_grad[0])
+                                   want_grad_background=ctx.needs_input_grad[0], deterministic=deterministic_default())
         if gbg is not None and bg_b == 1 and B > 1:
             gbg = gbg.sum(dim=0, keepdim=True)
         if gbg is not None and ctx.bg_on_host:
@@ -269,7 +321,7 @@ class _RasteriseShared(torch.autograd.Function):
         need_grad = any(ctx.needs_input_grad)
         ctx.bg_on_host = not background.is_cuda
         pixels, face_id, gbuffer = forward_raw(background, vertices, vertex_colors.unsqueeze(0), faces.unsqueeze(0),
-                                               want_aux=need_grad)
+                                               want_aux=need_grad, hint="auto")
         if need_grad:
             ctx.save_for_backward(faces, pixels, face_id, gbuffer, clip_from_world)
             ctx.meta = (world_vertices.shape[0], background.shape[0])
@@ -281,7 +333,8 @@ class _RasteriseShared(torch.autograd.Function):
         V, bg_b = ctx.meta
         C = pixels.shape[-1]
         packed, gbg = backward_shared_raw(faces.unsqueeze(0), pixels, grad_pixels.contiguous().to(torch.float32), face_id,
-                                          gbuffer, V, clip_from_world, want_grad_background=ctx.needs_input_grad[0])
+                                          gbuffer, V, clip_from_world, want_grad_background=ctx.needs_input_grad[0],
+                                          deterministic=deterministic_default())
         if gbg is not None and bg_b == 1 and pixels.shape[0] > 1:
             gbg = gbg.sum(dim=0, keepdim=True)
         if gbg is not None and ctx.bg_on_host:

@@ -51,7 +51,7 @@ def _scene_batch(scene, background, vertices, vertex_colors, faces, camera_pos, 
     else:
         bg, v, c, f = rasterise_ops._prepare(background, vertices, vertex_colors, faces, batched, height, width, channels)
         tex = bg
-    cam = rasterise_ops._as_tensor(camera_pos, torch.float32, bg.device, "camera_pos").reshape(-1).contiguous()
+    cam = rasterise_ops._as_tensor(camera_pos, torch.float32, v.device, "camera_pos").reshape(-1).contiguous()      # bg may be pinned host memory
     need = lib.dirt_scene_camera_floats(scene)
     if cam.numel() < need:
         raise _lib.InvalidArgumentError(-1, "this scene op expects camera_pos to hold at least %d values" % need)
@@ -64,9 +64,9 @@ def _scene_batch(scene, background, vertices, vertex_colors, faces, camera_pos, 
                 _lib.DirtShape(B, H, W, C, v.shape[1], f.shape[1]),
                 tex.data_ptr(), bs(tex, B), v.data_ptr(), bs(v, B), f.data_ptr(), bs(f, B),
                 face_id.data_ptr(), gbuffer.data_ptr(), cam.data_ptr(), pixels.data_ptr())
-            with torch.cuda.device(bg.device):
+            with torch.cuda.device(v.device):
                 _lib.check(lib.dirt_scene_shade(scene, ctypes.byref(args), int(tex.shape[3]), int(cam.numel()),
-                                                torch.cuda.current_stream(bg.device).cuda_stream))
+                                                torch.cuda.current_stream(v.device).cuda_stream))
     return pixels
 
 

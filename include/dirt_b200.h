@@ -36,7 +36,7 @@ extern "C" {
 #define DIRT_API
 #endif
 
-#define DIRT_B200_ABI_VERSION 1
+#define DIRT_B200_ABI_VERSION 2          /* 2: DirtForwardArgs.visibility_hint, DirtBackwardArgs recompute inputs */
 #define DIRT_MAX_CHANNELS 16          /* reference: channels in {1,3} (csrc/hwc.h:27); wider
                                          attribute sets serve deferred G-buffers in one call */
 
@@ -81,6 +81,16 @@ typedef struct DirtForwardArgs {
     float *gbuffer;               /* out [B,H,W,4]                                         */
     void *workspace;              /* device scratch, >= dirt_workspace_bytes(&shape)       */
     size_t workspace_bytes;
+    /* Optional visibility hint: caller-owned DEVICE memory of >= dirt_visibility_hint_bytes(&shape)
+     * bytes that PERSISTS between calls which render the same mesh (same B and F) with slowly
+     * changing vertices -- the inverse-rendering loop of tests/optimize_sequence.py:293-352.  Every
+     * call records which faces won a pixel; the next call samples those faces first and tests all
+     * others against the nearly final depth buffer they leave.  The hint only ORDERS work: the
+     * output is bit-identical with a fresh, a stale or a wrong hint, or none (NULL).  Zero it once
+     * after allocating (any content is safe, zero merely avoids a slow first call); one buffer per
+     * mesh and per stream, not shared between calls in flight.  Used by meshes of >= 4096 faces. */
+    void *visibility_hint;
+    size_t visibility_hint_bytes;
 } DirtForwardArgs;
 
 /* Backward arguments.  Replaces launch_grad_assembly (declared, never defined, in the fork:
@@ -98,7 +108,20 @@ typedef struct DirtBackwardArgs {
     float *grad_vertices;         int64_t grad_vertices_bstride;      /* out [B,V,4]       */
     float *grad_vertex_colors;    int64_t grad_vertex_colors_bstride; /* out [B,V,C]       */
     float *grad_background;       /* out [B,H,W,C]; may be NULL                            */
+    /* Stateless mode, as the reference's graph sees the op pair (RasteriseGrad receives the forward's
+     * INPUTS, csrc/rasterise_grad_egl.cpp:38-42, and re-renders what it needs): with face_id == NULL
+     * and gbuffer == NULL the backward re-derives both from `vertices` and `faces` with the forward's
+     * own kernels into `workspace` (>= dirt_backward_workspace_bytes(&shape)) -- identical values, no
+     * buffer carried from the forward.  Ignored when face_id / gbuffer are given. */
+    const float *vertices;        int64_t vertices_bstride;      /* [B,V,4] clip space     */
+    void *workspace;              size_t workspace_bytes;
+    /* DIRT_BACKWARD_DETERMINISTIC: bit-identical gradients from run to run (the default sums with fp32
+     * atomics, whose order varies: reproducible to ~1e-6 relative only).  A debugging mode, about three
+     * times slower; needs `workspace` of dirt_deterministic_workspace_bytes(&shape) more bytes (after the
+     * dirt_backward_workspace_bytes of the stateless mode, when both are used). */
+    uint32_t flags;
 } DirtBackwardArgs;
+#define DIRT_BACKWARD_DETERMINISTIC 1u
 
 /* Shared-mesh backward: every batch element renders the SAME mesh, element b
  * through its own matrix (clip_b = world @ M_b, row vectors: the convention of dirt/matrices.py and
@@ -118,6 +141,8 @@ typedef struct DirtSharedBackwardArgs {
     const float *clip_from_world; /* [B,4,4] row-major M_b                                 */
     float *grad_shared;           /* out [V, stride], 16-byte aligned, zeroed by the callee */
     float *grad_background;       /* out [B,H,W,C]; may be NULL                            */
+    void *workspace;              size_t workspace_bytes;        /* only for DIRT_BACKWARD_DETERMINISTIC */
+    uint32_t flags;
 } DirtSharedBackwardArgs;
 DIRT_API int dirt_shared_grad_stride(int channels);
 DIRT_API int dirt_rasterise_backward_shared(const DirtSharedBackwardArgs *args, void *stream);
@@ -148,6 +173,22 @@ DIRT_API const char *dirt_last_error(void);
  * keeps per GL thread (csrc/rasterise_egl.cpp:73-89, :199-274, :347-354); here the caller
  * owns it, so torch's / TF's caching allocator can. */
 DIRT_API size_t dirt_workspace_bytes(const DirtShape *shape);
+
+/* Scratch of the backward's stateless mode (face_id == gbuffer == NULL): the forward's workspace plus
+ * the two per-pixel buffers it re-derives. */
+DIRT_API size_t dirt_backward_workspace_bytes(const DirtShape *shape);
+/* Extra scratch of DIRT_BACKWARD_DETERMINISTIC (64-bit fixed-point accumulators, one per gradient value). */
+DIRT_API size_t dirt_deterministic_workspace_bytes(const DirtShape *shape);
+/* Convenience for callers without an allocator of their own (C programs): a workspace of
+ * max(dirt_workspace_bytes, dirt_backward_workspace_bytes)(shape) bytes on the current device, and its
+ * release.  Counterpart of the reference's per-thread grow-only buffers (csrc/rasterise_egl.cpp:73-89). */
+DIRT_API int dirt_workspace_create(const DirtShape *shape, void **workspace, size_t *workspace_bytes);
+DIRT_API int dirt_workspace_destroy(void *workspace);
+
+/* Size of DirtForwardArgs.visibility_hint for `shape` (one byte per face and batch element plus a
+ * 256-byte header); 0 for an invalid shape.  No reference counterpart: the reference's GL driver
+ * keeps no state between draws either (csrc/rasterise_egl.cpp:440-458 redraws from scratch). */
+DIRT_API size_t dirt_visibility_hint_bytes(const DirtShape *shape);
 
 /* Forward: replaces op "Rasterise" (REGISTER_OP csrc/rasterise_egl.cpp:33-53; kernel :284-514;
  * upload_background / download_pixels csrc/rasterise_egl.cu:16-129 are folded in).
@@ -236,7 +277,9 @@ DIRT_API uint64_t dirt_kernel_launch_count(void);
  *   dirt_profile_read()     -> cumulative milliseconds and timed runs per stage (a stage that
  *                              runs several times per call, e.g. one setup launch per depth
  *                              bucket, counts each run)
- * Stage order: see dirt_profile_stage_name(i), i in [0, DIRT_STAGE_COUNT). */
+ * Stage order: see dirt_profile_stage_name(i), i in [0, DIRT_STAGE_COUNT).
+ * The timer is ONE per process: profile from a single thread on a single device (the one current at
+ * dirt_profile_enable(1)); dirt_profile_enable refuses other devices while it is on. */
 #define DIRT_STAGE_COUNT 12
 DIRT_API int dirt_profile_enable(int enable);
 DIRT_API int dirt_profile_collect(void);

@@ -6,6 +6,7 @@
  *
  *   gcc -std=c99 -Iinclude samples/c_caller.c -Ldirt_b200 -ldirt_b200 -Wl,-rpath,$PWD/dirt_b200 -o c_caller
  */
+#include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -67,6 +68,22 @@ int main(void)
         fprintf(stderr, "backward: %s\n", dirt_last_error());
         return 1;
     }
+    /* the same backward in its stateless form: no face_id / gbuffer from the forward, visibility is re-derived
+     * from the vertices (what the TF op pair does: RasteriseGrad receives the forward's inputs) */
+    static float grad_colours2[4], grad_vertices2[16];
+    DirtBackwardArgs bwd2 = bwd;
+    bwd2.face_id = NULL; bwd2.gbuffer = NULL;
+    bwd2.vertices = vertices; bwd2.vertices_bstride = V * 4;
+    bwd2.grad_vertices = grad_vertices2; bwd2.grad_vertex_colors = grad_colours2;
+    if (dirt_rasterise_backward_host(&bwd2) != DIRT_STATUS_OK) {
+        fprintf(stderr, "stateless backward: %s\n", dirt_last_error());
+        return 1;
+    }
+    int same = 1;       /* equal up to the summation order of the fp32 atomics */
+    for (int k = 0; k < V; ++k) same = same && fabsf(grad_colours2[k] - grad_colours[k]) <= 1e-3f;
+    for (int k = 0; k < 4 * V; ++k) same = same && fabsf(grad_vertices2[k] - grad_vertices[k]) <= 1e-3f * (1.f + fabsf(grad_vertices[k]));
+    printf("stateless backward %s the one fed with the forward's buffers\n", same ? "matches" : "DIFFERS FROM");
+    if (!same) return 1;
     float sum = 0.f;
     for (int k = 0; k < V; ++k) sum += grad_colours[k];
     printf("grad_vertex_colors: %.3f %.3f %.3f %.3f (sum %.3f, expected 256)\n",

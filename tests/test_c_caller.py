@@ -16,7 +16,7 @@ def _build(tmp_path):
     exe = str(tmp_path / "c_caller")
     cmd = ["gcc", "-std=c99", "-Wall", "-Wextra", "-Werror", "-pedantic", "-I" + os.path.join(ROOT, "include"),
            os.path.join(ROOT, "samples", "c_caller.c"), "-L" + os.path.dirname(lib), "-ldirt_b200",
-           "-Wl,-rpath," + os.path.dirname(lib), "-o", exe]
+           "-Wl,-rpath," + os.path.dirname(lib), "-lm", "-o", exe]
     subprocess.check_call(cmd)
     return exe
 
@@ -39,3 +39,4 @@ def test_c_caller_renders_the_readme_square(tmp_path):
     r = subprocess.run([exe], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "covered pixels: 256 (expected 256), mismatches: 0" in r.stdout
+    assert "stateless backward matches" in r.stdout

@@ -60,3 +60,17 @@ def test_cuda_scene_matches_oracle(cam, C, noise):
     # unbatched form, the fork's call shape
     one = dirt_b200.oceanic_horizon(torch.from_numpy(bg[0]).cuda(), v[0], c[0], f[0], np.array(cam, np.float32))
     assert np.array_equal(one.cpu().numpy(), out[0])
+
+
+@pytest.mark.gpu
+def test_scene_op_with_a_pinned_host_background():
+    """the rasterise path reads a pinned host background in place; the scene ops must take their
+    device from the vertices, not from that background."""
+    import torch
+    import dirt_b200
+    B, H, W, C = 2, 60, 96, 3
+    bg, v, c, f = quad_scene(B, H, W, C, seed=2, noise=0.3)
+    dev = [torch.from_numpy(a).cuda() for a in (bg, v, c, f)]
+    ref = dirt_b200.oceanic_horizon_batch(dev[0], dev[1], dev[2], dev[3], CAMS[1])
+    out = dirt_b200.oceanic_horizon_batch(torch.from_numpy(bg).pin_memory(), dev[1], dev[2], dev[3], CAMS[1])
+    assert out.is_cuda and torch.equal(out, ref)

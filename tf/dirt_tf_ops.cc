@@ -1,4 +1,4 @@
-// dirt_tf_ops.cc -- TensorFlow shim: re-registers ops "Rasterise" and "RasteriseGrad" on top of
+// dirt_tf_ops.cc -- TensorFlow shim (UNCOMPILED here: no TensorFlow in this image): re-registers ops "Rasterise" and "RasteriseGrad" on top of
 // libdirt_b200.so's C ABI (include/dirt_b200.h), with the attrs / input order / output of the
 // reference registration (csrc/rasterise_egl.cpp:33-53, :520; csrc/rasterise_grad_egl.cpp:33-53),
 // so that `tf.load_op_library` in dirt/rasterise_ops.py:6-7 keeps working unchanged.
@@ -34,10 +34,10 @@ void *cuda_stream_of(OpKernelContext *ctx)
     return *reinterpret_cast<void **>(ctx->op_device_context()->stream()->implementation()->GpuStreamMemberHack());
 }
 
-DirtShape shape_of(const Tensor &background, const Tensor &vertices, const Tensor &faces, int channels)
+DirtShape shape_of(const Tensor &background, const Tensor &vertices, const Tensor &faces, int channels, int64 batch)
 {
     DirtShape s;
-    s.batch = static_cast<int32_t>(vertices.dim_size(0));
+    s.batch = static_cast<int32_t>(batch);
     s.height = static_cast<int32_t>(background.dim_size(1));
     s.width = static_cast<int32_t>(background.dim_size(2));
     s.channels = channels;
@@ -46,23 +46,39 @@ DirtShape shape_of(const Tensor &background, const Tensor &vertices, const Tenso
     return s;
 }
 
+// The batch of a call is the largest leading dim of its inputs; every input must have that leading dim or 1
+// (1 broadcasts: the relaxation wished for at csrc/rasterise_egl.cpp:334, whose check this generalises).
+bool common_batch(std::initializer_list<const Tensor *> ts, int64 *batch)
+{
+    int64 B = 0;
+    for (const Tensor *t : ts) B = std::max<int64>(B, t->dim_size(0));
+    for (const Tensor *t : ts)
+        if (t->dim_size(0) != B && t->dim_size(0) != 1) return false;
+    *batch = B;
+    return true;
+}
+
+int64_t batch_stride(const Tensor &t, int64 B)
+{
+    return t.dim_size(0) == 1 && B > 1 ? 0 : t.NumElements() / std::max<int64>(t.dim_size(0), 1);
+}
+
 }  // namespace
 
-// Same registration as csrc/rasterise_egl.cpp:33-53, plus two optional outputs the gradient needs.
+// The registration of csrc/rasterise_egl.cpp:33-53, unchanged: five inputs, ONE output.  The per-pixel state the
+// backward needs is not an output: RasteriseGrad re-derives it from the forward's inputs (stateless mode of
+// dirt_rasterise_backward), the way the reference's graph sees the pair (csrc/rasterise_grad_egl.cpp:38-42).
 REGISTER_OP("Rasterise")
     .Attr("height: int").Attr("width: int").Attr("channels: int = 3")
     .Input("background: float32").Input("vertices: float32").Input("vertex_colors: float32")
     .Input("faces: int32").Input("camera_pos: float32")
-    .Output("pixels: float32").Output("face_id: int32").Output("gbuffer: float32")
+    .Output("pixels: float32")
     .SetShapeFn([](shape_inference::InferenceContext *c) {
         int h, w, ch;
         TF_RETURN_IF_ERROR(c->GetAttr("height", &h));
         TF_RETURN_IF_ERROR(c->GetAttr("width", &w));
         TF_RETURN_IF_ERROR(c->GetAttr("channels", &ch));
-        auto b = c->Dim(c->input(1), 0);
-        c->set_output(0, c->MakeShape({b, h, w, ch}));
-        c->set_output(1, c->MakeShape({b, h, w}));
-        c->set_output(2, c->MakeShape({b, h, w, 4}));
+        c->set_output(0, c->MakeShape({c->Dim(c->input(1), 0), h, w, ch}));      // as csrc/rasterise_egl.cpp:44-52
         return Status::OK();
     });
 
@@ -77,30 +93,27 @@ public:
     void Compute(OpKernelContext *ctx) override
     {
         const Tensor &bg = ctx->input(0), &v = ctx->input(1), &col = ctx->input(2), &f = ctx->input(3);
-        // rank checks of csrc/rasterise_egl.cpp:310-321 (the C ABI re-checks extents and strides)
+        // the checks of csrc/rasterise_egl.cpp:310-336, message for message (the C ABI re-checks extents and strides)
         OP_REQUIRES(ctx, bg.dims() == 4 && bg.dim_size(1) == height_ && bg.dim_size(2) == width_ && bg.dim_size(3) == channels_,
                     errors::InvalidArgument("Rasterise expects background_tensor to be 4D, and bgcolor.shape == [None, height, width, channels]"));
         OP_REQUIRES(ctx, v.dims() == 3 && v.dim_size(2) == 4, errors::InvalidArgument("Rasterise expects vertices to be 3D, and vertices.shape[2] == 4"));
         OP_REQUIRES(ctx, col.dims() == 3 && col.dim_size(1) == v.dim_size(1) && col.dim_size(2) == channels_,
                     errors::InvalidArgument("Rasterise expects vertex_colors to be 3D, and vertex_colors.shape == [None, vertices.shape[1], channels]"));
         OP_REQUIRES(ctx, f.dims() == 3 && f.dim_size(2) == 3, errors::InvalidArgument("Rasterise expects faces to be 3D, and faces.shape[2] == 3"));
+        int64 B = 0;
+        OP_REQUIRES(ctx, common_batch({&bg, &v, &col, &f}, &B),
+                    errors::InvalidArgument("Rasterise expects all arguments to have same leading (batch) dimension"));
         DirtForwardArgs a = {};
-        a.shape = shape_of(bg, v, f, channels_);
-        const int64 B = a.shape.batch;
-        auto stride = [B](const Tensor &t) -> int64_t { return t.dim_size(0) == 1 && B > 1 ? 0 : t.NumElements() / std::max<int64>(t.dim_size(0), 1); };
-        a.background = bg.flat<float>().data();        a.background_bstride = stride(bg);
-        a.vertices = v.flat<float>().data();           a.vertices_bstride = stride(v);
-        a.vertex_colors = col.flat<float>().data();    a.vertex_colors_bstride = stride(col);
-        a.faces = f.flat<int32>().data();              a.faces_bstride = stride(f);
-        Tensor *pixels, *face_id, *gbuffer, ws;
+        a.shape = shape_of(bg, v, f, channels_, B);
+        a.background = bg.flat<float>().data();        a.background_bstride = batch_stride(bg, B);
+        a.vertices = v.flat<float>().data();           a.vertices_bstride = batch_stride(v, B);
+        a.vertex_colors = col.flat<float>().data();    a.vertex_colors_bstride = batch_stride(col, B);
+        a.faces = f.flat<int32>().data();              a.faces_bstride = batch_stride(f, B);
+        Tensor *pixels, ws;
         OP_REQUIRES_OK(ctx, ctx->allocate_output(0, {B, height_, width_, channels_}, &pixels));
-        OP_REQUIRES_OK(ctx, ctx->allocate_output(1, {B, height_, width_}, &face_id));
-        OP_REQUIRES_OK(ctx, ctx->allocate_output(2, {B, height_, width_, 4}, &gbuffer));
         a.workspace_bytes = dirt_workspace_bytes(&a.shape);
         OP_REQUIRES_OK(ctx, ctx->allocate_temp(DT_UINT8, {static_cast<int64>(a.workspace_bytes)}, &ws));
         a.pixels = pixels->flat<float>().data();
-        a.face_id = face_id->flat<int32>().data();
-        a.gbuffer = gbuffer->flat<float>().data();
         a.workspace = ws.flat<uint8>().data();
         OP_REQUIRES_OK(ctx, status_from(dirt_rasterise_forward(&a, cuda_stream_of(ctx))));
     }
@@ -109,11 +122,11 @@ private:
 };
 REGISTER_KERNEL_BUILDER(Name("Rasterise").Device(DEVICE_GPU), RasteriseOpB200);   // GPU only, as csrc/rasterise_egl.cpp:520
 
-// The intended backward (csrc/rasterise_grad_common.h:19-24): G-buffer + pixels + grad_pixels in,
-// grad_vertices / grad_vertex_colors / grad_background out.
+// The intended backward (csrc/rasterise_grad_common.h:19-24): the forward's vertices and faces, its output and the
+// incoming gradient in; grad_background / grad_vertices / grad_vertex_colors out.  Stateless: nothing but graph
+// tensors connects it to the forward op.
 REGISTER_OP("RasteriseGrad")
-    .Input("faces: int32").Input("pixels: float32").Input("grad_pixels: float32")
-    .Input("face_id: int32").Input("gbuffer: float32").Input("vertices: float32")
+    .Input("vertices: float32").Input("faces: int32").Input("pixels: float32").Input("grad_pixels: float32")
     .Output("grad_background: float32").Output("grad_vertices: float32").Output("grad_vertex_colors: float32");
 
 class RasteriseGradOpB200 : public OpKernel {
@@ -121,22 +134,27 @@ public:
     using OpKernel::OpKernel;
     void Compute(OpKernelContext *ctx) override
     {
-        const Tensor &f = ctx->input(0), &px = ctx->input(1), &g = ctx->input(2), &fid = ctx->input(3), &gb = ctx->input(4),
-                     &v = ctx->input(5);
+        const Tensor &v = ctx->input(0), &f = ctx->input(1), &px = ctx->input(2), &g = ctx->input(3);
         OP_REQUIRES(ctx, px.dims() == 4 && g.shape() == px.shape(), errors::InvalidArgument("RasteriseGrad expects pixels and grad_pixels of one 4D shape"));
+        OP_REQUIRES(ctx, v.dims() == 3 && v.dim_size(2) == 4, errors::InvalidArgument("RasteriseGrad expects vertices to be 3D, and vertices.shape[2] == 4"));
+        OP_REQUIRES(ctx, f.dims() == 3 && f.dim_size(2) == 3, errors::InvalidArgument("RasteriseGrad expects faces to be 3D, and faces.shape[2] == 3"));
+        int64 B = 0;
+        OP_REQUIRES(ctx, common_batch({&px, &v, &f}, &B) && px.dim_size(0) == B,
+                    errors::InvalidArgument("RasteriseGrad expects vertices and faces to have the leading (batch) dimension of pixels, or 1"));
         DirtBackwardArgs a = {};
-        a.shape = shape_of(px, v, f, static_cast<int>(px.dim_size(3)));
-        a.shape.batch = static_cast<int32_t>(px.dim_size(0));
-        const int64 B = a.shape.batch, V = a.shape.vertex_count, C = a.shape.channels;
-        a.faces = f.flat<int32>().data();
-        a.faces_bstride = f.dim_size(0) == 1 && B > 1 ? 0 : int64_t(a.shape.face_count) * 3;
+        a.shape = shape_of(px, v, f, static_cast<int>(px.dim_size(3)), B);
+        const int64 V = a.shape.vertex_count, C = a.shape.channels;
+        a.faces = f.flat<int32>().data();              a.faces_bstride = batch_stride(f, B);
+        a.vertices = v.flat<float>().data();           a.vertices_bstride = batch_stride(v, B);
         a.pixels = px.flat<float>().data(); a.grad_pixels = g.flat<float>().data();
-        a.face_id = fid.flat<int32>().data(); a.gbuffer = gb.flat<float>().data();
         const int64 Bv = v.dim_size(0);            // 1 = shared mesh: gradients summed over the batch
-        Tensor *gbg, *gv, *gc;
+        Tensor *gbg, *gv, *gc, ws;
         OP_REQUIRES_OK(ctx, ctx->allocate_output(0, px.shape(), &gbg));
         OP_REQUIRES_OK(ctx, ctx->allocate_output(1, {Bv, V, 4}, &gv));
         OP_REQUIRES_OK(ctx, ctx->allocate_output(2, {Bv, V, C}, &gc));
+        a.workspace_bytes = dirt_backward_workspace_bytes(&a.shape);
+        OP_REQUIRES_OK(ctx, ctx->allocate_temp(DT_UINT8, {static_cast<int64>(a.workspace_bytes)}, &ws));
+        a.workspace = ws.flat<uint8>().data();
         a.grad_background = gbg->flat<float>().data();
         a.grad_vertices = gv->flat<float>().data();            a.grad_vertices_bstride = Bv == 1 && B > 1 ? 0 : V * 4;
         a.grad_vertex_colors = gc->flat<float>().data();       a.grad_vertex_colors_bstride = Bv == 1 && B > 1 ? 0 : V * C;
@@ -165,10 +183,12 @@ public:
                     errors::InvalidArgument("Rasterise expects background_tensor to be 4D, and bgcolor.shape == [None, height, width, channels]"));
         OP_REQUIRES(ctx, v.dims() == 3 && v.dim_size(2) == 4, errors::InvalidArgument("Rasterise expects vertices to be 3D, and vertices.shape[2] == 4"));
         OP_REQUIRES(ctx, f.dims() == 3 && f.dim_size(2) == 3, errors::InvalidArgument("Rasterise expects faces to be 3D, and faces.shape[2] == 3"));
+        int64 B = 0;
+        OP_REQUIRES(ctx, common_batch({&bg, &v, &col, &f}, &B),
+                    errors::InvalidArgument("Rasterise expects all arguments to have same leading (batch) dimension"));
         DirtForwardArgs a = {};
-        a.shape = shape_of(bg, v, f, channels_);
-        const int64 B = a.shape.batch;
-        auto stride = [B](const Tensor &t) -> int64_t { return t.dim_size(0) == 1 && B > 1 ? 0 : t.NumElements() / std::max<int64>(t.dim_size(0), 1); };
+        a.shape = shape_of(bg, v, f, channels_, B);
+        auto stride = [B](const Tensor &t) -> int64_t { return batch_stride(t, B); };
         Tensor *pixels, face_id, gbuffer, ws, blank;
         OP_REQUIRES_OK(ctx, ctx->allocate_output(0, {B, height_, width_, channels_}, &pixels));
         OP_REQUIRES_OK(ctx, ctx->allocate_temp(DT_INT32, {B, height_, width_}, &face_id));
