@@ -75,6 +75,8 @@ EXPORTS = {
     "dirt_workspace_create": (ctypes.c_int, [ctypes.POINTER(DirtShape), ctypes.POINTER(ctypes.c_void_p), ctypes.POINTER(ctypes.c_size_t)]),
     "dirt_workspace_destroy": (ctypes.c_int, [ctypes.c_void_p]),
     "dirt_rasterise_forward": (ctypes.c_int, [ctypes.POINTER(DirtForwardArgs), ctypes.c_void_p]),
+    "dirt_noalloc_workspace_limit": (ctypes.c_size_t, []),
+    "dirt_rasterise_forward_noalloc": (ctypes.c_int, [ctypes.POINTER(DirtForwardArgs), ctypes.c_void_p]),
     "dirt_rasterise_backward": (ctypes.c_int, [ctypes.POINTER(DirtBackwardArgs), ctypes.c_void_p]),
     "dirt_shared_grad_stride": (ctypes.c_int, [ctypes.c_int]),
     "dirt_rasterise_backward_shared": (ctypes.c_int, [ctypes.POINTER(DirtSharedBackwardArgs), ctypes.c_void_p]),

@@ -195,6 +195,19 @@ DIRT_API size_t dirt_visibility_hint_bytes(const DirtShape *shape);
  * `stream` is a cudaStream_t passed as void* (NULL = legacy default stream). */
 DIRT_API int dirt_rasterise_forward(const DirtForwardArgs *args, void *stream);
 
+/* Forward without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it).  Same arguments and results as dirt_rasterise_forward, except that
+ * args->workspace / workspace_bytes are IGNORED: the scratch is a file-scope device array inside the
+ * library (DIRT_NOALLOC_WORKSPACE_BYTES, held by every GPU that loads the library until exit).  Shapes
+ * whose dirt_workspace_bytes() exceeds it are rejected with DIRT_STATUS_UNSUPPORTED and a message; the
+ * call itself issues no cudaMalloc / cudaFree.  All calls on a device share the array and it keeps the
+ * last call's contents (what must start empty is cleared by every call): calls that overlap on the GPU
+ * race -- serialise them, or use dirt_rasterise_forward with a workspace per stream. */
+#define DIRT_NOALLOC_WORKSPACE_BYTES (8u << 20)   /* 8 MiB: e.g. one 512x512 frame of a 100k-face mesh */
+DIRT_API size_t dirt_noalloc_workspace_limit(void);
+DIRT_API int dirt_rasterise_forward_noalloc(const DirtForwardArgs *args, void *stream);
+
 /* Backward: replaces op "RasteriseGrad" in its intended role (csrc/rasterise_grad_egl.cpp:33-53
  * carries the name; csrc/rasterise_grad_common.h:13-24 the intended kernels). */
 DIRT_API int dirt_rasterise_backward(const DirtBackwardArgs *args, void *stream);
