@@ -8,8 +8,8 @@ shard (weak scaling, no data-path collective; the `c5` shared-mesh workload adds
 allreduce of the vertex gradients).
 
   value         whole-job Mpix/s, inputs resident in HBM, CUDA events, max over ranks.  The geometry MOVES
-                between steps (4 pre-uploaded vertex sets, 0.25 degrees apart) and the forward carries
-                its visibility hint from call to call; --static / --no-hint give the round-1 protocol
+                between steps (4 pre-uploaded vertex sets, 0.25 degrees apart); --static gives the
+                round-1 protocol, --hint carries the visibility hint from call to call
   extra         c4 and c5 (with / without / overlapped allreduce) device-resident, and the e2e through
                 the host-buffer C ABI
   e2e           same metric through the public API with pinned HOST inputs: H2D of the step's
@@ -356,7 +356,7 @@ def run_ours(args, wl, rank, world, local_rank):
     dev_frames = [h.to(dev) for h in host_frames]
     order = frame_order(len(dev_frames))
     nframes = len(dev_frames)
-    hint = ops.visibility_hint(dev, B, F, key="bench") if (F >= ops.HINT_MIN_FACES and not args.no_hint) else None
+    hint = ops.visibility_hint(dev, B, F, key="bench") if (F >= ops.HINT_MIN_FACES and args.hint) else None
 
     def step(i):
         v = dev_frames[order[i % len(order)]]
@@ -433,7 +433,25 @@ def run_ours(args, wl, rank, world, local_rank):
     # that cross the bus are counted below from the step's own face-id map).
     in_keys = ("world", "matrices", "vertex_colors", "faces") if shared else ("vertices", "vertex_colors", "faces")
     s_in, s_out, s_main = torch.cuda.Stream(dev), torch.cuda.Stream(dev), torch.cuda.current_stream(dev)
-    dev_in = [{k: torch.empty_like(d[k]) for k in in_keys} for _ in range(2)]
+    # The step's inputs live in ONE pinned staging block per frame (the caller's upload arena) and cross the bus
+    # with ONE cudaMemcpyAsync; the device side is one block per buffer set, the tensors are views into it.
+    def carve(block, like):
+        views, off = {}, 0
+        for k in in_keys:
+            n = like[k].numel() * like[k].element_size()
+            views[k] = block[off:off + n].view(like[k].dtype).view(like[k].shape)
+            off += (n + 255) // 256 * 256
+        return views
+    arena_bytes = sum((host[k].numel() * host[k].element_size() + 255) // 256 * 256 for k in in_keys)
+    host_arena = []
+    for fr in range(nframes):
+        blk = torch.empty(arena_bytes, dtype=torch.uint8).pin_memory()
+        vw = carve(blk, host)
+        for k in in_keys:
+            vw[k].copy_(host_frames[fr] if k == "vertices" else host[k])
+        host_arena.append(blk)
+    dev_arena = [torch.empty(arena_bytes, dtype=torch.uint8, device=dev) for _ in range(2)]
+    dev_in = [carve(a, host) for a in dev_arena]
     out_gv = [torch.empty((1 if shared else B, V, 4), dtype=torch.float32).pin_memory() for _ in range(2)]
     out_gc = [torch.empty((1 if shared else B, V, C), dtype=torch.float32).pin_memory() for _ in range(2)]
     out_loss = [torch.empty((), dtype=torch.float32).pin_memory() for _ in range(2)]
@@ -442,19 +460,23 @@ def run_ours(args, wl, rank, world, local_rank):
     done = [torch.cuda.Event() for _ in range(2)]
     losses = []
 
+    # what one upload moves: the whole block, or (second e2e figure) only the tensors that change from step to step --
+    # `in_keys` lists them first and the constant topology (faces) last, so that is a prefix of the block
+    upload_bytes = [arena_bytes]
+    e2e_bg = [host["background"]]          # pinned host tensor, read in place; the third figure keeps it resident
+
     def e2e_upload(i):
         slot = i % 2
         with torch.cuda.stream(s_in):
             s_in.wait_event(free[slot])                 # the step that last used this buffer set has finished
-            for k in in_keys:
-                src = host_frames[order[i % len(order)]] if k == "vertices" else host[k]
-                dev_in[slot][k].copy_(src, non_blocking=True)
+            n = upload_bytes[0]
+            dev_arena[slot][:n].copy_(host_arena[order[i % len(order)]][:n], non_blocking=True)
             ready[slot].record(s_in)
 
     def e2e_compute(i):
         slot = i % 2
         s_main.wait_event(ready[slot])
-        bg = host["background"]
+        bg = e2e_bg[0]
         if shared:
             v = dev_in[slot]["world"].detach().requires_grad_(True)
             c = dev_in[slot]["vertex_colors"][0].detach().requires_grad_(True)
@@ -515,13 +537,66 @@ def run_ours(args, wl, rank, world, local_rank):
            "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": e2e_steps, "last_loss": losses[-1],
            "path": ("dirt_b200.rasterise_batch_shared" if shared else "dirt_b200.rasterise_batch") +
                    " + autograd backward; each step uploads its inputs (that step's vertex set) from pinned host "
-                   "memory and downloads loss + gradients; double-buffered over copy/compute/copy streams" + bg_note}
+                   "memory (one staging block, one cudaMemcpyAsync per step) and downloads loss + gradients; double-buffered over "
+                   "copy/compute/copy streams" + bg_note}
 
     extra = {}
+    # ---- e2e of a loop that keeps the constant topology resident (faces uploaded once, as the reference's caller
+    #      holds them in a graph constant, tests/optimize_sequence.py:293-352): vertices and colours still cross every step
+    if not shared and not args.no_extras:
+        for slot in range(2):
+            dev_arena[slot].copy_(host_arena[0])         # faces now live in both buffer sets
+        torch.cuda.synchronize()
+        upload_bytes[0] = sum((host[k].numel() * host[k].element_size() + 255) // 256 * 256 for k in in_keys if k != "faces")
+        e2e_run(3)
+        barrier()
+        ev0.record()
+        e2e_run(e2e_steps)
+        ev1.record()
+        barrier()
+        ms_r = max_over_ranks(ev0.elapsed_time(ev1)) / e2e_steps
+        extra["e2e_resident_topology"] = {
+            "value": world * B * H * W / (ms_r * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms_r, "steps": e2e_steps,
+            "h2d_bytes_per_step": h2d - host["faces"].numel() * 4, "d2h_bytes_per_step": d2h,
+            "path": "as e2e, but `faces` is uploaded once and stays resident; every step still uploads its vertices and colours"}
+        # ... and of a loop in which only the optimised variable crosses the bus: vertices up, loss + gradients down;
+        # background, colours and faces resident (the reference's own loop feeds 8 floats per iteration and fetches the
+        # image, tests/optimize_sequence.py:158-166: everything else is a graph constant on the device)
+        upload_bytes[0] = (host["vertices"].numel() * 4 + 255) // 256 * 256
+        e2e_bg[0] = d["background"]
+        e2e_run(3)
+        barrier()
+        ev0.record()
+        e2e_run(e2e_steps)
+        ev1.record()
+        barrier()
+        ms_v = max_over_ranks(ev0.elapsed_time(ev1)) / e2e_steps
+        extra["e2e_vertices_only"] = {
+            "value": world * B * H * W / (ms_v * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms_v, "steps": e2e_steps,
+            "h2d_bytes_per_step": host["vertices"].numel() * 4, "d2h_bytes_per_step": d2h,
+            "path": "as e2e, but background, vertex_colors and faces stay resident; every step uploads its vertices and downloads loss + gradients"}
+        upload_bytes[0] = arena_bytes
+        e2e_bg[0] = host["background"]
+    # ---- the same timed loop with the visibility hint carried from call to call (the other setting of --hint) ----
+    if F >= ops.HINT_MIN_FACES and not shared and not args.no_extras:
+        other = None if hint is not None else ops.visibility_hint(dev, B, F, key="bench-other")
+
+        def step_other(i):
+            v = dev_frames[order[i % len(order)]]
+            px, fid, gb = ops.forward_raw(d["background"], v, d["vertex_colors"], d["faces"], want_aux=True, hint=other)
+            return ops.backward_raw(d["faces"], px, grad_pixels, fid, gb, V)
+
+        ms_o = time_steps(step_other, min(args.steps, 10), 4, barrier, max_over_ranks)
+        st_o, _ = stage_profile(step_other, 6)
+        extra["visibility_hint" if other is not None else "no_visibility_hint"] = {
+            "ms_per_step": ms_o, "value": world * B * H * W / (ms_o * 1e-3) / 1e6, "unit": UNIT,
+            "stages_ms": {k: v for k, v in st_o.items() if v > 0},
+            "note": "same loop, same moving geometry; stages: depth_order reads one flag per face instead of three projected corners, "
+                    "resolve includes the pass that stamps the visible faces"}
     # ---- e2e through the host-buffer C ABI (what a non-torch caller pays): every tensor crosses the bus ----
     if rank == 0 and not shared and not args.no_extras:
         extra["e2e_host_abi"] = host_abi_e2e(lib, host, host_frames, order, B, H, W, C, V, F)
-    del dev_in, out_gv, out_gc
+    del dev_in, dev_arena, host_arena, out_gv, out_gc
     # ---- the other device-resident configs of BASELINE.json, so that a driver-run number exists for them ----
     if args.workload == "headline" and not args.no_extras:
         del d, dev_frames, grad_pixels
@@ -550,8 +625,7 @@ def run_ours(args, wl, rank, world, local_rank):
         "config": {"workload": args.workload + ": " + wl["desc"], "batch_per_gpu": B, "height": H, "width": W, "channels": C,
                    "vertices": V, "faces": F,
                    "geometry": ("moves between steps: %d pre-uploaded vertex sets, each element's object turned a further %.2f deg "
-                                "(<= 0.7 px on screen) per frame, visited 0 1 2 3 2 1 0 ...; the forward carries its visibility "
-                                "hint from call to call" % (nframes, FRAME_STEP_DEG)) if moving
+                                "(<= 0.7 px on screen) per frame, visited 0 1 2 3 2 1 0 ...%s" % (nframes, FRAME_STEP_DEG, "; the forward carries its visibility hint from call to call" if hint is not None else "")) if moving
                                else "static (the same inputs every step)" + ("" if hint is None else "; visibility hint carried from call to call"),
                    "visibility_hint": hint is not None,
                    "sharding": ("frames across ranks; one packed all_reduce of [V,4+C] shared-mesh gradients per step" if shared
@@ -611,7 +685,7 @@ def extra_sphere(wl, args, rank, world, dev, barrier, max_over_ranks):
     frames = [d["vertices"]] + [torch.from_numpy(v).to(dev) for v in build_frames(wl, B, rank)]
     order = frame_order(len(frames))
     g = torch.randn((B, H, W, C), device=dev)
-    hint = None if args.no_hint else ops.visibility_hint(dev, B, F, key="bench-" + str(H))
+    hint = ops.visibility_hint(dev, B, F, key="bench-" + str(H)) if args.hint else None
 
     def step(i):
         px, fid, gb = ops.forward_raw(d["background"], frames[order[i % len(order)]], d["vertex_colors"], d["faces"], hint=hint)
@@ -692,7 +766,8 @@ def main():
     ap.add_argument("--workload", default="headline", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--static", action="store_true", help="identical inputs every step (round-1 protocol)")
-    ap.add_argument("--no-hint", action="store_true", help="do not carry the visibility hint between calls")
+    ap.add_argument("--hint", action="store_true", help="carry the visibility hint between calls in the timed loops (default: "
+                    "off -- measured no faster; extra.visibility_hint reports it)")
     ap.add_argument("--no-extras", action="store_true", help="skip extra.c4 / extra.c5 / extra.e2e_host_abi")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

@@ -88,6 +88,10 @@ EXPORTS = {
     "dirt_scene_shade": (ctypes.c_int, [ctypes.c_int, ctypes.POINTER(DirtSceneArgs), ctypes.c_int, ctypes.c_int, ctypes.c_void_p]),
     "dirt_vertex_normals": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 3 + [ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 3),
     "dirt_vertex_normals_grad": (ctypes.c_int, [ctypes.c_void_p] + [ctypes.c_int] * 3 + [ctypes.c_void_p, ctypes.c_int] + [ctypes.c_void_p] * 5),
+    "dirt_diffuse_directional": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, _i64, ctypes.c_void_p, _i64] +
+                                 [ctypes.c_int] * 4 + [ctypes.c_void_p, ctypes.c_void_p]),
+    "dirt_diffuse_directional_grad": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, _i64, ctypes.c_void_p, _i64] +
+                                      [ctypes.c_int] * 4 + [ctypes.c_void_p] * 4),
     "dirt_dilate_silhouette": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p] + [ctypes.c_int] * 4 + [ctypes.c_void_p]),
     "dirt_dilate_silhouette_grad": (ctypes.c_int, [ctypes.c_void_p] * 3 + [ctypes.c_int] * 4 + [ctypes.c_void_p]),
     "dirt_kernel_launch_count": (ctypes.c_uint64, []),

@@ -215,7 +215,7 @@ __global__ void __launch_bounds__(256) k_depth_scatter(FwdParams p, int nb, floa
 // A CTA reserves its two ranges with one atomic each (ranks inside the CTA from shared counters);
 // the last CTA to finish publishes the boundaries.  bucket_count[0..2] serve as the two cursors and
 // the ticket (zeroed with the other counters before every forward pass).
-__global__ void __launch_bounds__(256) k_depth_split2(FwdParams p, float min_overdraw, int use_facing)
+__global__ void __launch_bounds__(256) k_depth_split2(FwdParams p, float min_overdraw, int use_facing, int hint_union)
 {
     if (!plan_is_ordered(p, min_overdraw)) return;
     __shared__ uint32_t s_cnt[2], s_base[2];
@@ -233,10 +233,14 @@ __global__ void __launch_bounds__(256) k_depth_split2(FwdParams p, float min_ove
         const int f = f0 + t + j * 256;
         if (f < f1) {
             int k;
-            if (gen) {
+            if (gen && !hint_union) {
                 // hinted: the faces that won a pixel in the previous call go first, everything else behind the
                 // pyramid they leave (no depth is looked at: one byte per face)
                 k = p.vis_flags[(size_t)b * p.F + f] == (uint8_t)gen ? 0 : 1;
+            } else if (gen) {
+                // experiment (DIRT_B200_HINT_UNION=1): hinted faces and the nearest ones together go first
+                const float z = face_near_depth(p, b, f, nullptr, nullptr);
+                k = (p.vis_flags[(size_t)b * p.F + f] == (uint8_t)gen || z < pivot) ? 0 : 1;
             } else {
                 int facing = 0;
                 const float z = face_near_depth(p, b, f, nullptr, use_facing ? &facing : nullptr);
@@ -375,7 +379,8 @@ void launch_depth_order(const FwdParams &p, const BucketPlan &plan, int sm_count
     const dim3 chunks((unsigned)((p.F + kChunkFaces - 1) / kChunkFaces), (unsigned)p.B);
     k_depth_pivots<<<p.B, kSamples, 0, stream>>>(p, plan);
     if (plan.n == 2) {
-        k_depth_split2<<<chunks, 256, 0, stream>>>(p, plan.min_overdraw, plan.facing ? 1 : 0);
+        static const int hint_union = [] { const char *e = std::getenv("DIRT_B200_HINT_UNION"); return (e && e[0] == '1') ? 1 : 0; }();
+        k_depth_split2<<<chunks, 256, 0, stream>>>(p, plan.min_overdraw, plan.facing ? 1 : 0, hint_union);
         return;
     }
     k_depth_classify<<<chunks, 256, 0, stream>>>(p, plan.n, plan.min_overdraw, plan.facing ? 1 : 0);

@@ -35,6 +35,12 @@ constexpr int kWarpsPerCta = 8;
 #ifndef KPRE0
 #define KPRE0 0
 #endif
+#ifndef KCHUNK_TWO
+#define KCHUNK_TWO 1     // chunk test: the pyramid words of the first two tiles are fetched together, before either is compared
+#endif
+#ifndef KCHUNK_MIN
+#define KCHUNK_MIN 0     // faces of at most this many lines skip the chunk test (their lines are sampled directly)
+#endif
 #ifndef KLDCG
 #define KLDCG 0      // 1: the depth pre-load bypasses L1 (sees the reductions of this launch)
 #endif
@@ -312,15 +318,28 @@ __device__ __forceinline__ bool chunk_visible(const uint32_t *rec, int ja, int j
     const float fl = __int2float_rn(zl >= 0.0f ? ja : jb);
     const uint32_t *hz = hz0 + (axis ? tl : tl * ntx);
     const int step = axis ? ntx : 1;
-    for (int t = (o + lo) >> kHizLog2; t <= (o + hi) >> kHizLog2; ++t) {
+    // smallest depth key of the rectangle's part inside tile t
+    auto tile_dmin = [&](int t) {
         const int q0 = max(lo, (t << kHizLog2) - o), q1 = min(hi, (t << kHizLog2) + (1 << kHizLog2) - 1 - o);
         const float fc = __int2float_rn(zq >= 0.0f ? q0 : q1);
         // (zref + dzdx * dx) + dzdy * dy, the operation order of sample_line / plane_depth()
         float zw = axis ? fadd(fadd(zref, fmul(dzdx, fl)), fmul(dzdy, fc)) : fadd(fadd(zref, fmul(dzdx, fc)), fmul(dzdy, fl));
         zw = fminf(fmaxf(zw, 0.0f), 1.0f);
-        const uint32_t dmin = __float2uint_rz(fadd(fmul(zw, 16777215.0f), 0.5f));
-        if (__ldg(hz + t * step) >= dmin) return true;
+        return __float2uint_rz(fadd(fmul(zw, 16777215.0f), 0.5f));
+    };
+    int t = (o + lo) >> kHizLog2;
+    const int t1 = (o + hi) >> kHizLog2;
+#if KCHUNK_TWO
+    {
+        // most chunks touch one or two tiles: both words are in flight before either is looked at
+        const int tb = min(t + 1, t1);
+        const uint32_t ha = __ldg(hz + t * step), hb = __ldg(hz + tb * step);
+        if (ha >= tile_dmin(t) || hb >= tile_dmin(tb)) return true;
+        t += 2;
     }
+#endif
+    for (; t <= t1; ++t)
+        if (__ldg(hz + t * step) >= tile_dmin(t)) return true;
     return false;
 }
 
@@ -355,7 +374,8 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
     // Batches of 32 faces are claimed dynamically (their line counts differ by orders of
     // magnitude); the claim for the next batch is issued before the current one is sampled.
     // Smaller batches shorten the tail of a launch but repeat the latency-bound setup phase more
-    // often: 16 and 8 faces per claim measured slower (profiles/r1_setup_notes.md).
+    // often: 16 and 8 faces per claim measured slower (profiles/r1_setup_notes.md); several batches
+    // per claim (fewer atomics on the one counter) lengthen the tail: slower too (profiles/r2_setup_notes.md).
     unsigned long long *work = p.work_next + launch_index;
     // a handful of faces cannot fill the machine line by line (one warp would walk every span in
     // turn): then anything but tiny triangles goes to the pixel-parallel tile path
@@ -367,15 +387,22 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
         const long long i0 = (long long)__shfl_sync(kFullMask, claim, 0);
         if (i0 >= total) break;
         const long long i = i0 + lane;
+        const long long i_end = min(total, i0 + 32ll);
         const bool preload = HIZ || i0 >= no_preload_below;
         if (lane == 0) claim = atomicAdd(work, 32ull);
         // ---- setup: one face per lane -------------------------------------------------------
         int nlines = 0;                  // > 0: this lane's face is line-sampled by the warp
         int nunits = 0;                  // what the warp distributes: lines, or (HIZ) chunks of eight lines
         uint32_t dims = 0;
-        if (i < total) {
-            const long long flat = ordered ? (long long)p.order[first_entry + i] : i;
-            const int b = (int)(flat / p.F), f = (int)(flat - (long long)b * p.F);
+        if (i < i_end) {
+            // flat face numbers of an ordered plan are below 2^32 (capi.cu): one 32-bit division
+            int b, f;
+            if (ordered) {
+                const uint32_t flat = p.order[first_entry + i];
+                b = (int)(flat / (uint32_t)p.F); f = (int)(flat - (uint32_t)b * (uint32_t)p.F);
+            } else {
+                b = (int)(i / p.F); f = (int)(i - (long long)b * p.F);
+            }
             const int32_t *fp = p.faces + (int64_t)b * p.faces_bs + 3 * (int64_t)f;
             const int i0 = __ldg(fp), i1 = __ldg(fp + 1), i2 = __ldg(fp + 2);
             if ((unsigned)i0 < (unsigned)p.V && (unsigned)i1 < (unsigned)p.V && (unsigned)i2 < (unsigned)p.V) {
@@ -458,7 +485,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdPara
                     const int first = (ci << kHizLog2) - (int)((aux >> 16) & 7u);
                     const int ja = max(first, 0), jb = min(first + 7, (int)(aux >> 19));
                     const uint32_t *hz0 = p.hiz + p.hiz_off[0] + (size_t)(aux & 0xFFFFu) * hz_nty * hz_ntx;
-                    visible = chunk_visible(rec, ja, jb, hz0, hz_ntx);
+                    visible = (KCHUNK_MIN > 0 && (int)(aux >> 19) < KCHUNK_MIN) || chunk_visible(rec, ja, jb, hz0, hz_ntx);
                     entry = (uint32_t)ol | (uint32_t)ja << 5 | (uint32_t)(jb - ja) << 12;
 #ifdef DIRT_STATS
                     atomicAdd(p.counters + 9, 1u);

@@ -4,9 +4,11 @@ dirt/lighting.py, on torch tensors.
 `vertex_normals` is the expensive one -- the reference builds a sparse tensor with 9*F*N entries
 and reduces it (dirt/lighting.py:74-88) -- and runs as hand-written CUDA kernels behind the C ABI
 (`dirt_vertex_normals`, `dirt_vertex_normals_grad`; dirt_b200/csrc/geometry.cu) with autograd wired.
-The shading functions are per-point arithmetic: they are written with torch operations (one to
-five element-wise kernels each, differentiable by torch), formula by formula as the reference has
-them, including its `+ 1e-12` terms.
+`diffuse_directional`, the shading of the c5 optimisation step, is one fused CUDA pass per direction
+(`dirt_diffuse_directional(_grad)`, csrc/lighting.cu: its torch composites took a third of that step,
+profiles/r2_c5_step_breakdown.json).  The other shading functions are per-point arithmetic written with
+torch operations (one to five element-wise kernels each, differentiable by torch), formula by formula as
+the reference has them, including its `+ 1e-12` terms.
 """
 import ctypes
 
@@ -133,11 +135,67 @@ def _cosine_term(cosines, double_sided):
     return cosines.abs() if double_sided else cosines.clamp_min(0.)
 
 
+class _DiffuseDirectional(torch.autograd.Function):
+    """One CUDA pass forward, one backward (csrc/lighting.cu) for the shading formula below."""
+
+    @staticmethod
+    def forward(ctx, n, c, d, lc, double_sided):
+        lib = _lib.load()
+        shape = c.shape
+        V, C = shape[-2], shape[-1]
+        B = c.numel() // max(V * C, 1)
+        n, c = n.contiguous(), c.contiguous()
+        d, lc = d.contiguous(), lc.contiguous()
+        out = torch.empty_like(c)
+        dbs, lbs = (3 if d.dim() > 1 else 0), (C if lc.dim() > 1 else 0)
+        with torch.cuda.device(c.device):
+            _lib.check(lib.dirt_diffuse_directional(n.data_ptr(), c.data_ptr(), d.data_ptr(), dbs, lc.data_ptr(), lbs,
+                                                    int(bool(double_sided)), B, V, C, out.data_ptr(),
+                                                    torch.cuda.current_stream(c.device).cuda_stream))
+        ctx.save_for_backward(n, c, d, lc)
+        ctx.meta = (B, V, C, dbs, lbs, bool(double_sided))
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        n, c, d, lc = ctx.saved_tensors
+        B, V, C, dbs, lbs, double_sided = ctx.meta
+        lib = _lib.load()
+        g = g.contiguous()
+        gn = torch.empty_like(n) if ctx.needs_input_grad[0] else None
+        gc = torch.empty_like(c) if ctx.needs_input_grad[1] else None
+        with torch.cuda.device(c.device):
+            _lib.check(lib.dirt_diffuse_directional_grad(n.data_ptr(), c.data_ptr(), d.data_ptr(), dbs, lc.data_ptr(), lbs,
+                                                         int(double_sided), B, V, C, g.data_ptr(),
+                                                         gn.data_ptr() if gn is not None else None,
+                                                         gc.data_ptr() if gc is not None else None,
+                                                         torch.cuda.current_stream(c.device).cuda_stream))
+        return gn, gc, None, None, None
+
+
+def _fusable(n, c, d, lc):
+    """The fused kernels serve the usual call: float32 CUDA tensors, normals / colours [*, V, 3|C] with the same
+    leading dims, the light either one for all ([3], [C]) or one per leading index ([*, 3], [*, C]), and no gradient
+    wanted for the light itself."""
+    if not (n.is_cuda and c.is_cuda and d.is_cuda and lc.is_cuda):
+        return False
+    if any(t.dtype != torch.float32 for t in (n, c, d, lc)) or d.requires_grad or lc.requires_grad:
+        return False
+    if n.dim() < 2 or c.dim() != n.dim() or n.shape[:-1] != c.shape[:-1] or n.shape[-1] != 3 or not (1 <= c.shape[-1] <= 16):
+        return False
+    lead = n.shape[:-2]
+    return (d.shape == (3,) or d.shape == lead + (3,)) and (lc.shape == c.shape[-1:] or lc.shape == lead + c.shape[-1:])
+
+
 def diffuse_directional(vertex_normals, vertex_colors, light_direction, light_color, double_sided=True, name=None):
     """Lambertian reflectance under one directional light (dirt/lighting.py:182-225).
-    vertex_normals [*, V, 3], vertex_colors [*, V, C], light_direction [*, 3], light_color [*, C]."""
+    vertex_normals [*, V, 3], vertex_colors [*, V, C], light_direction [*, 3], light_color [*, C].
+    CUDA float32 inputs run as one fused kernel per direction (csrc/lighting.cu); anything else (CPU tensors, other
+    dtypes, broadcasting beyond the above, a gradient w.r.t. the light) takes the reference's formula in torch ops."""
     del name
     n, c, d, lc = (torch.as_tensor(x) for x in (vertex_normals, vertex_colors, light_direction, light_color))
+    if _fusable(n, c, d, lc):
+        return _DiffuseDirectional.apply(n, c, d, lc, double_sided)
     cosines = torch.matmul(n, -d.unsqueeze(-1))                       # [*, V, 1]
     return lc.unsqueeze(-2) * c * _cosine_term(cosines, double_sided)
 

@@ -82,6 +82,14 @@ _HINT_SLOTS = 8
 _hints = {}
 
 
+def hint_default():
+    """Whether rasterise / rasterise_batch carry a visibility hint from call to call on their own.  Off unless
+    DIRT_B200_HINT=1: on the measured workloads the hinted order is no faster than the depth-ordered one
+    (DESIGN.md section 6); `forward_raw(..., hint=buffer)` uses it explicitly."""
+    import os
+    return os.environ.get("DIRT_B200_HINT", "0") not in ("", "0")
+
+
 def visibility_hint(device, B, F, key=None):
     """The persistent hint buffer for (device, current stream, B, F, key); zeroed when first created."""
     lib = _lib.load()
@@ -146,7 +154,7 @@ def forward_raw(background, vertices, vertex_colors, faces, want_aux=True, hint=
         _lib.check(-1)
     ws = _workspace(device, nbytes)
     if isinstance(hint, str):
-        hint = visibility_hint(device, B, F, key=(H, W)) if (hint == "auto" and F >= HINT_MIN_FACES) else None
+        hint = visibility_hint(device, B, F, key=(H, W)) if (hint == "auto" and F >= HINT_MIN_FACES and hint_default()) else None
     args = DirtForwardArgs(
         shape,
         background.data_ptr(), _bstride(background, B),

@@ -163,6 +163,21 @@ DIRT_API int dirt_vertex_normals_grad(const float *vertices, int batch, int vert
                                       int face_count, const float *sums, const float *grad_normals, float *grad_sums,
                                       float *grad_vertices, void *stream);
 
+/* Lambertian shading under one directional light, forward and backward, each ONE element-wise pass: replaces the
+ * framework ops (and their autodiff) of diffuse_directional, dirt/lighting.py:182-225:
+ *     out[b,v,c] = light_color[b,c] * colours[b,v,c] * f(normals[b,v] . (-light_direction[b])),
+ *     f = |.| when double_sided, else max(., 0).
+ * normals [batch,V,3], colours / out / grad_out / grad_colours [batch,V,C], grad_normals [batch,V,3]; light_direction
+ * and light_color are DEVICE pointers, `*_bstride` elements apart per batch element (0: one light for all).
+ * grad_normals / grad_colours may be NULL (not wanted).  Gradients w.r.t. the light itself are left to the caller. */
+DIRT_API int dirt_diffuse_directional(const float *normals, const float *colours, const float *light_direction,
+                                      int64_t light_direction_bstride, const float *light_color, int64_t light_color_bstride,
+                                      int double_sided, int batch, int vertex_count, int channels, float *out, void *stream);
+DIRT_API int dirt_diffuse_directional_grad(const float *normals, const float *colours, const float *light_direction,
+                                           int64_t light_direction_bstride, const float *light_color, int64_t light_color_bstride,
+                                           int double_sided, int batch, int vertex_count, int channels, const float *grad_out,
+                                           float *grad_normals, float *grad_colours, void *stream);
+
 /* Library identity. */
 DIRT_API int dirt_abi_version(void);
 /* Thread-local message of the last failing call on this thread ("" if none). */

@@ -173,3 +173,41 @@ def test_vertex_normals_edge_cases():
     assert torch.allclose(lighting.vertex_normals(v, bad), torch.tensor([[0., 0., 1.]] * 3, device="cuda"))
     with pytest.raises(RuntimeError):
         lighting.vertex_normals(torch.rand(5, 3), torch.zeros((1, 3), dtype=torch.int32))    # CPU tensors: no fallback
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("double_sided", [True, False])
+@pytest.mark.parametrize("batched_light", [False, True])
+@pytest.mark.parametrize("C", [1, 3, 5])
+def test_fused_diffuse_directional_matches_the_composite_and_the_oracle(double_sided, batched_light, C):
+    """csrc/lighting.cu: one pass forward, one backward, against the reference's formula in torch ops (which
+    the CPU test above pins to the numpy oracle) -- values and both gradients."""
+    rng = np.random.RandomState(3)
+    B, V = 3, 257
+    n = rng.randn(B, V, 3).astype(np.float32)
+    n /= np.linalg.norm(n, axis=-1, keepdims=True)
+    col = rng.uniform(0, 1, (B, V, C)).astype(np.float32)
+    d = rng.randn(*((B, 3) if batched_light else (3,))).astype(np.float32)
+    d /= np.linalg.norm(d, axis=-1, keepdims=True)
+    lc = rng.uniform(0.2, 1, (B, C) if batched_light else (C,)).astype(np.float32)
+    g = rng.randn(B, V, C).astype(np.float32)
+    tn, tc = (torch.tensor(x, device="cuda", requires_grad=True) for x in (n, col))
+    td, tl, tg = (torch.tensor(x, device="cuda") for x in (d, lc, g))
+    assert lighting._fusable(tn, tc, td, tl)
+    out = lighting.diffuse_directional(tn, tc, td, tl, double_sided=double_sided)
+    out.backward(tg)
+    rn, rc = (torch.tensor(x, device="cuda", requires_grad=True) for x in (n, col))
+    dd = td if batched_light else td.expand(B, 3)
+    ll = tl if batched_light else tl.expand(B, C)
+    cos = torch.matmul(rn, -dd.unsqueeze(-1))
+    ref = ll.unsqueeze(-2) * rc * (cos.abs() if double_sided else cos.clamp_min(0.))
+    ref.backward(tg)
+    torch.testing.assert_close(out, ref, rtol=1e-6, atol=1e-7)
+    torch.testing.assert_close(tn.grad, rn.grad, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(tc.grad, rc.grad, rtol=1e-6, atol=1e-7)
+    np.testing.assert_allclose(out.detach().cpu().numpy(),
+                               ol.diffuse_directional(n.astype(np.float64), col.astype(np.float64), np.broadcast_to(d, (B, 3)).astype(np.float64),
+                                                      np.broadcast_to(lc, (B, C)).astype(np.float64), double_sided), rtol=1e-5, atol=1e-6)
+    # a gradient w.r.t. the light, or CPU tensors, take the torch formula
+    assert not lighting._fusable(tn, tc, td.clone().requires_grad_(True), tl)
+    assert not lighting._fusable(tn.cpu(), tc.cpu(), td.cpu(), tl.cpu())

@@ -104,13 +104,16 @@ def test_hint_buffer_is_validated():
     assert bool((h == 5).all())
 
 
-def test_autograd_path_keeps_a_hint_per_mesh_and_matches_the_unhinted_result():
+def test_autograd_path_keeps_a_hint_per_mesh_and_matches_the_unhinted_result(monkeypatch):
     import torch
     import dirt_b200
     from dirt_b200 import rasterise_ops as ops
     B, H, W, n = 2, 128, 128, 64
     sc, t, vs = _frames(B, H, W, n, 3)
     ops.release_workspaces()
+    out = dirt_b200.rasterise_batch(t["background"], vs[0], t["vertex_colors"], t["faces"])
+    assert len(ops._hints) == 0                      # opt-in: DIRT_B200_HINT=1
+    monkeypatch.setenv("DIRT_B200_HINT", "1")
     for v in vs:
         ref = _render(t, v, None)[0]
         out = dirt_b200.rasterise_batch(t["background"], v, t["vertex_colors"], t["faces"])

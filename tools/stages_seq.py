@@ -16,10 +16,11 @@ SHAPES = {"headline": (64, 512, 512), "c4": (256, 256, 256), "h8": (8, 512, 512)
 
 
 def main():
-    name = sys.argv[1] if len(sys.argv) > 1 else "headline"
-    deg = float(sys.argv[2]) if len(sys.argv) > 2 else 0.25
-    noise = float(sys.argv[3]) if len(sys.argv) > 3 else 0.0
-    nfr = int(sys.argv[4]) if len(sys.argv) > 4 else 4
+    argv = [a for a in sys.argv if not a.startswith("--")]
+    name = argv[1] if len(argv) > 1 else "headline"
+    deg = float(argv[2]) if len(argv) > 2 else 0.25
+    noise = float(argv[3]) if len(argv) > 3 else 0.0
+    nfr = int(argv[4]) if len(argv) > 4 else 4
     B, H, W = SHAPES[name]
     lib = _lib.load()
     sc = scenes.sphere(B, H, W)
@@ -36,13 +37,21 @@ def main():
         px, fid, gb = ops.forward_raw(d["background"], v, d["vertex_colors"], d["faces"], hint=h)
         return (px, fid, gb), ops.backward_raw(d["faces"], px, g, fid, gb, V)
 
+    if "--ncu" in sys.argv:            # a few hinted steps for a profiler: no checks, no timing
+        for i in range(6):
+            step(i, hint)
+        torch.cuda.synchronize()
+        return
     # parity of the hinted path, frame by frame
     for i in range(len(order) + 2):
         a, _ = step(i, None)
         b, _ = step(i, hint)
         assert all(torch.equal(x, y) for x, y in zip(a, b)), "hinted output differs at step %d" % i
     print("%s: hinted output bit-identical over %d steps" % (name, len(order) + 2))
+    only = os.environ.get("SEQ_ONLY")
     for label, h, moving in (("static, no hint", None, False), ("moving, no hint", None, True), ("moving, hint", hint, True), ("static, hint", hint, False)):
+        if only and label not in only.split(";"):
+            continue
         idx = (lambda i: i) if moving else (lambda i: 0)
         for i in range(4):
             step(idx(i), h)
