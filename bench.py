@@ -744,10 +744,39 @@ def extra_c5(wl, args, rank, world, dev, barrier, max_over_ranks):
 
     steps = min(args.steps, 10)
     out = {"workload": wl["desc"], "frames_per_gpu": B, "allreduce_bytes": V * lib_stride(C) * 4, "unit": UNIT}
-    for name, fn in (("sync_allreduce", step_sync), ("no_allreduce", step_local), ("overlapped_two_groups", step_overlap)):
+    variants = [("sync_allreduce", step_sync), ("no_allreduce", step_local), ("overlapped_two_groups", step_overlap)]
+    # the same sum taken by kernels that work on peer memory directly (symmetric memory over NVLink / NVSwitch)
+    sym = None
+    if world > 1:
+        try:
+            sym = sharding.SymmetricPacked(V, C, dev)
+        except Exception as e:                       # no symmetric-memory support in this build / on this box
+            out["symmetric_memory"] = "unavailable: %s" % (str(e)[:120] or type(e).__name__)
+    if sym is not None:
+        def sym_step(mode):
+            def fn(i):
+                px, fid, gb = ops.forward_raw(d["background"], d["vertices"], d["vertex_colors"], d["faces"])
+                ops.backward_shared_raw(d["faces"], px, g, fid, gb, V, d["matrices"], out=sym.tensor)
+                return sym.allreduce(mode)
+            return fn
+        ref_sum = step_sync(0)
+        ref_sum = torch.cat([ref_sum[0], ref_sum[1]], 1).clone()
+        for mode in ("peer", "two_shot", "multimem") if sym.has_multicast else ("peer", "two_shot"):
+            try:
+                got = sym_step(mode)(0)
+                torch.cuda.synchronize()
+                err = float((torch.cat([got[0], got[1]], 1) - ref_sum).abs().max() / ref_sum.abs().max())
+                assert err < 1e-4, "symmetric %s all-reduce differs from NCCL by %g" % (mode, err)
+                variants.append(("symm_" + mode, sym_step(mode)))
+            except Exception as e:
+                out["symm_" + mode] = "failed: %s" % (str(e)[:160] or type(e).__name__)
+    for name, fn in variants:
         ms = time_steps(fn, steps, 3, barrier, max_over_ranks)
         out[name] = {"ms_per_step": ms, "value": world * B * H * W / (ms * 1e-3) / 1e6}
     out["allreduce_exposed_ms"] = out["sync_allreduce"]["ms_per_step"] - out["no_allreduce"]["ms_per_step"]
+    for name in ("symm_peer", "symm_two_shot", "symm_multimem"):
+        if isinstance(out.get(name), dict):
+            out[name]["exposed_ms"] = out[name]["ms_per_step"] - out["no_allreduce"]["ms_per_step"]
     out["nccl"] = {k: os.environ[k] for k in os.environ if k.startswith("NCCL_")}
     return out
 

@@ -56,6 +56,11 @@ class DirtSharedBackwardArgs(ctypes.Structure):
                 ("workspace", ctypes.c_void_p), ("workspace_bytes", ctypes.c_size_t), ("flags", ctypes.c_uint32)]
 
 
+class DirtPeerAllreduceArgs(ctypes.Structure):
+    _fields_ = [("buffers", ctypes.c_void_p), ("signals", ctypes.c_void_p), ("rank", ctypes.c_int32), ("world", ctypes.c_int32),
+                ("count", _i64), ("epoch", ctypes.c_void_p)]
+
+
 class DirtSceneArgs(ctypes.Structure):
     _fields_ = [("shape", DirtShape),
                 ("background", _f32p), ("background_bstride", _i64),
@@ -80,6 +85,7 @@ EXPORTS = {
     "dirt_rasterise_backward": (ctypes.c_int, [ctypes.POINTER(DirtBackwardArgs), ctypes.c_void_p]),
     "dirt_shared_grad_stride": (ctypes.c_int, [ctypes.c_int]),
     "dirt_rasterise_backward_shared": (ctypes.c_int, [ctypes.POINTER(DirtSharedBackwardArgs), ctypes.c_void_p]),
+    "dirt_allreduce_peer": (ctypes.c_int, [ctypes.POINTER(DirtPeerAllreduceArgs), ctypes.c_void_p]),
     "dirt_rasterise_forward_host": (ctypes.c_int, [ctypes.POINTER(DirtForwardArgs)]),
     "dirt_rasterise_backward_host": (ctypes.c_int, [ctypes.POINTER(DirtBackwardArgs)]),
     "dirt_release_host_staging": (ctypes.c_int, []),

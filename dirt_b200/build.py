@@ -13,7 +13,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libdirt_b200.so")
-SOURCES = ["setup_raster.cu", "depth_order.cu", "forward.cu", "backward.cu", "dilate.cu", "geometry.cu", "lighting.cu", "scene_oceanic.cu", "scene_shaders.cu", "capi.cu", "capi_host.cu", "capi_noalloc.cu"]
+SOURCES = ["setup_raster.cu", "depth_order.cu", "forward.cu", "backward.cu", "dilate.cu", "geometry.cu", "lighting.cu", "peer_allreduce.cu", "scene_oceanic.cu", "scene_shaders.cu", "capi.cu", "capi_host.cu", "capi_noalloc.cu"]
 HEADERS = ["raster_core.cuh", "forward_common.cuh", "kernels.h", os.path.join("..", "..", "include", "dirt_b200.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",

@@ -212,7 +212,7 @@ def backward_raw(faces, pixels, grad_pixels, face_id, gbuffer, V, shared_vertice
 
 
 def backward_shared_raw(faces, pixels, grad_pixels, face_id, gbuffer, V, clip_from_world, want_grad_background=True,
-                        deterministic=False):
+                        deterministic=False, out=None):
     """Shared-mesh backward: one C-ABI call that folds every element's
     clip-space vertex gradient to world space with its matrix (clip_b = world @ M_b) and sums
     position and colour gradients over the batch into ONE packed buffer [V, stride]: columns 0..3
@@ -223,7 +223,11 @@ def backward_shared_raw(faces, pixels, grad_pixels, face_id, gbuffer, V, clip_fr
     B, H, W, C = pixels.shape
     F = faces.shape[1]
     stride = lib.dirt_shared_grad_stride(C)
-    packed = torch.empty((V, stride), dtype=torch.float32, device=device)
+    # `out`: a caller-owned [V, stride] buffer, e.g. one in symmetric memory (sharding.SymmetricPacked) that the
+    # collective reduces in place without a copy
+    if out is not None and (tuple(out.shape) != (V, stride) or out.dtype != torch.float32 or not out.is_contiguous()):
+        raise _lib.InvalidArgumentError(-1, "out must be a contiguous float32 [V, %d] tensor" % stride)
+    packed = out if out is not None else torch.empty((V, stride), dtype=torch.float32, device=device)
     gbg = torch.empty((B, H, W, C), dtype=torch.float32, device=device) if want_grad_background else None
     m = clip_from_world.to(torch.float32).contiguous()
     if tuple(m.shape) != (B, 4, 4):

@@ -86,6 +86,71 @@ def allreduce_packed(packed, channels, group=None, async_op=False):
     return split()
 
 
+class SymmetricPacked:
+    """The packed shared-mesh gradient buffer [V, stride] allocated in SYMMETRIC memory (every rank's copy mapped into
+    every other rank's address space over NVLink; torch.distributed._symmetric_memory), so that the sum over the ranks
+    can be taken by a kernel that reads and writes peer memory directly instead of going through NCCL's channels:
+        peer       this project's kernels (dirt_allreduce_peer, csrc/peer_allreduce.cu): rank r sums slice r of all
+                   buffers in rank order and stores it into every buffer, between two flag handshakes
+        two_shot   torch's kernel of the same scheme
+        multimem   the same with the NVSwitch doing the additions (multimem.ld_reduce / multimem.st, NVLS)
+    At the 16 MB of config c5 the collective is latency-bound under NCCL (0.05 ms at 2 GPUs, 0.11 ms at 8 for a
+    0.49 ms step).  Allocate once per mesh, pass `.tensor` as `out=` of rasterise_ops.backward_shared_raw, then call
+    `allreduce()`."""
+
+    def __init__(self, V, channels, device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        from . import _lib
+        self.group = group if group is not None else dist.group.WORLD
+        self.channels = channels
+        stride = int(_lib.load().dirt_shared_grad_stride(channels))
+        self.tensor = symm_mem.empty((V, stride), dtype=torch.float32, device=device)
+        self.handle = symm_mem.rendezvous(self.tensor, group=self.group)
+        self.has_multicast = bool(getattr(self.handle, "multicast_ptr", 0))
+        self._peer = None
+
+    def _peer_state(self):
+        """Device tables for dirt_allreduce_peer: every rank's buffer and flag pad as this process addresses them.  The
+        flags live in a second symmetric allocation of their own (torch's signal pad stays torch's)."""
+        if self._peer is None:
+            import ctypes
+            import torch.distributed._symmetric_memory as symm_mem
+            from . import _lib
+            dev = self.tensor.device
+            world, rank = dist.get_world_size(self.group), dist.get_rank(self.group)
+            flags = symm_mem.empty(256, dtype=torch.int32, device=dev)
+            fh = symm_mem.rendezvous(flags, group=self.group)
+            flags.zero_()
+            epoch = torch.zeros(2, dtype=torch.int32, device=dev)     # [0] calls completed, [1] != 0: a peer never arrived
+            torch.cuda.synchronize(dev)
+            dist.barrier(group=self.group)                 # every pad is zero before anyone raises a flag
+            bufs = torch.tensor([int(p) for p in self.handle.buffer_ptrs], dtype=torch.int64, device=dev)
+            sigs = torch.tensor([int(p) for p in fh.buffer_ptrs], dtype=torch.int64, device=dev)
+            args = _lib.DirtPeerAllreduceArgs(bufs.data_ptr(), sigs.data_ptr(), rank, world, self.tensor.numel(), epoch.data_ptr())
+            self._peer = (args, bufs, sigs, flags, fh, epoch, ctypes)
+        return self._peer
+
+    def allreduce(self, mode="two_shot"):
+        """Sums `.tensor` over the ranks in place; returns (grad_world [V,4], grad_vertex_colors [V,C]) views."""
+        name = self.group.group_name
+        if mode == "multimem":
+            torch.ops.symm_mem.multimem_all_reduce_(self.tensor, "sum", name)
+        elif mode == "two_shot":
+            torch.ops.symm_mem.two_shot_all_reduce_(self.tensor, "sum", name)
+        elif mode == "nccl":
+            dist.all_reduce(self.tensor, op=dist.ReduceOp.SUM, group=self.group)
+        elif mode == "peer":
+            # this project's own kernels over the peer mappings (csrc/peer_allreduce.cu)
+            from . import _lib
+            st = self._peer_state()
+            dev = self.tensor.device
+            with torch.cuda.device(dev):
+                _lib.check(_lib.load().dirt_allreduce_peer(st[6].byref(st[0]), torch.cuda.current_stream(dev).cuda_stream))
+        else:
+            raise ValueError("mode must be peer, two_shot, multimem or nccl")
+        return self.tensor[:, :4], self.tensor[:, 4:4 + self.channels]
+
+
 def rasterise_batch_sharded(background, vertices, vertex_colors, faces, rank=None, world=None):
     """`rasterise_batch` on this rank's shard of the batch (no collective; outputs stay sharded,
     as the reference's per-device graphs do).  Returns (pixels_shard, (lo, hi))."""

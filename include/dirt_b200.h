@@ -147,6 +147,22 @@ typedef struct DirtSharedBackwardArgs {
 DIRT_API int dirt_shared_grad_stride(int channels);
 DIRT_API int dirt_rasterise_backward_shared(const DirtSharedBackwardArgs *args, void *stream);
 
+/* The sum of `grad_shared` over the GPUs of one box, taken over peer memory (no counterpart in the reference, whose loop
+ * runs on one device): every rank's buffer must be mapped into every process -- symmetric memory, cudaIpc or
+ * the VMM API over NVLink.  Rank r sums slice r of all buffers in rank order (all ranks end up with identical bits) and
+ * stores it into slice r of every buffer; two handshakes on flag words bracket that.  In place, asynchronous on `stream`.
+ * Every rank of the group must make the call, once per reduction. */
+typedef struct DirtPeerAllreduceArgs {
+    float *const *buffers;        /* DEVICE array [world]: rank p's buffer as this process addresses it; 16-byte aligned   */
+    uint32_t *const *signals;     /* DEVICE array [world]: rank p's flag pad, >= 2 * world words, zeroed once before use  */
+    int32_t rank, world;          /* 1 <= world <= 32                                                                      */
+    int64_t count;                /* floats per buffer, a multiple of 4                                                    */
+    uint32_t *epoch;              /* DEVICE, TWO words of this rank, zeroed once before use (together with the pads):
+                                     [0] calls completed; [1] stays 0, or 1 + the rank a handshake gave up waiting for
+                                     (~30 s: that peer never made its call; the buffer's contents are then undefined)     */
+} DirtPeerAllreduceArgs;
+DIRT_API int dirt_allreduce_peer(const DirtPeerAllreduceArgs *args, void *stream);
+
 /* Vertex normals of `batch` meshes with common topology: replaces
  * vertex_normals / vertex_normals_pre_split, dirt/lighting.py:34-93, :101-133 -- the normalised
  * sum, per vertex, of the unit normals (v1 - v0) x (v2 - v0) of the faces that use it, with the

@@ -167,3 +167,38 @@ def test_deterministic_shared_mesh_backward():
     runs = [ops.backward_shared_raw(t["faces"], px, g, fid, gb, V, t["matrices"], deterministic=True)[0] for _ in range(3)]
     assert torch.equal(runs[0], runs[1]) and torch.equal(runs[0], runs[2])
     assert float((runs[0] - ref).abs().max()) <= GRAD_RTOL * float(ref.abs().max())
+
+
+def test_peer_allreduce_protocol_between_two_streams_of_one_gpu():
+    """dirt_allreduce_peer (csrc/peer_allreduce.cu) needs every rank's buffer and flag pad mapped into every process; on one
+    GPU two "ranks" are two streams of this process that address each other's buffers directly -- the same kernels, the
+    same handshakes.  (Between real GPUs: tools/peer_allreduce_check.py under torchrun, profiles/r2_peer_allreduce_n*.json.)"""
+    import torch
+    lib = _lib.load()
+    n = 4 * 50021                                     # not a multiple of the slice size
+    world = 2
+    streams = [torch.cuda.Stream() for _ in range(world)]
+    for it in range(3):
+        src = [torch.randn(n, device="cuda") for _ in range(world)]
+        bufs = [s.clone() for s in src]
+        if it == 0:
+            pads = [torch.zeros(2 * world, dtype=torch.int32, device="cuda") for _ in range(world)]
+            epochs = [torch.zeros(2, dtype=torch.int32, device="cuda") for _ in range(world)]
+        bt = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64, device="cuda")
+        pt = torch.tensor([p.data_ptr() for p in pads], dtype=torch.int64, device="cuda")
+        torch.cuda.synchronize()
+        for r in range(world):
+            a = _lib.DirtPeerAllreduceArgs(bt.data_ptr(), pt.data_ptr(), r, world, n, epochs[r].data_ptr())
+            _lib.check(lib.dirt_allreduce_peer(ctypes.byref(a), streams[r].cuda_stream))
+        torch.cuda.synchronize()
+        want = src[0] + src[1]
+        for r in range(world):
+            assert torch.equal(bufs[r], want)
+            assert epochs[r].tolist() == [it + 1, 0]
+    # argument checks need no second rank
+    a = _lib.DirtPeerAllreduceArgs(bt.data_ptr(), pt.data_ptr(), 2, 2, n, epochs[0].data_ptr())
+    assert lib.dirt_allreduce_peer(ctypes.byref(a), None) == -1
+    a = _lib.DirtPeerAllreduceArgs(bt.data_ptr(), pt.data_ptr(), 0, 2, n + 1, epochs[0].data_ptr())
+    assert lib.dirt_allreduce_peer(ctypes.byref(a), None) == -1
+    a = _lib.DirtPeerAllreduceArgs(None, None, 0, 1, n, None)                 # a world of one: nothing to do
+    assert lib.dirt_allreduce_peer(ctypes.byref(a), None) == 0
