@@ -761,7 +761,7 @@ def extra_c5(wl, args, rank, world, dev, barrier, max_over_ranks):
             return fn
         ref_sum = step_sync(0)
         ref_sum = torch.cat([ref_sum[0], ref_sum[1]], 1).clone()
-        for mode in ("peer", "two_shot", "multimem") if sym.has_multicast else ("peer", "two_shot"):
+        for mode in ("peer", "peer_multicast", "two_shot", "multimem") if sym.has_multicast else ("peer", "two_shot"):
             try:
                 got = sym_step(mode)(0)
                 torch.cuda.synchronize()
@@ -774,7 +774,7 @@ def extra_c5(wl, args, rank, world, dev, barrier, max_over_ranks):
         ms = time_steps(fn, steps, 3, barrier, max_over_ranks)
         out[name] = {"ms_per_step": ms, "value": world * B * H * W / (ms * 1e-3) / 1e6}
     out["allreduce_exposed_ms"] = out["sync_allreduce"]["ms_per_step"] - out["no_allreduce"]["ms_per_step"]
-    for name in ("symm_peer", "symm_two_shot", "symm_multimem"):
+    for name in ("symm_peer", "symm_peer_multicast", "symm_two_shot", "symm_multimem"):
         if isinstance(out.get(name), dict):
             out[name]["exposed_ms"] = out[name]["ms_per_step"] - out["no_allreduce"]["ms_per_step"]
     out["nccl"] = {k: os.environ[k] for k in os.environ if k.startswith("NCCL_")}

@@ -58,7 +58,7 @@ class DirtSharedBackwardArgs(ctypes.Structure):
 
 class DirtPeerAllreduceArgs(ctypes.Structure):
     _fields_ = [("buffers", ctypes.c_void_p), ("signals", ctypes.c_void_p), ("rank", ctypes.c_int32), ("world", ctypes.c_int32),
-                ("count", _i64), ("epoch", ctypes.c_void_p)]
+                ("count", _i64), ("epoch", ctypes.c_void_p), ("multicast", ctypes.c_void_p)]
 
 
 class DirtSceneArgs(ctypes.Structure):

@@ -90,8 +90,9 @@ class SymmetricPacked:
     """The packed shared-mesh gradient buffer [V, stride] allocated in SYMMETRIC memory (every rank's copy mapped into
     every other rank's address space over NVLink; torch.distributed._symmetric_memory), so that the sum over the ranks
     can be taken by a kernel that reads and writes peer memory directly instead of going through NCCL's channels:
-        peer       this project's kernels (dirt_allreduce_peer, csrc/peer_allreduce.cu): rank r sums slice r of all
+        peer       this project's kernel (dirt_allreduce_peer, csrc/peer_allreduce.cu): rank r sums slice r of all
                    buffers in rank order and stores it into every buffer, between two flag handshakes
+        peer_multicast   the same kernel on the NVSwitch's multicast mapping: the switch adds (multimem.ld_reduce / .st)
         two_shot   torch's kernel of the same scheme
         multimem   the same with the NVSwitch doing the additions (multimem.ld_reduce / multimem.st, NVLS)
     At the 16 MB of config c5 the collective is latency-bound under NCCL (0.05 ms at 2 GPUs, 0.11 ms at 8 for a
@@ -121,12 +122,14 @@ class SymmetricPacked:
             flags = symm_mem.empty(256, dtype=torch.int32, device=dev)
             fh = symm_mem.rendezvous(flags, group=self.group)
             flags.zero_()
-            epoch = torch.zeros(2, dtype=torch.int32, device=dev)     # [0] calls completed, [1] != 0: a peer never arrived
+            epoch = torch.zeros(4, dtype=torch.int32, device=dev)     # [0] calls completed, [1] != 0: a peer never arrived
             torch.cuda.synchronize(dev)
             dist.barrier(group=self.group)                 # every pad is zero before anyone raises a flag
             bufs = torch.tensor([int(p) for p in self.handle.buffer_ptrs], dtype=torch.int64, device=dev)
             sigs = torch.tensor([int(p) for p in fh.buffer_ptrs], dtype=torch.int64, device=dev)
-            args = _lib.DirtPeerAllreduceArgs(bufs.data_ptr(), sigs.data_ptr(), rank, world, self.tensor.numel(), epoch.data_ptr())
+            mc = int(getattr(self.handle, "multicast_ptr", 0) or 0)
+            args = [_lib.DirtPeerAllreduceArgs(bufs.data_ptr(), sigs.data_ptr(), rank, world, self.tensor.numel(), epoch.data_ptr(), m)
+                    for m in (None, mc or None)]                 # [0] peer loads / stores, [1] through the switch's multicast mapping
             self._peer = (args, bufs, sigs, flags, fh, epoch, ctypes)
         return self._peer
 
@@ -139,15 +142,18 @@ class SymmetricPacked:
             torch.ops.symm_mem.two_shot_all_reduce_(self.tensor, "sum", name)
         elif mode == "nccl":
             dist.all_reduce(self.tensor, op=dist.ReduceOp.SUM, group=self.group)
-        elif mode == "peer":
-            # this project's own kernels over the peer mappings (csrc/peer_allreduce.cu)
+        elif mode in ("peer", "peer_multicast"):
+            # this project's own kernel over the peer mappings, or over the switch's multicast mapping (csrc/peer_allreduce.cu)
             from . import _lib
             st = self._peer_state()
             dev = self.tensor.device
+            if mode == "peer_multicast" and not self.has_multicast:
+                raise ValueError("no multicast mapping of the buffer on this system")
             with torch.cuda.device(dev):
-                _lib.check(_lib.load().dirt_allreduce_peer(st[6].byref(st[0]), torch.cuda.current_stream(dev).cuda_stream))
+                _lib.check(_lib.load().dirt_allreduce_peer(st[6].byref(st[0][1 if mode == "peer_multicast" else 0]),
+                                                           torch.cuda.current_stream(dev).cuda_stream))
         else:
-            raise ValueError("mode must be peer, two_shot, multimem or nccl")
+            raise ValueError("mode must be peer, peer_multicast, two_shot, multimem or nccl")
         return self.tensor[:, :4], self.tensor[:, 4:4 + self.channels]
 
 

@@ -147,19 +147,22 @@ typedef struct DirtSharedBackwardArgs {
 DIRT_API int dirt_shared_grad_stride(int channels);
 DIRT_API int dirt_rasterise_backward_shared(const DirtSharedBackwardArgs *args, void *stream);
 
-/* The sum of `grad_shared` over the GPUs of one box, taken over peer memory (no counterpart in the reference, whose loop
- * runs on one device): every rank's buffer must be mapped into every process -- symmetric memory, cudaIpc or
- * the VMM API over NVLink.  Rank r sums slice r of all buffers in rank order (all ranks end up with identical bits) and
- * stores it into slice r of every buffer; two handshakes on flag words bracket that.  In place, asynchronous on `stream`.
- * Every rank of the group must make the call, once per reduction. */
+/* The sum of `grad_shared` over the GPUs of one box, taken over peer memory in one kernel (no counterpart in the reference,
+ * whose loop runs on one device): every rank's buffer must be mapped into every process -- symmetric memory,
+ * cudaIpc or the VMM API over NVLink.  Rank r sums slice r of all buffers in rank order (all ranks end up with identical
+ * bits) and stores it into slice r of every buffer; with `multicast` (an NVSwitch multicast mapping of the same buffers) the
+ * switch does the additions (multimem.ld_reduce / multimem.st).  Two handshakes on flag words bracket the sums.  In place,
+ * asynchronous on `stream`.  Every rank of the group must make the call, once per reduction. */
 typedef struct DirtPeerAllreduceArgs {
     float *const *buffers;        /* DEVICE array [world]: rank p's buffer as this process addresses it; 16-byte aligned   */
     uint32_t *const *signals;     /* DEVICE array [world]: rank p's flag pad, >= 2 * world words, zeroed once before use  */
     int32_t rank, world;          /* 1 <= world <= 32                                                                      */
     int64_t count;                /* floats per buffer, a multiple of 4                                                    */
-    uint32_t *epoch;              /* DEVICE, TWO words of this rank, zeroed once before use (together with the pads):
+    uint32_t *epoch;              /* DEVICE, FOUR words of this rank, zeroed once before use (together with the pads):
                                      [0] calls completed; [1] stays 0, or 1 + the rank a handshake gave up waiting for
-                                     (~30 s: that peer never made its call; the buffer's contents are then undefined)     */
+                                     (~30 s: that peer never made its call; the buffer's contents are then undefined);
+                                     [2], [3] internal                                                                     */
+    float *multicast;             /* optional: multicast address of the buffers (all ranks' copies), or NULL               */
 } DirtPeerAllreduceArgs;
 DIRT_API int dirt_allreduce_peer(const DirtPeerAllreduceArgs *args, void *stream);
 

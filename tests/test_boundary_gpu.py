@@ -183,22 +183,22 @@ def test_peer_allreduce_protocol_between_two_streams_of_one_gpu():
         bufs = [s.clone() for s in src]
         if it == 0:
             pads = [torch.zeros(2 * world, dtype=torch.int32, device="cuda") for _ in range(world)]
-            epochs = [torch.zeros(2, dtype=torch.int32, device="cuda") for _ in range(world)]
+            epochs = [torch.zeros(4, dtype=torch.int32, device="cuda") for _ in range(world)]
         bt = torch.tensor([b.data_ptr() for b in bufs], dtype=torch.int64, device="cuda")
         pt = torch.tensor([p.data_ptr() for p in pads], dtype=torch.int64, device="cuda")
         torch.cuda.synchronize()
         for r in range(world):
-            a = _lib.DirtPeerAllreduceArgs(bt.data_ptr(), pt.data_ptr(), r, world, n, epochs[r].data_ptr())
+            a = _lib.DirtPeerAllreduceArgs(bt.data_ptr(), pt.data_ptr(), r, world, n, epochs[r].data_ptr(), None)
             _lib.check(lib.dirt_allreduce_peer(ctypes.byref(a), streams[r].cuda_stream))
         torch.cuda.synchronize()
         want = src[0] + src[1]
         for r in range(world):
             assert torch.equal(bufs[r], want)
-            assert epochs[r].tolist() == [it + 1, 0]
+            assert epochs[r].tolist()[:2] == [it + 1, 0]
     # argument checks need no second rank
-    a = _lib.DirtPeerAllreduceArgs(bt.data_ptr(), pt.data_ptr(), 2, 2, n, epochs[0].data_ptr())
+    a = _lib.DirtPeerAllreduceArgs(bt.data_ptr(), pt.data_ptr(), 2, 2, n, epochs[0].data_ptr(), None)
     assert lib.dirt_allreduce_peer(ctypes.byref(a), None) == -1
-    a = _lib.DirtPeerAllreduceArgs(bt.data_ptr(), pt.data_ptr(), 0, 2, n + 1, epochs[0].data_ptr())
+    a = _lib.DirtPeerAllreduceArgs(bt.data_ptr(), pt.data_ptr(), 0, 2, n + 1, epochs[0].data_ptr(), None)
     assert lib.dirt_allreduce_peer(ctypes.byref(a), None) == -1
-    a = _lib.DirtPeerAllreduceArgs(None, None, 0, 1, n, None)                 # a world of one: nothing to do
+    a = _lib.DirtPeerAllreduceArgs(None, None, 0, 1, n, None, None)           # a world of one: nothing to do
     assert lib.dirt_allreduce_peer(ctypes.byref(a), None) == 0

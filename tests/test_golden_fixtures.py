@@ -1,6 +1,7 @@
 """The committed fixtures of tests/golden/ (written by tests/golden/make_golden.py).
 CPU: the oracle reproduces them bit for bit (kat1/kat2 are the reference's analytic known-answer
-cases; the others pin the written spec against drift).  GPU: the CUDA path, through the C ABI,
+cases; the others are outputs of this project's own oracle and pin the written spec against drift -- they are
+regression guards, NOT evidence of parity with the reference: attribute values and gradients stay "parity unpinned").  GPU: the CUDA path, through the C ABI,
 matches them at the parity bars."""
 import os
 

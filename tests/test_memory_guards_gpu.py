@@ -284,3 +284,67 @@ def test_guard_zones_host_entry_points():
     from oracle import golden
     _, ofid, _ = golden.forward(sc["background"], sc["vertices"], sc["vertex_colors"], sc["faces"])
     assert np.array_equal(arena[o:o + npx * 4].view(np.int32).reshape(B, H, W), ofid)
+
+
+@pytest.mark.parametrize("poison", [0x00, 0xFF])
+def test_guard_zones_of_the_hint_and_of_the_stateless_deterministic_backward(poison):
+    """Round-2 buffers: a visibility hint of EXACTLY dirt_visibility_hint_bytes() (whatever it held before: the output
+    must not change), and the backward in its stateless + deterministic form on a workspace of exactly
+    dirt_backward_workspace_bytes() + dirt_deterministic_workspace_bytes()."""
+    import torch
+    from dirt_b200 import _lib, rasterise_ops as ops
+    from dirt_b200._lib import DirtShape, DirtForwardArgs, DirtBackwardArgs
+    lib = _lib.load()
+    sc = scenes.sphere(3, 170, 210, n_lat=80, n_lon=60)                 # 9,440 faces per element: the ordered path
+    B, H, W, C = sc["background"].shape
+    V, F = sc["vertices"].shape[1], sc["faces"].shape[1]
+    shape = DirtShape(B, H, W, C, V, F)
+    ws_bytes = lib.dirt_workspace_bytes(ctypes.byref(shape))
+    hint_bytes = lib.dirt_visibility_hint_bytes(ctypes.byref(shape))
+    bws_bytes = lib.dirt_backward_workspace_bytes(ctypes.byref(shape)) + lib.dirt_deterministic_workspace_bytes(ctypes.byref(shape))
+    g = np.random.RandomState(0).randn(B, H, W, C).astype(np.float32)
+    out_bytes = {"pixels": B * H * W * C * 4, "face_id": B * H * W * 4, "gbuffer": B * H * W * 16,
+                 "gv": B * V * 16, "gc": B * V * C * 4, "gbg": B * H * W * C * 4}
+    total = (sum(v.nbytes for k, v in sc.items() if k != "expected") + g.nbytes + sum(out_bytes.values()) + ws_bytes + hint_bytes
+             + bws_bytes + 20 * (GUARD + 256))
+    arena = Arena(total)
+    ins = {k: arena.put(sc[k]) for k in ("background", "vertices", "vertex_colors", "faces")}
+    ws, hint, bws = arena.carve(ws_bytes), arena.carve(hint_bytes), arena.carve(bws_bytes)
+    ws.fill_(poison); hint.fill_(poison); bws.fill_(poison)
+    outs = {k: arena.carve(n) for k, n in out_bytes.items()}
+    gp = arena.put(g)
+    stream = torch.cuda.current_stream().cuda_stream
+    t = {k: torch.from_numpy(np.ascontiguousarray(v)).cuda() for k, v in sc.items()}
+    ref = ops.forward_raw(t["background"], t["vertices"], t["vertex_colors"], t["faces"])
+    for call in range(3):                   # the hint is written by call 1 and read by calls 2 and 3
+        fwd = DirtForwardArgs(shape,
+                              ins["background"].data_ptr(), H * W * C, ins["vertices"].data_ptr(), V * 4,
+                              ins["vertex_colors"].data_ptr(), V * C, ins["faces"].data_ptr(), F * 3,
+                              outs["pixels"].data_ptr(), outs["face_id"].data_ptr(), outs["gbuffer"].data_ptr(),
+                              ws.data_ptr(), ws_bytes, hint.data_ptr(), hint_bytes)
+        _lib.check(lib.dirt_rasterise_forward(ctypes.byref(fwd), stream))
+        torch.cuda.synchronize()
+        assert arena.guards_intact(), "the forward wrote outside its buffers (call %d)" % call
+        assert torch.equal(outs["face_id"].view(torch.int32).view(B, H, W), ref[1])
+        assert torch.equal(outs["pixels"].view(torch.float32).view(B, H, W, C), ref[0])
+    hdr = hint[:16].view(torch.int32).tolist()
+    assert hdr[1:3] == [B, F] and hdr[3] in (2, 3)          # poison 0xFF is no valid header either: first call starts over
+    results = []
+    for _ in range(2):
+        for k in ("gv", "gc", "gbg"):
+            outs[k].fill_(0x5A)
+        bwd = DirtBackwardArgs(shape, ins["faces"].data_ptr(), F * 3, outs["pixels"].data_ptr(), gp.data_ptr(), None, None,
+                               outs["gv"].data_ptr(), V * 4, outs["gc"].data_ptr(), V * C, outs["gbg"].data_ptr(),
+                               ins["vertices"].data_ptr(), V * 4, bws.data_ptr(), bws_bytes, _lib.BACKWARD_DETERMINISTIC)
+        _lib.check(lib.dirt_rasterise_backward(ctypes.byref(bwd), stream))
+        torch.cuda.synchronize()
+        assert arena.guards_intact(), "the backward wrote outside its buffers"
+        results.append({k: outs[k].clone() for k in ("gv", "gc", "gbg")})
+    for k in ("gv", "gc", "gbg"):
+        assert torch.equal(results[0][k], results[1][k]), k + ": deterministic mode is not reproducible"
+    want = ops.backward_raw(t["faces"], ref[0], torch.from_numpy(g).cuda(), ref[1], ref[2], V)
+    for k, wt in (("gv", want[0]), ("gc", want[1])):
+        got = results[0][k].view(torch.float32).view(wt.shape)
+        assert float((got - wt).abs().max()) <= 1e-4 * float(wt.abs().max())
+    for k, tns in ins.items():
+        assert np.array_equal(tns.cpu().numpy(), np.ascontiguousarray(sc[k]).view(np.uint8).reshape(-1)), k + " was modified"

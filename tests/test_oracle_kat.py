@@ -86,6 +86,36 @@ def test_near_plane_crossing_keeps_barycentrics_of_original_vertices():
     assert (gb[0, :, :, 2][m] > 0).all()
 
 
+@pytest.mark.parametrize("winding", [(0, 1, 2), (0, 2, 1)])
+@pytest.mark.parametrize("plane", ["near", "far"])
+def test_depth_plane_clip_of_a_known_triangle_has_the_coverage_derived_by_hand(winding, plane):
+    """A known answer that owes nothing to this project's code: a triangle with w = 1 whose third corner lies
+    beyond the near (far) plane.  Clipping at z = -w (z = w) cuts the two edges that reach it at t = 3/4, i.e. at
+    NDC (-1/8, -1/4) and (1/8, -1/4); what is left is the trapezoid between y = -1/4 and y = 1/2 whose sides run from
+    (-1/2, 1/2) to (-1/8, -1/4) and from (1/2, 1/2) to (1/8, -1/4).  At 64 x 64 no pixel centre lies on any of its edges,
+    so the covered set follows from the OpenGL rule "centre inside the polygon" alone (OpenGL 3.3 core, 3.6.1 / 2.20)."""
+    W = H = 64
+    z_out = -1.5 if plane == "near" else 1.5
+    z_in = 0.5 if plane == "near" else -0.5
+    v = np.array([[-0.5, 0.5, z_in, 1.0], [0.5, 0.5, z_in, 1.0], [0.0, -0.5, z_out, 1.0]], np.float32)
+    px, fid, gb = golden.forward(np.zeros((H, W, 1)), v, np.ones((3, 1)), [list(winding)])
+    expect = np.zeros((H, W), bool)
+    for row in range(H):
+        y = (H - 1 - row) + 0.5                       # window y of the row's pixel centres, y up
+        if not (24.0 < y < 48.0):                     # -1/4 and 1/2 in NDC are 24 and 48 in window coordinates
+            continue
+        half = 16.0 - (48.0 - y) * 0.5                # half width: 16 px at the top edge, 4 px at the cut
+        xs = np.arange(W) + 0.5
+        expect[row] = np.abs(xs - 32.0) < half
+    assert expect.sum() > 400
+    assert np.array_equal(fid[0] >= 0, expect)
+    # window depth along the cut is the clip plane's: 0 (near) or 1 (far); the row of centres just above the cut is
+    # 1/48 of the way up the trapezoid's 24-px height in z, i.e. within 0.05 of it
+    cut_row = H - 1 - 24
+    d = gb[0, cut_row][expect[cut_row], 3]
+    assert np.all(np.abs(d - (0.0 if plane == "near" else 1.0)) < 0.05)
+
+
 def test_batch_local_indices_and_broadcast():
     sc = scenes.cube(B=3, H=48, W=48)
     px, fid, _ = _fwd(sc)

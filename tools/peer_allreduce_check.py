@@ -27,19 +27,22 @@ def main():
         src = torch.randn(sym.tensor.shape, device=dev, generator=g)
         ref = src.clone()
         dist.all_reduce(ref)
-        sym.tensor.copy_(src)
-        sym.allreduce("peer")
-        torch.cuda.synchronize()
-        err = float((sym.tensor - ref).abs().max() / ref.abs().max())
-        assert err < 1e-5, "peer all-reduce differs from NCCL by %g" % err
-        # every rank holds the same bits (the sum is taken in rank order)
-        mine = sym.tensor.clone()
-        other = mine.clone()
-        dist.broadcast(other, src=0)
-        assert torch.equal(mine, other), "ranks disagree"
-        out["max_rel_dev_vs_nccl"] = max(out.get("max_rel_dev_vs_nccl", 0.0), err)
+        for mode in ("peer", "peer_multicast") if sym.has_multicast else ("peer",):
+            sym.tensor.copy_(src)
+            dist.barrier()
+            sym.allreduce(mode)
+            torch.cuda.synchronize()
+            err = float((sym.tensor - ref).abs().max() / ref.abs().max())
+            assert err < 1e-5, "%s all-reduce differs from NCCL by %g" % (mode, err)
+            # every rank holds the same bits (one sum per slice, delivered to all)
+            mine = sym.tensor.clone()
+            other = mine.clone()
+            dist.broadcast(other, src=0)
+            assert torch.equal(mine, other), "ranks disagree (%s)" % mode
+            out["max_rel_dev_vs_nccl"] = max(out.get("max_rel_dev_vs_nccl", 0.0), err)
+        assert sym._peer[5].tolist()[1] == 0, "a handshake timed out"
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    modes = ["nccl", "peer", "two_shot"] + (["multimem"] if sym.has_multicast else [])
+    modes = ["nccl", "peer", "two_shot"] + (["peer_multicast", "multimem"] if sym.has_multicast else [])
     for mode in modes:
         try:
             for _ in range(5):

@@ -35,6 +35,17 @@ first = np.zeros(len(f), bool)
 if mode == "hint":
     _, fid0, _ = golden.forward(sc0["background"], sc0["vertices"], sc0["vertex_colors"], sc0["faces"], threads=8)
     first[np.unique(fid0[fid0 >= 0])] = True
+elif mode.startswith("tile="):
+    # per screen tile (centroid of the face's box) its own depth quantile: "tile=<fraction>,<tile px>"
+    q, tpx = mode[5:].split(",")
+    q, tpx = float(q), int(tpx)
+    cxs = np.clip((xmin + xmax) // 2 // tpx, 0, (W - 1) // tpx)
+    cys = np.clip((ymin + ymax) // 2 // tpx, 0, (H - 1) // tpx)
+    tid = cys * ((W - 1) // tpx + 1) + cxs
+    for t_ in np.unique(tid[valid]):
+        idx = np.nonzero(valid & (tid == t_))[0]
+        k = max(1, int(np.ceil(q * len(idx))))
+        first[idx[np.argsort(znear[idx], kind="stable")[:k]]] = True
 else:
     first[np.argsort(np.where(valid, znear, 9.0), kind="stable")[:int(float(mode) * len(f))]] = True
 first &= valid
