@@ -518,13 +518,23 @@ def run_ours(args, wl, rank, world, local_rank):
         losses.append(float(out_loss[(n - 1) % 2]))
 
     e2e_steps = max(2, min(args.steps, 12))
-    e2e_run(3)
-    barrier()
-    ev0.record()
-    e2e_run(e2e_steps)
-    ev1.record()
-    barrier()
-    e2e_ms = max_over_ranks(ev0.elapsed_time(ev1)) / e2e_steps
+
+    def e2e_time():
+        """ms per step: three timed runs of e2e_steps steps after a warm-up run, the MEDIAN of the three (the loop
+        synchronises with the host every step, so one stall of the host -- a page fault, the allocator -- would
+        otherwise double a 50 ms measurement); every run is max over ranks."""
+        e2e_run(3)
+        runs = []
+        for _ in range(3):
+            barrier()
+            ev0.record()
+            e2e_run(e2e_steps)
+            ev1.record()
+            barrier()
+            runs.append(max_over_ranks(ev0.elapsed_time(ev1)) / e2e_steps)
+        return sorted(runs)[1], runs
+
+    e2e_ms, e2e_runs = e2e_time()
     h2d = sum(host[k].numel() * host[k].element_size() for k in in_keys)
     bg_note = ""
     _, fid_now, _ = ops.forward_raw(d["background"], d["vertices"], d["vertex_colors"], d["faces"], want_aux=True)
@@ -534,7 +544,8 @@ def run_ours(args, wl, rank, world, local_rank):
                "pixels no face covers (%d bytes counted; the bus moves whole 32-byte sectors)" % (uncovered, B * H * W, uncovered * C * 4))
     d2h = out_gv[0].numel() * 4 + out_gc[0].numel() * 4 + 4
     e2e = {"value": world * B * H * W / (e2e_ms * 1e-3) / 1e6, "unit": UNIT, "h2d_bytes_per_step": h2d,
-           "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": e2e_steps, "last_loss": losses[-1],
+           "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms, "steps": e2e_steps, "runs_ms_per_step": e2e_runs,
+           "timing": "median of three runs of %d steps" % e2e_steps, "last_loss": losses[-1],
            "path": ("dirt_b200.rasterise_batch_shared" if shared else "dirt_b200.rasterise_batch") +
                    " + autograd backward; each step uploads its inputs (that step's vertex set) from pinned host "
                    "memory (one staging block, one cudaMemcpyAsync per step) and downloads loss + gradients; double-buffered over "
@@ -548,13 +559,7 @@ def run_ours(args, wl, rank, world, local_rank):
             dev_arena[slot].copy_(host_arena[0])         # faces now live in both buffer sets
         torch.cuda.synchronize()
         upload_bytes[0] = sum((host[k].numel() * host[k].element_size() + 255) // 256 * 256 for k in in_keys if k != "faces")
-        e2e_run(3)
-        barrier()
-        ev0.record()
-        e2e_run(e2e_steps)
-        ev1.record()
-        barrier()
-        ms_r = max_over_ranks(ev0.elapsed_time(ev1)) / e2e_steps
+        ms_r, _ = e2e_time()
         extra["e2e_resident_topology"] = {
             "value": world * B * H * W / (ms_r * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms_r, "steps": e2e_steps,
             "h2d_bytes_per_step": h2d - host["faces"].numel() * 4, "d2h_bytes_per_step": d2h,
@@ -564,13 +569,7 @@ def run_ours(args, wl, rank, world, local_rank):
         # image, tests/optimize_sequence.py:158-166: everything else is a graph constant on the device)
         upload_bytes[0] = (host["vertices"].numel() * 4 + 255) // 256 * 256
         e2e_bg[0] = d["background"]
-        e2e_run(3)
-        barrier()
-        ev0.record()
-        e2e_run(e2e_steps)
-        ev1.record()
-        barrier()
-        ms_v = max_over_ranks(ev0.elapsed_time(ev1)) / e2e_steps
+        ms_v, _ = e2e_time()
         extra["e2e_vertices_only"] = {
             "value": world * B * H * W / (ms_v * 1e-3) / 1e6, "unit": UNIT, "ms_per_step": ms_v, "steps": e2e_steps,
             "h2d_bytes_per_step": host["vertices"].numel() * 4, "d2h_bytes_per_step": d2h,
