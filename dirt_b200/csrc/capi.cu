@@ -44,7 +44,7 @@ inline size_t align_up(size_t v) { return (v + kAlign - 1) / kAlign * kAlign; }
 // Workspace carve-up.  Offsets are a pure function of the shape.
 struct Layout {
     size_t keys, proj, counters, tile_count, tile_cursor, bucket_count, tile_offset, big, queue, total;
-    size_t order, bucket_of, pivots, bucket_cursor, bucket_base, hiz, work_next, active_tiles;
+    size_t order, bucket_of, pivots, bucket_cursor, bucket_base, hiz, work_next, active_tiles, zvert;
     uint32_t hiz_off[dirt::kHizLevels];
     size_t zero_bytes;
     uint32_t cap_big;
@@ -70,6 +70,7 @@ Layout workspace_layout(const DirtShape &s)
     size_t off = 0;
     L.keys = off;        off = align_up(off + npix * sizeof(unsigned long long));
     L.proj = off;        off = align_up(off + (size_t)s.batch * s.vertex_count * 16);
+    L.zvert = off;       off = align_up(off + (size_t)s.batch * s.vertex_count * sizeof(float));
     L.counters = off;    off += dirt::kCtrCount * sizeof(uint32_t);
     L.tile_count = off;  off += ntiles * sizeof(uint32_t);
     L.tile_cursor = off; off += ntiles * sizeof(uint32_t);
@@ -217,6 +218,7 @@ int forward_impl(const DirtForwardArgs *a, void *stream, bool aux_only)
     p.keys = reinterpret_cast<unsigned long long *>(ws + L.keys);
     p.proj = reinterpret_cast<const int4 *>(ws + L.proj);
     p.proj_bs = a->vertices_bstride == 0 ? 0 : s.vertex_count;
+    p.zvert = reinterpret_cast<float *>(ws + L.zvert);
     p.counters = reinterpret_cast<uint32_t *>(ws + L.counters);
     p.tile_count = reinterpret_cast<uint32_t *>(ws + L.tile_count);
     p.tile_cursor = reinterpret_cast<uint32_t *>(ws + L.tile_cursor);

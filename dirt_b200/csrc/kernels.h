@@ -22,6 +22,8 @@ struct FwdParams {
     // workspace carve-up (see workspace_layout in capi.cu)
     const int4 *proj;            // [mB*V] projected vertices (k_project); mB = 1 when vertices are broadcast
     int64_t proj_bs;             // V, or 0 when vertices are broadcast
+    float *zvert;                // [mB*V] the window depth of every projected vertex again, packed (0 for a vertex that needs the
+                                 // clipper): the ordering pass gathers three of these per face instead of three 16-byte records
     unsigned long long *keys;    // [B*H*W] depth24 << 32 | face
     uint32_t *counters;          // [kCtrCount]; counters, tile_count, tile_cursor are contiguous
     uint32_t *tile_count;        // [B*tiles]

@@ -70,6 +70,7 @@ __global__ void __launch_bounds__(256) k_project(FwdParams p, int nbatch)
         }
         if (r.x == kProjSlow) p.counters[kCtrSlow] = 1u;      // k_resolve_clipped has work (benign race: everyone writes 1)
         const_cast<int4 *>(p.proj)[(int64_t)b * p.V + v] = r;
+        p.zvert[(int64_t)b * p.V + v] = r.x == kProjSlow ? 0.0f : __int_as_float(r.z);
     }
 }
 

@@ -288,3 +288,54 @@ def test_fuzz_vertex_normals(seed):
     assert np.abs(got[..., :3] - exp[..., :3]).max() <= 2e-4 * np.abs(exp).max()
     if D == 4:
         assert not got[..., 3].any()
+
+
+def _spiky_case(seed):
+    """The headline's kind of geometry -- a UV sphere with per-vertex radial noise: long slivers seen edge-on, depth
+    complexity ~10 -- at random sizes, zooms and offsets: partly outside the frame, so bounding boxes are cut by the
+    viewport and the 8-line chunks of the second occlusion test start and end inside pyramid tiles; sometimes so close
+    that faces cross the near plane."""
+    rng = np.random.RandomState(9000 + seed)
+    B = int(rng.randint(1, 3))
+    H, W = int(rng.randint(48, 260)), int(rng.randint(48, 260))
+    n_lat, n_lon = int(rng.randint(46, 90)), int(rng.randint(46, 90))
+    sc = scenes.sphere_frames(B, H, W, 3, n_lat, n_lon, fill=float(rng.uniform(0.3, 0.75)),
+                              seeds=(seed + 1, seed + 2, seed + 3, seed + 4))
+    sc = {k: np.ascontiguousarray(v).copy() for k, v in sc.items()}
+    zoom = float(rng.choice([0.6, 1.0, 1.7, 2.6]))
+    off = rng.uniform(-0.7, 0.7, size=2) if zoom > 1.0 else rng.uniform(-0.3, 0.3, size=2)
+    v = sc["vertices"]
+    v[..., 0] = v[..., 0] * zoom + off[0] * v[..., 3]
+    v[..., 1] = v[..., 1] * zoom + off[1] * v[..., 3]
+    if rng.randint(4) == 0:
+        v[..., 3] -= 2.2          # the camera moves into the object: w <= 0 for part of it, faces cross the near plane
+        v[..., 2] -= 2.2
+    return sc
+
+
+@pytest.mark.parametrize("seed", range(24))
+def test_fuzz_spiky_spheres_with_and_without_a_hint(seed):
+    import torch
+    from dirt_b200 import rasterise_ops as ops
+    sc = _spiky_case(seed)
+    t = {k: torch.from_numpy(v).cuda() for k, v in sc.items()}
+    B, V, F = sc["vertices"].shape[0], sc["vertices"].shape[1], sc["faces"].shape[1]
+    px, fid, gb = ops.forward_raw(t["background"], t["vertices"], t["vertex_colors"], t["faces"])
+    opx, ofid, ogb = golden.forward(sc["background"], sc["vertices"], sc["vertex_colors"], sc["faces"], threads=8)
+    assert np.array_equal(fid.cpu().numpy(), ofid), "face ids differ at %d pixels" % (fid.cpu().numpy() != ofid).sum()
+    np.testing.assert_allclose(px.cpu().numpy(), opx, rtol=1e-5, atol=1e-6)
+    np.testing.assert_allclose(gb.cpu().numpy(), ogb, rtol=1e-5, atol=1e-6)
+    # a hint of random bytes, then the hint that call left behind: same bits both times
+    hint = ops.visibility_hint(t["vertices"].device, B, F, key="fuzz-spiky")
+    hint.copy_(torch.randint(0, 256, (hint.numel(),), dtype=torch.uint8, device=hint.device,
+                             generator=torch.Generator(device=hint.device).manual_seed(seed)))
+    for _ in range(2):
+        hp, hf, hg = ops.forward_raw(t["background"], t["vertices"], t["vertex_colors"], t["faces"], hint=hint)
+        assert torch.equal(hf, fid) and torch.equal(hp, px) and torch.equal(hg, gb)
+    if seed % 4 == 0:
+        g = np.random.RandomState(seed).randn(*opx.shape).astype(np.float32)
+        gv, gc, gbg = ops.backward_raw(t["faces"], px, torch.from_numpy(g).cuda(), fid, gb, V)
+        ogv, ogc, ogbg = golden.backward(sc["faces"], opx, g, ofid, ogb, V, threads=8)
+        assert np.array_equal(gbg.cpu().numpy(), ogbg)
+        for a, b in ((gv.cpu().numpy(), ogv), (gc.cpu().numpy(), ogc)):
+            assert np.abs(a - b).max() <= 1e-4 * max(np.abs(b).max(), 1e-12)

@@ -7,7 +7,7 @@ import test_fuzz_gpu as t
 
 first, count = int(sys.argv[1]), int(sys.argv[2])
 families = [("forward_backward", t.test_fuzz_forward_backward, 1.0), ("depth_ordered", t.test_fuzz_depth_ordered_path, 0.25),
-            ("extreme", t.test_fuzz_extreme_geometry, 0.5), ("shared", t.test_fuzz_shared_mesh_backward, 0.2), ("dilate", t.test_fuzz_dilate, 0.2)]
+            ("extreme", t.test_fuzz_extreme_geometry, 0.5), ("spiky", t.test_fuzz_spiky_spheres_with_and_without_a_hint, 0.25), ("shared", t.test_fuzz_shared_mesh_backward, 0.2), ("dilate", t.test_fuzz_dilate, 0.2)]
 bad = 0
 for name, fn, share in families:
     n = int(count * share)
