@@ -88,7 +88,9 @@ typedef struct DirtForwardArgs {
      * others against the nearly final depth buffer they leave.  The hint only ORDERS work: the
      * output is bit-identical with a fresh, a stale or a wrong hint, or none (NULL).  Zero it once
      * after allocating (any content is safe, zero merely avoids a slow first call); one buffer per
-     * mesh and per stream, not shared between calls in flight.  Used by meshes of >= 4096 faces. */
+     * mesh and per stream, not shared between calls in flight.  Used by meshes of >= 4096 faces.
+     * Measured on the 100k-face sphere workloads it is no faster than the depth-ordered plan the
+     * library uses without a hint: an option, not a recommendation. */
     void *visibility_hint;
     size_t visibility_hint_bytes;
 } DirtForwardArgs;
