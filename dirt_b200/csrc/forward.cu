@@ -324,6 +324,8 @@ __global__ void __launch_bounds__(256, KRES_CTAS) k_resolve(FwdParams p)
 {
     const int CC = C > 0 ? C : p.C;
     const int npix = p.H * p.W;
+    // visibility hint for the next call on this mesh: a face that wins a pixel is stamped with the next generation
+    const uint8_t stamp = p.vis_flags ? (uint8_t)hint_next_generation(hint_generation(p)) : (uint8_t)0;
     // kResolvePix pixels per thread: a CTA that resolves only 256 pixels is launch-rate bound.
     // The gather chain key -> face -> corners is software-pipelined over those pixels: the key of
     // pixel j+2 and the corner indices of pixel j+1 are in flight while pixel j is shaded.
@@ -371,6 +373,16 @@ __global__ void __launch_bounds__(256, KRES_CTAS) k_resolve(FwdParams p)
         const int f = (int)(uint32_t)(key & 0xFFFFFFFFull);
         const int4 *pp = proj_ptr(p, b);
         const int4 ra = __ldg(pp + i0), rb = __ldg(pp + i1), rc = __ldg(pp + i2);
+        if (p.vis_flags) {
+            // One byte store per run of pixels a face owns along a row, not per pixel: the lanes of a warp hold
+            // neighbouring pixels, and a lane whose left neighbour (if it is here: the covered lanes of the warp)
+            // has the same face leaves the store to it.  A missed or doubled store only costs time: the hint orders work.
+            const unsigned here = __activemask();
+            const uint32_t left = __shfl_up_sync(here, (uint32_t)f, 1);
+            const int lane = threadIdx.x & 31;
+            if (lane == 0 || !((here >> (lane - 1)) & 1u) || left != (uint32_t)f)
+                p.vis_flags[(size_t)b * p.F + (uint32_t)f] = stamp;
+        }
         float B0 = 0.f, B1 = 0.f, wc = 1.f;
         if (ra.x != kProjSlow && rb.x != kProjSlow && rc.x != kProjSlow) {
             // the pixel is known to be covered: only the sign and 1/area of the setup are needed
@@ -431,44 +443,15 @@ __global__ void __launch_bounds__(256, KRES_CTAS) k_resolve(FwdParams p)
 // weights through the clipped fan and rewrites colour and G-buffer with the formulas of k_resolve.
 __global__ void __launch_bounds__(256) k_resolve_clipped(FwdParams p)
 {
-    if (p.hint_hdr) {
-        // Visibility hint for the next call on this mesh: every face that won a pixel is stamped with the next
-        // generation.  One pass over the keys, a warp on 32 neighbouring pixels: a face is stamped once per run of
-        // pixels it owns along a row (visible faces cover many pixels; measured inside k_resolve, a load-compare-
-        // store per covered pixel cost that kernel 60 %).  The generation is published by the kernel's last block.
-        const uint32_t next = hint_next_generation(hint_generation(p));
-        const int hw = p.H * p.W;                                // below 2^30: check_shape
-        const int per_round = 4 * (int)(gridDim.x * blockDim.x);
-        const int rounds = (hw + per_round - 1) / per_round;
-        for (int b = blockIdx.y; b < p.B; b += gridDim.y) {
-            const unsigned long long *kb = p.keys + (size_t)b * hw;
-            uint8_t *fl = p.vis_flags + (size_t)b * p.F;
-            for (int r = 0; r < rounds; ++r) {                   // every lane runs every round: the shuffle needs full warps
-                unsigned long long key[4];
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {                    // four independent loads in flight per thread
-                    const long long at = ((long long)(r * 4 + u) * gridDim.x + blockIdx.x) * blockDim.x + threadIdx.x;
-                    key[u] = at < hw ? kb[at] : kKeyEmpty;
-                }
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const uint32_t f = (uint32_t)key[u];
-                    const uint32_t left = __shfl_up_sync(0xFFFFFFFFu, f, 1);
-                    if (key[u] != kKeyEmpty && ((threadIdx.x & 31) == 0 || left != f)) fl[f] = (uint8_t)next;
-                }
-            }
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            __threadfence();
-            if (atomicAdd(p.counters + kCtrHintTicket, 1u) == gridDim.x * gridDim.y - 1)
-                *reinterpret_cast<uint4 *>(p.hint_hdr) = make_uint4(kHintMagic, (uint32_t)p.B, (uint32_t)p.F, next);
-        }
+    if (p.hint_hdr && blockIdx.x == 0 && threadIdx.x == 0) {
+        // k_resolve has stamped this call's visible faces with the next generation (as a pass of its own over the key
+        // buffer the stamping cost 0.06 ms, as a load-compare-store per pixel in k_resolve 0.14, as it is now 0.02): publish it
+        *reinterpret_cast<uint4 *>(p.hint_hdr) = make_uint4(kHintMagic, (uint32_t)p.B, (uint32_t)p.F, hint_next_generation(hint_generation(p)));
     }
     if (p.counters[kCtrSlow] == 0u) return;
     const FwdParams pc = p;      // resolve_clipped takes a reference: keep the parameter block itself out of local memory
     const int npix = pc.H * pc.W, CC = pc.C;
-    for (int b = blockIdx.y; b < pc.B; b += gridDim.y) {
+    for (int b = 0; b < pc.B; ++b) {
         const unsigned long long *kb = pc.keys + (size_t)b * npix;
         const int4 *pp = proj_ptr(pc, b);
         for (int o = blockIdx.x * blockDim.x + threadIdx.x; o < npix; o += gridDim.x * blockDim.x) {
@@ -526,15 +509,7 @@ static cudaError_t launch_resolve(const FwdParams &p, cudaStream_t stream, uint6
         // empty CTAs would cost more than the few microseconds of the launch itself
         long long gx = ((long long)p.H * p.W + 255) / 256;
         if (gx > 592) gx = 592;
-        dim3 g((unsigned)gx, 1);
-        if (p.hint_hdr) {
-            // it also walks every key once (visibility hint): about eight CTAs per SM, elements along y
-            const long long per_elem = ((long long)p.H * p.W + 1023) / 1024;
-            g.y = (unsigned)(p.B < 1184 ? p.B : 1184);
-            long long want = (1184 + g.y - 1) / g.y;
-            g.x = (unsigned)(want < per_elem ? want : per_elem);
-            if (g.x < 1) g.x = 1;
-        }
+        const dim3 g((unsigned)gx, 1);
         k_resolve_clipped<<<g, 256, 0, stream>>>(p);
     }
     tm.end(kStageResolve, stream);

@@ -7,7 +7,7 @@
 
 namespace dirt {
 
-enum { kCtrBig = 0, kCtrQueue = 1, kCtrOverdraw = 2, kCtrActiveTiles = 3, kCtrSlow = 8, kCtrHintTicket = 11, kCtrCount = 12 };   // 4..7, 9, 10: -DDIRT_STATS; kCtrHintTicket: blocks of k_resolve_clipped that have stamped their share of the visibility hint; kCtrSlow: some vertex needs the clip path; kCtrOverdraw: float bits, see depth_order.cu
+enum { kCtrBig = 0, kCtrQueue = 1, kCtrOverdraw = 2, kCtrActiveTiles = 3, kCtrSlow = 8, kCtrCount = 12 };   // 4..7, 9, 10: -DDIRT_STATS; kCtrSlow: some vertex needs the clip path; kCtrOverdraw: float bits, see depth_order.cu
 
 struct FwdParams {
     int B, H, W, C, V, F;

@@ -89,8 +89,9 @@ typedef struct DirtForwardArgs {
      * output is bit-identical with a fresh, a stale or a wrong hint, or none (NULL).  Zero it once
      * after allocating (any content is safe, zero merely avoids a slow first call); one buffer per
      * mesh and per stream, not shared between calls in flight.  Used by meshes of >= 4096 faces.
-     * Measured on the 100k-face sphere workloads it is no faster than the depth-ordered plan the
-     * library uses without a hint: an option, not a recommendation. */
+     * Measured on the 100k-face sphere workloads: 2 % faster at 512 x 512, 5 % slower at 256 x 256 than
+     * the depth-ordered plan the library uses without a hint: an option, not a
+     * recommendation. */
     void *visibility_hint;
     size_t visibility_hint_bytes;
 } DirtForwardArgs;
