@@ -398,6 +398,7 @@ cudaError_t launch_backward(const BwdParams &p, int sm_count, cudaStream_t strea
     switch (p.C) {
         case 1: k_grad_assemble<1, 0><<<grid, kThreads, 0, stream>>>(p); break;
         case 3: k_grad_assemble<3, 0><<<grid, kThreads, 0, stream>>>(p); break;
+        case 9: k_grad_assemble<9, 0><<<grid, kThreads, 0, stream>>>(p); break;      // the deferred G-buffer of samples/deferred.py in one call
         default: k_grad_assemble<0, 0><<<grid, kThreads, 0, stream>>>(p); break;
     }
     tm.end(kStageGradAssemble, stream);

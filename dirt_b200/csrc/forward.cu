@@ -502,6 +502,7 @@ static cudaError_t launch_resolve(const FwdParams &p, cudaStream_t stream, uint6
     switch (p.C) {
         case 1: k_resolve<1><<<g, 256, 0, stream>>>(p); break;
         case 3: k_resolve<3><<<g, 256, 0, stream>>>(p); break;
+        case 9: k_resolve<9><<<g, 256, 0, stream>>>(p); break;
         default: k_resolve<0><<<g, 256, 0, stream>>>(p); break;
     }
     {

@@ -21,6 +21,12 @@ def scene(name):
         return scenes.sphere(256, 256, 256)
     if name == "c3":
         return scenes.cube(B=16, H=512, W=512)
+    if name == "c3g":                     # the deferred G-buffer call of samples/deferred.py as ONE 9-channel call
+        sc = scenes.cube(B=16, H=512, W=512)
+        rng = np.random.RandomState(3)
+        sc["vertex_colors"] = rng.uniform(0, 1, sc["vertex_colors"].shape[:2] + (9,)).astype(np.float32)
+        sc["background"] = np.zeros(sc["background"].shape[:3] + (9,), np.float32)
+        return sc
     if name == "c2":
         return scenes.cube(B=1, H=256, W=256)
     if name == "c1":                      # README.md:46-70, forward only
