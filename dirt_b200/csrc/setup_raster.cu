@@ -26,11 +26,20 @@ namespace dirt {
 
 constexpr unsigned kFullMask = 0xFFFFFFFFu;
 constexpr int kWarpsPerCta = 8;
+// Resident CTAs per SM and fragments per round, per launch kind (A/B in profiles/r2_setup_notes.md):
+// the blind launch is bound by the reductions it issues, not by latency, and runs best with 64
+// registers (4 CTAs); the pyramid-tested launches wait on depth loads and want occupancy (6 CTAs).
 #ifndef KCTAS
-#define KCTAS 6
+#define KCTAS 4
+#endif
+#ifndef KCTAS_HIZ
+#define KCTAS_HIZ 6
 #endif
 #ifndef KFRAG
-#define KFRAG 2
+#define KFRAG 4
+#endif
+#ifndef KFRAG_HIZ
+#define KFRAG_HIZ 4
 #endif
 #ifndef KPRE0
 #define KPRE0 0
@@ -45,7 +54,10 @@ constexpr int kWarpsPerCta = 8;
 #define KLDCG 0      // 1: the depth pre-load bypasses L1 (sees the reductions of this launch)
 #endif
 constexpr int kCtasPerSm = KCTAS;                     // the kernel waits on depth loads: occupancy over registers
-constexpr int kFragRound = KFRAG;                     // spans are 1-2 pixels on 3 lines out of 4 (profiles/r1_setup_notes.md)
+constexpr int kCtasPerSmHiz = KCTAS_HIZ;              // the launches that test against the pyramid
+constexpr int ctas_per_sm(bool hiz) { return hiz ? kCtasPerSmHiz : kCtasPerSm; }
+constexpr int kFragRoundBlind = KFRAG;            // launch 0: no pre-load, the round only unrolls the loop
+constexpr int kFragRoundHiz = KFRAG_HIZ;                   // spans are 1-2 pixels on 3 lines out of 4 (profiles/r1_setup_notes.md)
 constexpr long long kFewFaces = 4096;
 constexpr float kLineRcpAreaMin = 1.0f / (2.0f * 65536.0f * 1024.0f);   // 1 / |2 area| of a 1024 px triangle: fatter ones go to the tile path
 
@@ -199,6 +211,7 @@ __device__ __forceinline__ void sample_line(const uint32_t *rec, int j, const Fw
     float fi = __int2float_rn(lo);
     // kFragRound fragments per round: their current depths are fetched together (independent
     // loads), so a line pays the memory latency once per round instead of once per fragment.
+    constexpr int kFragRound = PRELOAD ? kFragRoundHiz : kFragRoundBlind;
     for (int i = lo; i <= hi; i += kFragRound) {
         const int n = hi - i + 1;
         uint32_t cur[kFragRound];
@@ -350,7 +363,7 @@ __device__ __forceinline__ bool chunk_visible(const uint32_t *rec, int ja, int j
 // that are tested again, each against the 8-px tiles it touches (chunk_visible).  Otherwise all
 // faces in index order.
 template <bool ORDERED, bool HIZ>
-__global__ void __launch_bounds__(kWarpsPerCta * 32, kCtasPerSm) k_setup(FwdParams p, int k0, int k1, int launch_index, float min_overdraw)
+__global__ void __launch_bounds__(kWarpsPerCta * 32, ctas_per_sm(HIZ)) k_setup(FwdParams p, int k0, int k1, int launch_index, float min_overdraw)
 {
     __shared__ __align__(16) uint32_t s_recs[kWarpsPerCta][32 * kRecWords];
     __shared__ uint8_t s_owner[kWarpsPerCta][32];
@@ -528,9 +541,11 @@ void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_
     const long long nfaces = (long long)p.B * p.F;
     launch_project(p, sm_count, stream, tm);
     long long g = (nfaces + kWarpsPerCta * 32 - 1) / (kWarpsPerCta * 32);
-    const long long cap = (long long)sm_count * kCtasPerSm;        // resident CTAs: work is claimed dynamically
-    if (g > cap) g = cap;
-    if (g < 1) g = 1;
+    const long long gall = g < 1 ? 1 : g;
+    auto grid_for = [&](bool hiz) {                                 // resident CTAs: work is claimed dynamically
+        const long long cap = (long long)sm_count * ctas_per_sm(hiz);
+        return (int)(gall > cap ? cap : gall);
+    };
     const BucketPlan plan = bucket_plan();
     if (p.order && plan.n > 0) {
         // front-to-back buckets; the hierarchical depth buffer is refreshed between them
@@ -544,8 +559,8 @@ void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_
                 tm.end(kStageHizBuild, stream);
             }
             tm.begin(kStageSetup, stream);
-            if (j == 0) k_setup<true, false><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, plan.launch_first[j], plan.launch_first[j + 1] - 1, j, plan.min_overdraw);
-            else k_setup<true, true><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, plan.launch_first[j], plan.launch_first[j + 1] - 1, j, plan.min_overdraw);
+            if (j == 0) k_setup<true, false><<<grid_for(false), kWarpsPerCta * 32, 0, stream>>>(p, plan.launch_first[j], plan.launch_first[j + 1] - 1, j, plan.min_overdraw);
+            else k_setup<true, true><<<grid_for(true), kWarpsPerCta * 32, 0, stream>>>(p, plan.launch_first[j], plan.launch_first[j + 1] - 1, j, plan.min_overdraw);
             tm.end(kStageSetup, stream);
 #ifdef DIRT_STATS
             uint32_t c[12], bb[kMaxBuckets + 1];
@@ -559,7 +574,7 @@ void launch_setup(const FwdParams &p, int sm_count, cudaStream_t stream, uint64_
         *launches += (plan.n == 2 ? 2 : 4) + 2 * plan.nlaunch - 1;     // ordering kernels + setup launches + pyramid builds
     } else {
         tm.begin(kStageSetup, stream);
-        k_setup<false, false><<<(int)g, kWarpsPerCta * 32, 0, stream>>>(p, 0, 0, 0, 0.0f);
+        k_setup<false, false><<<grid_for(false), kWarpsPerCta * 32, 0, stream>>>(p, 0, 0, 0, 0.0f);
         tm.end(kStageSetup, stream);
         *launches += 1;
     }
