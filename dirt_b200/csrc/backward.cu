@@ -373,13 +373,18 @@ cudaError_t launch_backward(const BwdParams &p, int sm_count, cudaStream_t strea
     }
     tm.end(kStageGradClear, stream);
     if ((long long)p.B * p.H * p.W == 0) return cudaSuccess;
-    // each CTA walks several batch elements: tiles are small, and a grid of ~32 CTAs per SM is
-    // enough to balance without paying a block launch per 192 pixels
+    // each CTA walks several batch elements: tiles are small, and a grid of ~96 CTAs per SM balances
+    // without paying a block launch per 192 pixels (32 per SM: 2.7 % slower, one CTA per tile and element: 4 % slower;
+    // profiles/r2_setup_notes.md)
     const long long tiles = (long long)((p.W + kTX - 1) / kTX) * ((p.H + kTY - 1) / kTY);
-    long long gz = ((long long)sm_count * 32 + tiles - 1) / tiles;
+#ifndef KBWD_WAVES
+#define KBWD_WAVES 96
+#endif
+    long long gz = ((long long)sm_count * KBWD_WAVES + tiles - 1) / tiles;
     if (gz > p.B) gz = p.B;
     if (gz > 65535) gz = 65535;
     if (gz < 1) gz = 1;
+    gz = (p.B + (p.B + gz - 1) / gz - 1) / ((p.B + gz - 1) / gz);       // same number of loop trips, spread evenly
     const dim3 grid((p.W + kTX - 1) / kTX, (p.H + kTY - 1) / kTY, (unsigned)gz);
     tm.begin(kStageGradAssemble, stream);
     if (p.det_pos) {

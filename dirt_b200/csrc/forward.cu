@@ -313,7 +313,10 @@ static __device__ __noinline__ void resolve_clipped(const FwdParams &p, int b, i
     }
 }
 
-constexpr int kResolvePix = 8;
+#ifndef KRES_PIX
+#define KRES_PIX 8
+#endif
+constexpr int kResolvePix = KRES_PIX;
 
 // S4: one thread per pixel (kResolvePix of them in turn); blockIdx.y walks the batch.
 #ifndef KRES_CTAS
