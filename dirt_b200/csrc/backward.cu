@@ -29,8 +29,14 @@
 namespace dirt {
 
 constexpr unsigned kFull = 0xFFFFFFFFu;
-constexpr int kThreads = 256;
-constexpr int kTX = 16, kTY = 12;       // interior (output) pixels per CTA
+#ifndef KBWD_TY
+#define KBWD_TY 12
+#endif
+#ifndef KBWD_THREADS
+#define KBWD_THREADS 256
+#endif
+constexpr int kThreads = KBWD_THREADS;
+constexpr int kTX = 16, kTY = KBWD_TY;       // interior (output) pixels per CTA
 constexpr int kRX = kTX + 2, kRY = kTY + 2;   // pixels that compute a response (interior + ring)
 constexpr int kSX = kTX + 4, kSY = kTY + 4;   // staged region
 constexpr int kInteriorWarps = (kTX / 8) * (kTY / 4);
