@@ -61,6 +61,17 @@ class DirtPeerAllreduceArgs(ctypes.Structure):
                 ("count", _i64), ("epoch", ctypes.c_void_p), ("multicast", ctypes.c_void_p)]
 
 
+class DirtVertexShadeArgs(ctypes.Structure):
+    _fields_ = [("batch", ctypes.c_int), ("vertex_count", ctypes.c_int), ("channels", ctypes.c_int), ("double_sided", ctypes.c_int),
+                ("positions", ctypes.c_void_p), ("normals", ctypes.c_void_p), ("colours", ctypes.c_void_p),
+                ("light_vector", ctypes.c_void_p), ("light_vector_bstride", _i64),
+                ("light_color", ctypes.c_void_p), ("light_color_bstride", _i64),
+                ("camera_position", ctypes.c_void_p), ("camera_position_bstride", _i64),
+                ("shininess", ctypes.c_void_p), ("shininess_bstride", _i64),
+                ("out", ctypes.c_void_p), ("grad_out", ctypes.c_void_p),
+                ("grad_positions", ctypes.c_void_p), ("grad_normals", ctypes.c_void_p), ("grad_colours", ctypes.c_void_p)]
+
+
 class DirtSceneArgs(ctypes.Structure):
     _fields_ = [("shape", DirtShape),
                 ("background", _f32p), ("background_bstride", _i64),
@@ -98,6 +109,10 @@ EXPORTS = {
                                  [ctypes.c_int] * 4 + [ctypes.c_void_p, ctypes.c_void_p]),
     "dirt_diffuse_directional_grad": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, _i64, ctypes.c_void_p, _i64] +
                                       [ctypes.c_int] * 4 + [ctypes.c_void_p] * 4),
+    "dirt_diffuse_point": (ctypes.c_int, [ctypes.POINTER(DirtVertexShadeArgs), ctypes.c_void_p]),
+    "dirt_diffuse_point_grad": (ctypes.c_int, [ctypes.POINTER(DirtVertexShadeArgs), ctypes.c_void_p]),
+    "dirt_specular_directional": (ctypes.c_int, [ctypes.POINTER(DirtVertexShadeArgs), ctypes.c_void_p]),
+    "dirt_specular_directional_grad": (ctypes.c_int, [ctypes.POINTER(DirtVertexShadeArgs), ctypes.c_void_p]),
     "dirt_dilate_silhouette": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p] + [ctypes.c_int] * 4 + [ctypes.c_void_p]),
     "dirt_dilate_silhouette_grad": (ctypes.c_int, [ctypes.c_void_p] * 3 + [ctypes.c_int] * 4 + [ctypes.c_void_p]),
     "dirt_kernel_launch_count": (ctypes.c_uint64, []),

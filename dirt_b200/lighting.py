@@ -6,9 +6,10 @@ and reduces it (dirt/lighting.py:74-88) -- and runs as hand-written CUDA kernels
 (`dirt_vertex_normals`, `dirt_vertex_normals_grad`; dirt_b200/csrc/geometry.cu) with autograd wired.
 `diffuse_directional`, the shading of the c5 optimisation step, is one fused CUDA pass per direction
 (`dirt_diffuse_directional(_grad)`, csrc/lighting.cu: its torch composites took a third of that step,
-profiles/r2_c5_step_breakdown.json).  The other shading functions are per-point arithmetic written with
-torch operations (one to five element-wise kernels each, differentiable by torch), formula by formula as
-the reference has them, including its `+ 1e-12` terms.
+profiles/r2_c5_step_breakdown.json); `diffuse_point` and `specular_directional` likewise
+(`dirt_diffuse_point(_grad)`, `dirt_specular_directional(_grad)`).  Calls the fused kernels do not serve (CPU
+tensors, other dtypes, a gradient w.r.t. a light, the camera or the shininess) take the reference's formula in
+torch operations, formula by formula as the reference has them, including its `+ 1e-12` terms.
 """
 import ctypes
 
@@ -200,13 +201,88 @@ def diffuse_directional(vertex_normals, vertex_colors, light_direction, light_co
     return lc.unsqueeze(-2) * c * _cosine_term(cosines, double_sided)
 
 
+class _VertexShade(torch.autograd.Function):
+    """`diffuse_point` / `specular_directional` as one CUDA pass forward and one backward (csrc/lighting.cu)."""
+
+    @staticmethod
+    def _args(specular, p, n, c, lv, lc, cam, sh, double_sided):
+        V, C = c.shape[-2], c.shape[-1]
+        a = _lib.DirtVertexShadeArgs()
+        a.batch, a.vertex_count, a.channels, a.double_sided = c.numel() // max(V * C, 1), V, C, int(bool(double_sided))
+        a.positions, a.normals, a.colours = p.data_ptr(), n.data_ptr(), c.data_ptr()
+        a.light_vector, a.light_vector_bstride = lv.data_ptr(), (3 if lv.dim() > 1 else 0)
+        a.light_color, a.light_color_bstride = lc.data_ptr(), (C if lc.dim() > 1 else 0)
+        if specular:
+            a.camera_position, a.camera_position_bstride = cam.data_ptr(), (3 if cam.dim() > 1 else 0)
+            a.shininess, a.shininess_bstride = sh.data_ptr(), (1 if sh.dim() > 0 else 0)
+        return a
+
+    @staticmethod
+    def forward(ctx, specular, p, n, c, lv, lc, cam, sh, double_sided):
+        lib = _lib.load()
+        tensors = [t.contiguous() if t is not None else None for t in (p, n, c, lv, lc, cam, sh)]
+        p, n, c, lv, lc, cam, sh = tensors
+        out = torch.empty_like(c)
+        a = _VertexShade._args(specular, p, n, c, lv, lc, cam, sh, double_sided)
+        a.out = out.data_ptr()
+        with torch.cuda.device(c.device):
+            fn = lib.dirt_specular_directional if specular else lib.dirt_diffuse_point
+            _lib.check(fn(ctypes.byref(a), torch.cuda.current_stream(c.device).cuda_stream))
+        ctx.save_for_backward(*[t for t in tensors if t is not None])
+        ctx.meta = (specular, bool(double_sided))
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        specular, double_sided = ctx.meta
+        saved = list(ctx.saved_tensors)
+        p, n, c, lv, lc = saved[:5]
+        cam, sh = (saved[5], saved[6]) if specular else (None, None)
+        lib = _lib.load()
+        g = g.contiguous()
+        gp = torch.empty_like(p) if ctx.needs_input_grad[1] else None
+        gn = torch.empty_like(n) if ctx.needs_input_grad[2] else None
+        gc = torch.empty_like(c) if ctx.needs_input_grad[3] else None
+        a = _VertexShade._args(specular, p, n, c, lv, lc, cam, sh, double_sided)
+        a.grad_out = g.data_ptr()
+        a.grad_positions = gp.data_ptr() if gp is not None else None
+        a.grad_normals = gn.data_ptr() if gn is not None else None
+        a.grad_colours = gc.data_ptr() if gc is not None else None
+        with torch.cuda.device(c.device):
+            fn = lib.dirt_specular_directional_grad if specular else lib.dirt_diffuse_point_grad
+            _lib.check(fn(ctypes.byref(a), torch.cuda.current_stream(c.device).cuda_stream))
+        return None, gp, gn, gc, None, None, None, None, None
+
+
+def _fusable_shade(p, n, c, lights, per_batch_scalars=()):
+    """As _fusable, for the helpers that also take positions: `lights` are the [3] / [*, 3] / [C] / [*, C] inputs,
+    `per_batch_scalars` the [] / [*] ones; none of them may want a gradient."""
+    small = tuple(lights) + tuple(per_batch_scalars)
+    if not all(t.is_cuda and t.dtype == torch.float32 for t in (p, n, c) + small) or any(t.requires_grad for t in small):
+        return False
+    if c.dim() < 2 or p.shape != n.shape or p.dim() != c.dim() or p.shape[:-1] != c.shape[:-1] or p.shape[-1] != 3:
+        return False
+    if not (1 <= c.shape[-1] <= 16):
+        return False
+    lead = c.shape[:-2]
+    for t in lights:
+        if t.dim() == 0 or not (t.shape == (t.shape[-1],) or t.shape == lead + (t.shape[-1],)) or t.shape[-1] not in (3, c.shape[-1]):
+            return False
+    return all(t.dim() == 0 or t.shape == lead for t in per_batch_scalars)
+
+
 def specular_directional(vertex_positions, vertex_normals, vertex_reflectivities, light_direction, light_color,
                          camera_position, shininess, double_sided=True, name=None):
     """Phong reflectance under one directional light (dirt/lighting.py:228-288), including the
-    reference's operator precedence: the 1e-12 is added AFTER the division by the norm."""
+    reference's operator precedence: the 1e-12 is added AFTER the division by the norm.
+    CUDA float32 inputs run as one fused kernel per direction (csrc/lighting.cu), everything else in torch ops."""
     del name
     p, n, r, d, lc, cam, sh = (torch.as_tensor(x) for x in (vertex_positions, vertex_normals, vertex_reflectivities,
                                                             light_direction, light_color, camera_position, shininess))
+    if r.is_cuda and not sh.is_cuda and not sh.requires_grad:
+        sh = sh.to(device=r.device, dtype=torch.float32)          # the usual call passes a Python number
+    if _fusable_shade(p, n, r, (d, lc, cam), (sh,)) and d.shape[-1] == 3 and cam.shape[-1] == 3 and lc.shape[-1] == r.shape[-1]:
+        return _VertexShade.apply(True, p, n, r, d, lc, cam, sh, double_sided)
     to_light = -d
     reflected = -to_light.unsqueeze(-2) + 2. * torch.matmul(n, to_light.unsqueeze(-1)) * n
     to_camera = cam.unsqueeze(-2) - p
@@ -215,9 +291,12 @@ def specular_directional(vertex_positions, vertex_normals, vertex_reflectivities
 
 
 def diffuse_point(vertex_positions, vertex_normals, vertex_colors, light_position, light_color, double_sided=True, name=None):
-    """Lambertian reflectance under one point light (dirt/lighting.py:291-343)."""
+    """Lambertian reflectance under one point light (dirt/lighting.py:291-343).
+    CUDA float32 inputs run as one fused kernel per direction (csrc/lighting.cu), everything else in torch ops."""
     del name
     p, n, c, lp, lc = (torch.as_tensor(x) for x in (vertex_positions, vertex_normals, vertex_colors, light_position, light_color))
+    if _fusable_shade(p, n, c, (lp, lc)) and lp.shape[-1] == 3 and lc.shape[-1] == c.shape[-1]:
+        return _VertexShade.apply(False, p, n, c, lp, lc, None, None, double_sided)
     relative = p - lp.unsqueeze(-2)
     incident = relative / (relative.norm(dim=-1, keepdim=True) + 1.e-12)
     cosines = (n * incident).sum(dim=-1)

@@ -200,6 +200,35 @@ DIRT_API int dirt_diffuse_directional_grad(const float *normals, const float *co
                                            int double_sided, int batch, int vertex_count, int channels, const float *grad_out,
                                            float *grad_normals, float *grad_colours, void *stream);
 
+/* The other two per-vertex shading helpers of dirt/lighting.py, each ONE element-wise pass forward and ONE backward:
+ *   dirt_diffuse_point         Lambertian reflectance under one point light (dirt/lighting.py:291-343):
+ *                              inc = (p - light_position) / (|p - light_position| + 1e-12),
+ *                              out = light_color * colours * f(normals . inc)
+ *   dirt_specular_directional  Phong reflectance under one directional light (dirt/lighting.py:228-288), with the
+ *                              reference's operator precedence (1e-12 is added AFTER the division by the norm):
+ *                              L = -light_direction, R = -L + 2 (n . L) n, T = (camera - p) / |camera - p| + 1e-12,
+ *                              out = light_color * reflectivities * f(T . R) ^ shininess
+ * f = |.| when double_sided, else max(., 0).  positions / normals [batch,V,3]; colours (vertex_colors resp.
+ * vertex_reflectivities), out, grad_out, grad_colours [batch,V,C]; light_vector = light_position resp. light_direction
+ * [*,3]; light_color [*,C]; camera_position [*,3] and shininess [*] (specular only): DEVICE pointers, `*_bstride`
+ * elements apart per batch element (0: one for all).  The *_grad calls read grad_out and write the gradients that are
+ * not NULL; gradients w.r.t. lights, camera and shininess are left to the caller. */
+typedef struct DirtVertexShadeArgs {
+    int batch, vertex_count, channels, double_sided;
+    const float *positions, *normals, *colours;
+    const float *light_vector;      int64_t light_vector_bstride;
+    const float *light_color;       int64_t light_color_bstride;
+    const float *camera_position;   int64_t camera_position_bstride;
+    const float *shininess;         int64_t shininess_bstride;
+    float *out;
+    const float *grad_out;
+    float *grad_positions, *grad_normals, *grad_colours;
+} DirtVertexShadeArgs;
+DIRT_API int dirt_diffuse_point(const DirtVertexShadeArgs *args, void *stream);
+DIRT_API int dirt_diffuse_point_grad(const DirtVertexShadeArgs *args, void *stream);
+DIRT_API int dirt_specular_directional(const DirtVertexShadeArgs *args, void *stream);
+DIRT_API int dirt_specular_directional_grad(const DirtVertexShadeArgs *args, void *stream);
+
 /* Library identity. */
 DIRT_API int dirt_abi_version(void);
 /* Thread-local message of the last failing call on this thread ("" if none). */

@@ -211,3 +211,76 @@ def test_fused_diffuse_directional_matches_the_composite_and_the_oracle(double_s
     # a gradient w.r.t. the light, or CPU tensors, take the torch formula
     assert not lighting._fusable(tn, tc, td.clone().requires_grad_(True), tl)
     assert not lighting._fusable(tn.cpu(), tc.cpu(), td.cpu(), tl.cpu())
+
+
+def _shade_inputs(rng, B, V, C, batched):
+    p = rng.uniform(-1, 1, (B, V, 3)).astype(np.float32)
+    n = rng.randn(B, V, 3).astype(np.float32)
+    n /= np.linalg.norm(n, axis=-1, keepdims=True)
+    col = rng.uniform(0, 1, (B, V, C)).astype(np.float32)
+    lc = rng.uniform(0.2, 1, (B, C) if batched else (C,)).astype(np.float32)
+    g = rng.randn(B, V, C).astype(np.float32)
+    return p, n, col, lc, g
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("double_sided", [True, False])
+@pytest.mark.parametrize("batched", [False, True])
+@pytest.mark.parametrize("C", [1, 3])
+def test_fused_diffuse_point_matches_the_composite_and_the_oracle(double_sided, batched, C):
+    """csrc/lighting.cu k_vertex_shade<false, *>: values and the three gradients against the reference's formula in
+    torch ops (pinned to the numpy oracle by the CPU test above)."""
+    rng = np.random.RandomState(11)
+    B, V = 3, 301
+    p, n, col, lc, g = _shade_inputs(rng, B, V, C, batched)
+    lp = rng.uniform(2, 3, (B, 3) if batched else (3,)).astype(np.float32)
+    tp, tn, tc = (torch.tensor(x, device="cuda", requires_grad=True) for x in (p, n, col))
+    tlp, tl, tg = (torch.tensor(x, device="cuda") for x in (lp, lc, g))
+    assert lighting._fusable_shade(tp, tn, tc, (tlp, tl))
+    out = lighting.diffuse_point(tp, tn, tc, tlp, tl, double_sided=double_sided)
+    out.backward(tg)
+    rp, rn, rc = (torch.tensor(x, device="cuda", requires_grad=True) for x in (p, n, col))
+    # the same call with a light that wants a gradient takes the torch formula
+    ref = lighting.diffuse_point(rp, rn, rc, tlp.clone().requires_grad_(True), tl, double_sided=double_sided)
+    ref.backward(tg)
+    torch.testing.assert_close(out, ref, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(tp.grad, rp.grad, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(tn.grad, rn.grad, rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(tc.grad, rc.grad, rtol=1e-5, atol=1e-6)
+    want = ol.diffuse_point(p.astype(np.float64), n.astype(np.float64), col.astype(np.float64), np.broadcast_to(lp, (B, 3)).astype(np.float64),
+                            np.broadcast_to(lc, (B, C)).astype(np.float64), double_sided)
+    np.testing.assert_allclose(out.detach().cpu().numpy(), want, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("double_sided", [True, False])
+@pytest.mark.parametrize("batched", [False, True])
+@pytest.mark.parametrize("shininess", [1.0, 4.0, 12.5])
+def test_fused_specular_directional_matches_the_composite_and_the_oracle(double_sided, batched, shininess):
+    """csrc/lighting.cu k_vertex_shade<true, *>: Phong term, values and the three gradients."""
+    rng = np.random.RandomState(12)
+    B, V, C = 3, 301, 3
+    p, n, col, lc, g = _shade_inputs(rng, B, V, C, batched)
+    d = rng.randn(*((B, 3) if batched else (3,))).astype(np.float32)
+    d /= np.linalg.norm(d, axis=-1, keepdims=True)
+    cam = rng.uniform(3, 4, (B, 3) if batched else (3,)).astype(np.float32)
+    sh = np.full((B,), shininess, np.float32) + (np.arange(B, dtype=np.float32) if batched else 0)
+    tp, tn, tc = (torch.tensor(x, device="cuda", requires_grad=True) for x in (p, n, col))
+    td, tl, tcam, tg = (torch.tensor(x, device="cuda") for x in (d, lc, cam, g))
+    tsh = torch.tensor(sh, device="cuda") if batched else shininess          # a Python number is the usual call
+    out = lighting.specular_directional(tp, tn, tc, td, tl, tcam, tsh, double_sided=double_sided)
+    assert out.grad_fn.name().startswith("_VertexShade")
+    out.backward(tg)
+    rp, rn, rc = (torch.tensor(x, device="cuda", requires_grad=True) for x in (p, n, col))
+    rsh = torch.tensor(sh if batched else np.float32(shininess), device="cuda")
+    ref = lighting.specular_directional(rp, rn, rc, td.clone().requires_grad_(True), tl, tcam, rsh, double_sided=double_sided)
+    assert not ref.grad_fn.name().startswith("_VertexShade")
+    ref.backward(tg)
+    torch.testing.assert_close(out, ref, rtol=2e-5, atol=1e-6)
+    torch.testing.assert_close(tp.grad, rp.grad, rtol=2e-4, atol=2e-5)
+    torch.testing.assert_close(tn.grad, rn.grad, rtol=2e-4, atol=2e-5)
+    torch.testing.assert_close(tc.grad, rc.grad, rtol=2e-5, atol=1e-6)
+    want = ol.specular_directional(p.astype(np.float64), n.astype(np.float64), col.astype(np.float64), np.broadcast_to(d, (B, 3)).astype(np.float64),
+                                   np.broadcast_to(lc, (B, C)).astype(np.float64), np.broadcast_to(cam, (B, 3)).astype(np.float64),
+                                   sh.astype(np.float64), double_sided)
+    np.testing.assert_allclose(out.detach().cpu().numpy(), want, rtol=1e-4, atol=1e-6)
