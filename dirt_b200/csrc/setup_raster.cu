@@ -53,11 +53,11 @@ constexpr int kWarpsPerCta = 8;
 #ifndef KLDCG
 #define KLDCG 0      // 1: the depth pre-load bypasses L1 (sees the reductions of this launch)
 #endif
-constexpr int kCtasPerSm = KCTAS;                     // the kernel waits on depth loads: occupancy over registers
+constexpr int kCtasPerSm = KCTAS;                     // launches without the pyramid test (the blind first launch, unordered meshes)
 constexpr int kCtasPerSmHiz = KCTAS_HIZ;              // the launches that test against the pyramid
 constexpr int ctas_per_sm(bool hiz) { return hiz ? kCtasPerSmHiz : kCtasPerSm; }
-constexpr int kFragRoundBlind = KFRAG;            // launch 0: no pre-load, the round only unrolls the loop
-constexpr int kFragRoundHiz = KFRAG_HIZ;                   // spans are 1-2 pixels on 3 lines out of 4 (profiles/r1_setup_notes.md)
+constexpr int kFragRoundBlind = KFRAG;                // launch 0: no pre-load, the round only unrolls the loop
+constexpr int kFragRoundHiz = KFRAG_HIZ;              // depths fetched together per round; spans are 1-2 pixels on 3 lines out of 4 (profiles/r1_setup_notes.md)
 constexpr long long kFewFaces = 4096;
 constexpr float kLineRcpAreaMin = 1.0f / (2.0f * 65536.0f * 1024.0f);   // 1 / |2 area| of a 1024 px triangle: fatter ones go to the tile path
 
