@@ -96,6 +96,39 @@ def test_shading_functions_match_the_oracle(double_sided):
                                ol.specular_directional(p, n, col, d, lc, cam, sh, double_sided), rtol=1e-10, atol=1e-14)
 
 
+def test_shading_known_answers_derived_by_hand():
+    """Pins the oracle's shading formulas (and with them the torch composites) by cases worked out on paper from
+    dirt/lighting.py:182-343 -- not by another implementation of the same code."""
+    n = np.array([[0., 0., 1.]])
+    col = np.array([[0.5, 0.25, 1.0]])
+    lc = np.array([2., 4., 1.])
+    # directional light shining straight down (-z) on an upward normal: cos = n . (-d) = 1; at 60 degrees: 0.5
+    np.testing.assert_allclose(ol.diffuse_directional(n, col, np.array([0., 0., -1.]), lc), [[1.0, 1.0, 1.0]], atol=1e-15)
+    d60 = np.array([np.sin(np.pi / 3), 0., -np.cos(np.pi / 3)])
+    np.testing.assert_allclose(ol.diffuse_directional(n, col, d60, lc), [[0.5, 0.5, 0.5]], atol=1e-15)
+    # the same light from below: double sided |cos| = 1, single sided 0
+    np.testing.assert_allclose(ol.diffuse_directional(n, col, np.array([0., 0., 1.]), lc, True), [[1.0, 1.0, 1.0]], atol=1e-15)
+    np.testing.assert_allclose(ol.diffuse_directional(n, col, np.array([0., 0., 1.]), lc, False), [[0.0, 0.0, 0.0]], atol=1e-15)
+    # point light two units above the vertex: the reference's `incident` points FROM the light TO the vertex, so
+    # cos = n . (p - l)/|p - l| = -1 -> lit only when double sided (dirt/lighting.py:333-343 as written)
+    p = np.array([[1., 2., 3.]])
+    lp = np.array([1., 2., 5.])
+    np.testing.assert_allclose(ol.diffuse_point(p, n, col, lp, lc, True), [[1.0, 1.0, 1.0]], atol=1e-11)
+    np.testing.assert_allclose(ol.diffuse_point(p, n, col, lp, lc, False), [[0.0, 0.0, 0.0]], atol=1e-15)
+    # Phong: light straight down, camera straight above: L = +z, R = -L + 2 (n.L) n = +z, T = +z -> cos = 1, any shininess
+    cam = np.array([1., 2., 10.])
+    np.testing.assert_allclose(ol.specular_directional(p, n, col, np.array([0., 0., -1.]), lc, cam, np.array(7.)), [[1.0, 1.0, 1.0]], atol=1e-10)
+    # camera 60 degrees off the mirror direction: cos = 0.5 -> 0.5 ** 3 = 0.125
+    cam60 = p[0] + 4. * np.array([np.sin(np.pi / 3), 0., np.cos(np.pi / 3)])
+    np.testing.assert_allclose(ol.specular_directional(p, n, col, np.array([0., 0., -1.]), lc, cam60, np.array(3.)),
+                               [[0.125, 0.125, 0.125]], atol=1e-10)
+    # and the torch composites give the same numbers
+    t = lambda *xs: [torch.tensor(x) for x in xs]  # noqa: E731
+    np.testing.assert_allclose(lighting.specular_directional(*t(p, n, col, np.array([0., 0., -1.]), lc, cam60, np.array(3.))).numpy(),
+                               [[0.125, 0.125, 0.125]], atol=1e-10)
+    np.testing.assert_allclose(lighting.diffuse_point(*t(p, n, col, lp, lc), double_sided=False).numpy(), [[0.0, 0.0, 0.0]], atol=1e-15)
+
+
 def test_split_vertices_by_face_matches_the_oracle():
     v, f = _cube()
     vb = np.stack([v, v * 2.0])
